@@ -1,0 +1,243 @@
+"""Array-level API over the C ABI: numpy arrays (host) or torch CUDA tensors (device) in, same kind out.
+
+PyTorch is only a carrier here: it owns device buffers and the current stream; every computation is a
+kernel of libth_b200.so.  Host arrays take the TH_MEM_HOST path (the library stages them itself), CUDA
+tensors the TH_MEM_DEVICE path (no copies, work is enqueued on torch's current stream).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import native
+from .native import NativeError, MEM_HOST, MEM_DEVICE  # noqa: F401
+
+MODE_STRICT, MODE_INCLUSIVE, MODE_UPCOMING = 0, 1, 2
+OWNER_ANY, OWNER_OTHER, OWNER_SAME = 0, 1, 2
+TH_ECAPACITY = -5
+
+
+def _is_torch_cuda(x) -> bool:
+    return hasattr(x, 'is_cuda') and bool(x.is_cuda)
+
+
+class _Args:
+    """Collects the arrays of one call, checks they live in one place and keeps them alive."""
+
+    def __init__(self, *probe):
+        self.device_mode = any(_is_torch_cuda(p) for p in probe if p is not None)
+        self.keep = []
+        self.torch = None
+        self.device_index = None
+        if self.device_mode:
+            import torch
+            self.torch = torch
+            for p in probe:
+                if p is not None and not _is_torch_cuda(p):
+                    raise TypeError('all arrays of a call must be CUDA tensors, or none of them')
+            self.device_index = next(p for p in probe if p is not None).device.index
+
+    @property
+    def mem(self) -> int:
+        return MEM_DEVICE if self.device_mode else MEM_HOST
+
+    def stream(self):
+        if self.device_mode:
+            return C.c_void_p(self.torch.cuda.current_stream(self.device_index).cuda_stream)
+        return C.c_void_p(0)
+
+    def inp(self, x, dtype=np.int64):
+        if x is None:
+            return C.c_void_p(0)
+        if self.device_mode:
+            want = {np.int64: self.torch.int64, np.uint8: self.torch.uint8, np.uint32: self.torch.int32}[dtype]
+            t = x if (x.dtype == want and x.is_contiguous()) else x.to(want).contiguous()
+            self.keep.append(t)
+            return C.c_void_p(t.data_ptr())
+        a = np.ascontiguousarray(x, dtype=dtype)
+        self.keep.append(a)
+        return C.c_void_p(a.ctypes.data)
+
+    def out(self, n: int, dtype=np.int64):
+        if self.device_mode:
+            want = {np.int64: self.torch.int64, np.uint8: self.torch.uint8, np.uint32: self.torch.int32}[dtype]
+            t = self.torch.empty(int(n), dtype=want, device='cuda:%d' % self.device_index)
+            self.keep.append(t)
+            return t, C.c_void_p(t.data_ptr())
+        a = np.empty(int(n), dtype=dtype)
+        self.keep.append(a)
+        return a, C.c_void_p(a.ctypes.data)
+
+
+def unpack_bits(words, m: int):
+    """bitmap words (uint32, bit i%32 of word i/32) -> bool[m] (host numpy)."""
+    if _is_torch_cuda(words):
+        words = words.cpu().numpy()
+    w = np.ascontiguousarray(words).view(np.uint32)
+    bits = np.unpackbits(w.view(np.uint8), bitorder='little')
+    return bits[:m].astype(bool)
+
+
+class Snapshot:
+    """Device-resident, indexed copy of the ``reservations`` table (tensorhive/models/Reservation.py:14-37)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = native.load()
+        self._h = C.c_void_p(0)
+        native.check(self._lib.th_snapshot_create(int(device), C.byref(self._h)))
+        self.device = int(device)
+        self.n = 0
+        self.n_uuids = 0
+
+    # -- lifecycle ---------------------------------------------------------------------------------
+    def close(self) -> None:
+        if self._h:
+            self._lib.th_snapshot_destroy(self._h)
+            self._h = C.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def load(self, id, uuid_id, start, end, owner, cancelled, n_uuids: int) -> 'Snapshot':
+        a = _Args(id, uuid_id, start, end, owner, cancelled)
+        n = int(len(id))
+        for name, col in (('uuid_id', uuid_id), ('start', start), ('end', end), ('owner', owner),
+                          ('cancelled', cancelled)):
+            if len(col) != n:
+                raise ValueError('column %s has %d rows, id has %d' % (name, len(col), n))
+        native.check(self._lib.th_snapshot_load(self._h, n, int(n_uuids), a.inp(id), a.inp(uuid_id), a.inp(start),
+                                                a.inp(end), a.inp(owner), a.inp(cancelled, np.uint8), a.mem, a.stream()))
+        self.n, self.n_uuids = n, int(n_uuids)
+        return self
+
+    def info(self) -> dict:
+        v = [C.c_int64(0) for _ in range(4)]
+        native.check(self._lib.th_snapshot_info(self._h, *[C.byref(x) for x in v]))
+        return {'n': v[0].value, 'n_uuids': v[1].value, 'device_bytes': v[2].value, 'radix_passes': v[3].value}
+
+    def export(self) -> dict:
+        """Indexed table back on the host, in snapshot order (uuid, start, id)."""
+        a = _Args()
+        cols = {}
+        ptrs = []
+        for name, dt, size in (('id', np.int64, self.n), ('uuid_id', np.int64, self.n), ('start', np.int64, self.n),
+                               ('end', np.int64, self.n), ('owner', np.int64, self.n), ('cancelled', np.uint8, self.n),
+                               ('seg_offsets', np.int64, self.n_uuids + 1)):
+            arr, p = a.out(size, dt)
+            cols[name] = arr
+            ptrs.append(p)
+        native.check(self._lib.th_snapshot_export(self._h, *ptrs, MEM_HOST, C.c_void_p(0)))
+        return cols
+
+    # -- R1 / R2 verdicts -----------------------------------------------------------------------------
+    def conflict_words(self, q_uuid, q_start, q_end, q_self=None, mode: int = MODE_STRICT):
+        """Raw bitmap words (uint32 numpy / int32 CUDA tensor)."""
+        a = _Args(q_uuid, q_start, q_end, q_self)
+        m = int(len(q_uuid))
+        if q_self is None and mode == MODE_STRICT:
+            q_self = np.full(m, -1, np.int64) if not a.device_mode else a.torch.full(
+                (m,), -1, dtype=a.torch.int64, device=q_uuid.device)
+        words, wp = a.out((m + 31) // 32, np.uint32)
+        native.check(self._lib.th_conflict_bitmap(self._h, m, a.inp(q_uuid), a.inp(q_start), a.inp(q_end),
+                                                  a.inp(q_self), int(mode), wp, a.mem, a.stream()))
+        return words
+
+    def conflict_bitmap(self, q_uuid, q_start, q_end, q_self=None, mode: int = MODE_STRICT) -> np.ndarray:
+        """bool[m]: the value ``Reservation.would_interfere`` returns for each candidate."""
+        return unpack_bits(self.conflict_words(q_uuid, q_start, q_end, q_self, mode), int(len(q_uuid)))
+
+    # -- R1..R4 row lists -------------------------------------------------------------------------------
+    def conflict_sets(self, q_uuid, q_start, q_end, q_self=None, mode: int = MODE_STRICT,
+                      capacity: Optional[int] = None):
+        """CSR (offsets[m+1], ids, cancelled).  Retries once with the exact capacity if the guess was short."""
+        a = _Args(q_uuid, q_start, q_end, q_self)
+        m = int(len(q_uuid))
+        cap = int(capacity) if capacity is not None else max(64, 2 * m)
+        needed = C.c_int64(0)
+        for _attempt in range(2):
+            offsets, op = a.out(m + 1, np.int64)
+            ids, ip = a.out(cap, np.int64)
+            canc, cp = a.out(cap, np.uint8)
+            rc = self._lib.th_conflict_sets(self._h, m, a.inp(q_uuid), a.inp(q_start), a.inp(q_end), a.inp(q_self),
+                                            int(mode), op, ip, cp, cap, C.byref(needed), a.mem, a.stream())
+            if rc == TH_ECAPACITY:
+                cap = int(needed.value)
+                continue
+            native.check(rc)
+            total = int(needed.value)
+            return offsets, ids[:total], canc[:total]
+        raise NativeError(TH_ECAPACITY, native.last_error())
+
+    # -- R3 / R4 per-uuid lookups -------------------------------------------------------------------------
+    def current_owner(self, now_us: int, device_out: bool = False):
+        a = _Args()
+        if device_out:
+            import torch
+            a.device_mode, a.torch, a.device_index = True, torch, self.device
+        res, rp = a.out(self.n_uuids)
+        own, op = a.out(self.n_uuids)
+        native.check(self._lib.th_current_owner(self._h, int(now_us), rp, op, a.mem, a.stream()))
+        return res, own
+
+    def upcoming(self, now_us: int, period_us: int, uuids):
+        a = _Args(uuids)
+        k = int(len(uuids))
+        outs = [a.out(k) for _ in range(4)]
+        native.check(self._lib.th_upcoming(self._h, int(now_us), int(period_us), k, a.inp(uuids),
+                                           outs[0][1], outs[1][1], outs[2][1], outs[3][1], a.mem, a.stream()))
+        return tuple(o[0] for o in outs)   # first_id, first_start, first_owner, count
+
+    def upcoming_owner_flags(self, now_us: int, period_us: int, task_uuid, task_owner, test: int):
+        a = _Args(task_uuid, task_owner)
+        t = int(len(task_uuid))
+        flags, fp = a.out(t, np.uint8)
+        native.check(self._lib.th_upcoming_owner_flags(self._h, int(now_us), int(period_us), t, a.inp(task_uuid),
+                                                       a.inp(task_owner), int(test), fp, a.mem, a.stream()))
+        return flags
+
+    # -- V ----------------------------------------------------------------------------------------------------
+    def violation_join(self, now_us: int, strict: bool, proc_uuid, proc_owner):
+        a = _Args(proc_uuid, proc_owner)
+        p = int(len(proc_uuid))
+        flags, fp = a.out(p, np.uint8)
+        res, rp = a.out(p)
+        native.check(self._lib.th_violation_join(self._h, int(now_us), 1 if strict else 0, p, a.inp(proc_uuid),
+                                                 a.inp(proc_owner), fp, rp, a.mem, a.stream()))
+        return flags, res
+
+
+def usage_reduce(uuid_offsets, ts, gpu, mem, win_uuid, win_start, win_end, device: int = 0):
+    """(sum_gpu, sum_mem, count, avg_gpu, avg_mem) per window; avg = sum // count or -1
+    (tensorhive/core/services/UsageLoggingService.py:25-30)."""
+    lib = native.load()
+    a = _Args(uuid_offsets, ts, gpu, mem, win_uuid, win_start, win_end)
+    s, w = int(len(ts)), int(len(win_uuid))
+    n_uuids = int(len(uuid_offsets)) - 1
+    outs = [a.out(w) for _ in range(5)]
+    dev = a.device_index if a.device_mode else int(device)
+    native.check(lib.th_usage_reduce(dev, s, n_uuids, a.inp(uuid_offsets), a.inp(ts), a.inp(gpu), a.inp(mem), w,
+                                     a.inp(win_uuid), a.inp(win_start), a.inp(win_end),
+                                     outs[0][1], outs[1][1], outs[2][1], outs[3][1], outs[4][1], a.mem, a.stream()))
+    return tuple(o[0] for o in outs)
+
+
+def sort_pairs(k_hi, k_lo, device: int = 0):
+    """Stable argsort of (k_hi, k_lo) pairs by K1 (the onesweep radix sort)."""
+    lib = native.load()
+    a = _Args(k_hi, k_lo)
+    n = int(len(k_hi))
+    perm, pp = a.out(n)
+    dev = a.device_index if a.device_mode else int(device)
+    native.check(lib.th_sort_pairs(dev, n, a.inp(k_hi), a.inp(k_lo), pp, a.mem, a.stream()))
+    return perm

@@ -1,0 +1,109 @@
+// Error plumbing, staging scratch and handle lifecycle of libth_b200.so.
+#include "th_common.cuh"
+#include <string.h>
+
+static thread_local char g_th_err[512] = "";
+
+void th_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_th_err, sizeof(g_th_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *th_last_error(void) { return g_th_err; }
+extern "C" int th_version(void) { return TH_ABI_VERSION; }
+
+// ---- ThScratch ---------------------------------------------------------------------------------------
+int ThScratch::alloc(void **out, size_t bytes) {
+    if (count >= (int)(sizeof(ptrs) / sizeof(ptrs[0]))) {
+        th_set_error("ThScratch: too many staging buffers");
+        return TH_EINTERNAL;
+    }
+    if (bytes == 0) bytes = 16;
+    void *p = nullptr;
+    cudaError_t e = cudaMallocAsync(&p, bytes, st);
+    if (e != cudaSuccess) {
+        th_set_error("cudaMallocAsync(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
+        return TH_ENOMEM;
+    }
+    ptrs[count++] = p;
+    *out = p;
+    return TH_OK;
+}
+
+int ThScratch::in(const void *src, size_t bytes, int mem, const void **out) {
+    if (mem == TH_MEM_DEVICE) { *out = src; return TH_OK; }
+    void *d = nullptr;
+    TH_TRY(alloc(&d, bytes));
+    if (bytes) TH_CUDA(cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st));
+    *out = d;
+    return TH_OK;
+}
+
+int ThScratch::out(void *dst, size_t bytes, int mem, void **out_dev) {
+    if (dst == nullptr) { *out_dev = nullptr; return TH_OK; }
+    if (mem == TH_MEM_DEVICE) { *out_dev = dst; return TH_OK; }
+    return alloc(out_dev, bytes);
+}
+
+int th_copy_back(void *host_dst, const void *dev_src, size_t bytes, int mem, cudaStream_t st) {
+    if (mem == TH_MEM_DEVICE || host_dst == nullptr || bytes == 0) return TH_OK;
+    TH_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, st));
+    return TH_OK;
+}
+
+// ---- handle lifecycle ---------------------------------------------------------------------------------
+static void th_snapshot_release(th_snapshot *h) {
+    if (h->seg) cudaFree(h->seg);
+    if (h->p1) cudaFree(h->p1);
+    if (h->p2) cudaFree(h->p2);
+    if (h->p3) cudaFree(h->p3);
+    if (h->p4) cudaFree(h->p4);
+    if (h->uuid) cudaFree(h->uuid);
+    h->seg = nullptr; h->p1 = nullptr; h->p2 = nullptr; h->p3 = nullptr; h->p4 = nullptr; h->uuid = nullptr;
+    h->loaded = 0; h->n = 0; h->n_uuids = 0; h->device_bytes = 0;
+}
+
+extern "C" int th_snapshot_create(int device, th_snapshot **out) {
+    TH_REQUIRE(out != nullptr, "th_snapshot_create: out is NULL");
+    int count = 0;
+    TH_CUDA(cudaGetDeviceCount(&count));
+    TH_REQUIRE(device >= 0 && device < count, "th_snapshot_create: device %d not in [0, %d)", device, count);
+    cudaDeviceProp prop;
+    TH_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        th_set_error("th_snapshot_create: device %d is sm_%d%d; this library is built for sm_100a only", device,
+                     prop.major, prop.minor);
+        return TH_ESTATE;
+    }
+    th_snapshot *h = new th_snapshot();
+    memset(h, 0, sizeof(*h));
+    h->device = device;
+    *out = h;
+    return TH_OK;
+}
+
+extern "C" int th_snapshot_destroy(th_snapshot *h) {
+    if (!h) return TH_OK;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(h->device);
+    th_snapshot_release(h);
+    cudaSetDevice(prev);
+    delete h;
+    return TH_OK;
+}
+
+extern "C" int th_snapshot_info(const th_snapshot *h, int64_t *n, int64_t *n_uuids, int64_t *device_bytes,
+                                int64_t *radix_passes) {
+    TH_REQUIRE(h != nullptr, "th_snapshot_info: handle is NULL");
+    if (n) *n = h->n;
+    if (n_uuids) *n_uuids = h->n_uuids;
+    if (device_bytes) *device_bytes = h->device_bytes;
+    if (radix_passes) *radix_passes = h->radix_passes;
+    return TH_OK;
+}
+
+// used by th_snapshot.cu
+void th_snapshot_release_internal(th_snapshot *h) { th_snapshot_release(h); }

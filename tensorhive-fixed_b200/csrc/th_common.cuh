@@ -1,0 +1,135 @@
+// Shared declarations for libth_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/th_b200.h"
+
+#ifndef TH_NUM_SMS
+#define TH_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+#endif
+
+typedef long long i64;
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef unsigned char u8;
+
+#define TH_I64_MIN (-0x7fffffffffffffffLL - 1)
+#define TH_I64_MAX (0x7fffffffffffffffLL)
+
+// ---- error plumbing -------------------------------------------------------------------------------
+void th_set_error(const char *fmt, ...);
+
+#define TH_CUDA(call)                                                                          \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            th_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return e__ == cudaErrorMemoryAllocation ? TH_ENOMEM : TH_ECUDA;                    \
+        }                                                                                      \
+    } while (0)
+
+#define TH_TRY(call)              \
+    do {                          \
+        int r__ = (call);         \
+        if (r__ != TH_OK) return r__; \
+    } while (0)
+
+#define TH_REQUIRE(cond, ...)         \
+    do {                              \
+        if (!(cond)) {                \
+            th_set_error(__VA_ARGS__); \
+            return TH_EINVAL;         \
+        }                             \
+    } while (0)
+
+// ---- records moved by the radix sort (K1) ------------------------------------------------------------
+// 16 bytes so that one record is one 128-bit load/store.
+struct __align__(16) ThRec {
+    u64 k0;   // low key word  (start_us - min_start, or id - min_id)
+    u32 k1;   // high key word (uuid_id, or query index)
+    u32 idx;  // original row
+};
+
+// ---- per-row index entries of a loaded snapshot -------------------------------------------------------
+// All pairs are 16 B so that every probe is one 128-bit load.
+struct __align__(16) ThP1 { i64 start; i64 m1;  };  // m1  = max end over non-cancelled rows of the segment prefix
+struct __align__(16) ThP2 { i64 a1;    i64 m2;  };  // a1  = id of the row attaining m1, m2 = max over the others
+struct __align__(16) ThP3 { i64 end;   i64 idc; };  // idc = id | cancelled << 63
+struct __align__(16) ThP4 { i64 owner; i64 mall; }; // mall = max end over ALL rows of the segment prefix
+
+struct th_snapshot {
+    int device;
+    int loaded;
+    i64 n, n_uuids;
+    i64 device_bytes;
+    i64 radix_passes;
+    int *seg;      // [n_uuids + 1] segment offsets (int32: n < 2^30)
+    ThP1 *p1;      // [n]
+    ThP2 *p2;      // [n]
+    ThP3 *p3;      // [n]
+    ThP4 *p4;      // [n]
+    u32 *uuid;     // [n] uuid of each sorted row (export / rebuild)
+};
+
+// ---- device helpers -------------------------------------------------------------------------------------
+__device__ __forceinline__ longlong2 th_ld16(const void *p) {
+    // read-only 128-bit load; the index entries are immutable while a snapshot is live
+    return __ldg(reinterpret_cast<const longlong2 *>(p));
+}
+__device__ __forceinline__ i64 th_idc_id(i64 idc) { return idc & TH_I64_MAX; }
+__device__ __forceinline__ bool th_idc_cancelled(i64 idc) { return idc < 0; }
+
+__device__ __forceinline__ i64 th_warp_min(i64 v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        i64 t = __shfl_xor_sync(0xffffffffu, v, o);
+        v = t < v ? t : v;
+    }
+    return v;
+}
+__device__ __forceinline__ i64 th_warp_sum(i64 v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- host-side scratch: stream-ordered device buffers used to stage TH_MEM_HOST calls -----------------
+struct ThScratch {
+    cudaStream_t st;
+    void *ptrs[24];
+    int count;
+    explicit ThScratch(cudaStream_t s) : st(s), count(0) {}
+    ~ThScratch() {
+        for (int i = 0; i < count; ++i) cudaFreeAsync(ptrs[i], st);
+    }
+    int alloc(void **out, size_t bytes);
+    // device copy of a host array (or the pointer itself when mem == TH_MEM_DEVICE)
+    int in(const void *src, size_t bytes, int mem, const void **out);
+    // device buffer standing in for a host output (or the pointer itself)
+    int out(void *dst, size_t bytes, int mem, void **out_dev);
+};
+int th_copy_back(void *host_dst, const void *dev_src, size_t bytes, int mem, cudaStream_t st);
+
+// ---- K1 internal entry (th_sort.cu) ----------------------------------------------------------------------
+// Sorts n records by (k1, k0) ascending, stable, using only the low k0_bits / k1_bits of each word.
+// `a` holds the input; the sorted result is returned in *sorted (either a or b).  `passes` gets the
+// number of digit passes that ran.
+int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **sorted, int *passes,
+                  cudaStream_t st);
+
+static inline int th_bits_for(u64 maxval) {
+    int b = 0;
+    while (maxval) { ++b; maxval >>= 1; }
+    return b;
+}
+static inline int th_grid_for(i64 work_items, int per_block, int max_waves = 32) {
+    i64 blocks = (work_items + per_block - 1) / per_block;
+    if (blocks < 1) blocks = 1;
+    // round up to whole waves of the 148 SMs once the grid is larger than one wave
+    i64 cap = (i64)TH_NUM_SMS * max_waves;
+    if (blocks > cap) blocks = cap;
+    if (blocks > TH_NUM_SMS) blocks = ((blocks + TH_NUM_SMS - 1) / TH_NUM_SMS) * TH_NUM_SMS;
+    return (int)blocks;
+}

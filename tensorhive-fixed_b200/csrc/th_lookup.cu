@@ -1,0 +1,317 @@
+// K3 / K5 -- per-uuid point-in-time lookups and the joins the service ticks run on top of them (sm_100a).
+//
+// Replaces (reference):
+//   Reservation.current_events(uuid)[0]           tensorhive/models/Reservation.py:89-104 as used by
+//                                                 tensorhive/core/services/ProtectionService.py:90-93
+//   Reservation.upcoming_events_for_resource      Reservation.py:106-118 as used by
+//                                                 JobSchedulingService.py:94-102,117-132 and scheduling.py:48-53
+//   ProtectionService.do_run join                 ProtectionService.py:84-102
+//
+// One warp per uuid / task: a warp-uniform binary search finds the end of the candidate prefix, then the
+// warp walks backwards 32 rows per step with 16-byte loads until the running maximum of non-cancelled
+// `end` (m1) proves nothing earlier can still be current.
+#include "th_common.cuh"
+
+namespace {
+
+struct DeviceGuard {
+    int prev;
+    bool ok;
+    explicit DeviceGuard(int dev) : prev(0), ok(true) {
+        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
+        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
+constexpr int LK_THREADS = 256;
+constexpr int LK_WARPS = LK_THREADS / 32;
+
+template <bool STRICT>
+__device__ __forceinline__ int lk_prefix_end(const ThP1 *__restrict__ p1, int lo, int hi, i64 key) {
+    while (lo < hi) {
+        const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+        const i64 s = __ldg(&p1[mid].start);
+        const bool left = STRICT ? (s < key) : (s <= key);
+        if (left) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// lowest-id non-cancelled row of segment [lo, hi) with start <= now <= end; returns row index or -1 (all lanes)
+__device__ __forceinline__ int lk_current_row(const ThP1 *__restrict__ p1, const ThP3 *__restrict__ p3, int lo, int hi,
+                                              i64 now, int lane, i64 *best_id_out) {
+    int c1 = lk_prefix_end<false>(p1, lo, hi, now);   // rows with start <= now
+    i64 best_id = TH_I64_MAX;
+    int best_row = -1;
+    while (c1 > lo && __ldg(&p1[c1 - 1].m1) >= now) {
+        const int c0 = c1 - 32 > lo ? c1 - 32 : lo;
+        const int j = c0 + lane;
+        if (j < c1) {
+            const longlong2 e = th_ld16(&p3[j]);   // {end, idc}
+            if (!th_idc_cancelled(e.y) && e.x >= now && th_idc_id(e.y) < best_id) {
+                best_id = th_idc_id(e.y);
+                best_row = j;
+            }
+        }
+        c1 = c0;
+    }
+    const i64 wmin = th_warp_min(best_id);
+    const u32 who = __ballot_sync(0xffffffffu, best_id == wmin && best_row >= 0);
+    int row = -1;
+    if (who) row = __shfl_sync(0xffffffffu, best_row, __ffs(who) - 1);
+    *best_id_out = wmin;
+    return row;
+}
+
+__global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+                                                                const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
+                                                                i64 n_uuids, i64 now, i64 *__restrict__ out_res,
+                                                                i64 *__restrict__ out_owner) {
+    const int lane = threadIdx.x & 31;
+    const i64 wstride = (i64)gridDim.x * LK_WARPS;
+    for (i64 u = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); u < n_uuids; u += wstride) {
+        i64 id;
+        const int row = lk_current_row(p1, p3, seg[u], seg[u + 1], now, lane, &id);
+        if (lane == 0) {
+            out_res[u] = row >= 0 ? id : -1;
+            out_owner[u] = row >= 0 ? __ldg(&p4[row].owner) : -1;
+        }
+    }
+}
+
+// Walks the rows of upcoming_events_for_resource(uuid, period) for one warp:
+//   (start < now AND end > now) OR (now <= start <= now + period), cancelled rows dropped.
+// Calls f(row, owner-needed?) through the accumulators below; returns count and the first row in
+// (start, id) order = the lowest row index.
+struct UpAcc {
+    int count;
+    int first_row;
+    int owner_hit;   // any matching row whose owner passes the test
+};
+
+template <bool WANT_OWNER>
+__device__ __forceinline__ UpAcc lk_upcoming(const ThP1 *__restrict__ p1, const ThP3 *__restrict__ p3,
+                                             const ThP4 *__restrict__ p4, int lo, int hi, i64 now, i64 later, int lane,
+                                             int test, i64 owner) {
+    UpAcc a;
+    a.count = 0; a.first_row = 0x7fffffff; a.owner_hit = 0;
+    int c1 = lk_prefix_end<false>(p1, lo, hi, later);   // rows with start <= now + period
+    while (c1 > lo) {
+        const longlong2 top = th_ld16(&p1[c1 - 1]);     // {start, m1}
+        if (!(top.x >= now || top.y > now)) break;     // earlier rows start before now and none is still running
+        const int c0 = c1 - 32 > lo ? c1 - 32 : lo;
+        const int j = c0 + lane;
+        bool mt = false;
+        if (j < c1) {
+            const longlong2 e = th_ld16(&p3[j]);        // {end, idc}
+            const i64 s = __ldg(&p1[j].start);
+            mt = !th_idc_cancelled(e.y) && (s >= now || e.x > now);
+        }
+        bool oh = false;
+        if (WANT_OWNER && mt) {
+            const i64 o = __ldg(&p4[j].owner);
+            oh = test == TH_OWNER_ANY ? true : (test == TH_OWNER_OTHER ? (o != owner) : (o == owner));
+        }
+        const u32 bal = __ballot_sync(0xffffffffu, mt);
+        if (bal) {
+            a.count += __popc(bal);
+            a.first_row = c0 + (__ffs(bal) - 1);        // chunks go downwards, so the last one seen wins
+        }
+        if (WANT_OWNER && __any_sync(0xffffffffu, oh)) a.owner_hit = 1;
+        c1 = c0;
+    }
+    return a;
+}
+
+__global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+                                                                 const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
+                                                                 i64 n_uuids, i64 now, i64 later, i64 k,
+                                                                 const i64 *__restrict__ uuids, i64 *__restrict__ o_id,
+                                                                 i64 *__restrict__ o_start, i64 *__restrict__ o_owner,
+                                                                 i64 *__restrict__ o_count) {
+    const int lane = threadIdx.x & 31;
+    const i64 wstride = (i64)gridDim.x * LK_WARPS;
+    for (i64 q = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); q < k; q += wstride) {
+        const i64 u = uuids[q];
+        UpAcc a;
+        a.count = 0; a.first_row = 0; a.owner_hit = 0;
+        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(p1, p3, p4, seg[u], seg[u + 1], now, later, lane, 0, 0);
+        if (lane == 0) {
+            if (a.count > 0) {
+                const int r = a.first_row;
+                o_id[q] = th_idc_id(__ldg(&p3[r].idc));
+                o_start[q] = __ldg(&p1[r].start);
+                o_owner[q] = __ldg(&p4[r].owner);
+            } else {
+                o_id[q] = -1; o_start[q] = -1; o_owner[q] = -1;
+            }
+            o_count[q] = a.count;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+                                                                    const ThP3 *__restrict__ p3,
+                                                                    const ThP4 *__restrict__ p4, i64 n_uuids, i64 now,
+                                                                    i64 later, i64 t, const i64 *__restrict__ task_uuid,
+                                                                    const i64 *__restrict__ task_owner, int test,
+                                                                    u8 *__restrict__ out_flag) {
+    const int lane = threadIdx.x & 31;
+    const i64 wstride = (i64)gridDim.x * LK_WARPS;
+    for (i64 q = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); q < t; q += wstride) {
+        const i64 u = task_uuid[q];
+        int flag = 0;
+        if (u >= 0 && u < n_uuids) {
+            const UpAcc a = lk_upcoming<true>(p1, p3, p4, seg[u], seg[u + 1], now, later, lane, test, task_owner[q]);
+            flag = a.owner_hit;
+        }
+        if (lane == 0) out_flag[q] = (u8)flag;
+    }
+}
+
+// ProtectionService.py:89-102 for one process row, given the per-uuid current reservation table
+__global__ void __launch_bounds__(256) k5_violation_kernel(const i64 *__restrict__ cur_res, const i64 *__restrict__ cur_owner,
+                                                           i64 n_uuids, int strict, i64 p,
+                                                           const i64 *__restrict__ proc_uuid,
+                                                           const i64 *__restrict__ proc_owner, u8 *__restrict__ out_flag,
+                                                           i64 *__restrict__ out_res) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < p; i += (i64)gridDim.x * blockDim.x) {
+        const i64 u = proc_uuid[i];
+        i64 res = -1, owner = -1;
+        if (u >= 0 && u < n_uuids) { res = cur_res[u]; owner = cur_owner[u]; }
+        u8 flag = 0;
+        i64 rid = -1;
+        if (res >= 0) {
+            // a reservation is current: `reservation.user is None` (owner < 0) silences the GPU (:94-95)
+            if (owner >= 0 && proc_owner[i] != owner) { flag = 1; rid = res; }
+        } else if (strict) {
+            flag = 1;   // unreserved GPU in strict mode: every process is an intruder, reservation=None (:100-102)
+        }
+        out_flag[i] = flag;
+        out_res[i] = rid;
+    }
+}
+
+}  // namespace
+
+extern "C" int th_current_owner(const th_snapshot *h, int64_t now_us, int64_t *out_res_id, int64_t *out_owner, int mem,
+                                void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_current_owner: snapshot not loaded");
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_current_owner: bad mem flag %d", mem);
+    if (h->n_uuids == 0) return TH_OK;
+    TH_REQUIRE(out_res_id && out_owner, "th_current_owner: NULL output");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_current_owner: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zu = (size_t)h->n_uuids;
+    void *d_res, *d_own;
+    TH_TRY(sc.out(out_res_id, 8 * zu, mem, &d_res));
+    TH_TRY(sc.out(out_owner, 8 * zu, mem, &d_own));
+    k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids,
+                                                                                    now_us, (i64 *)d_res, (i64 *)d_own);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(out_res_id, d_res, 8 * zu, mem, st));
+    TH_TRY(th_copy_back(out_owner, d_own, 8 * zu, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_us, int64_t k, const int64_t *uuids,
+                           int64_t *out_first_id, int64_t *out_first_start, int64_t *out_first_owner,
+                           int64_t *out_count, int mem, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_upcoming: snapshot not loaded");
+    TH_REQUIRE(k >= 0 && period_us >= 0, "th_upcoming: negative k or period");
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_upcoming: bad mem flag %d", mem);
+    if (k == 0) return TH_OK;
+    TH_REQUIRE(uuids && out_first_id && out_first_start && out_first_owner && out_count, "th_upcoming: NULL array");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_upcoming: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zk = (size_t)k;
+    const void *d_u;
+    void *d_id, *d_s, *d_o, *d_c;
+    TH_TRY(sc.in(uuids, 8 * zk, mem, &d_u));
+    TH_TRY(sc.out(out_first_id, 8 * zk, mem, &d_id));
+    TH_TRY(sc.out(out_first_start, 8 * zk, mem, &d_s));
+    TH_TRY(sc.out(out_first_owner, 8 * zk, mem, &d_o));
+    TH_TRY(sc.out(out_count, 8 * zk, mem, &d_c));
+    k3_upcoming_kernel<<<th_grid_for(k, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+                                                                            now_us + period_us, k, (const i64 *)d_u,
+                                                                            (i64 *)d_id, (i64 *)d_s, (i64 *)d_o, (i64 *)d_c);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(out_first_id, d_id, 8 * zk, mem, st));
+    TH_TRY(th_copy_back(out_first_start, d_s, 8 * zk, mem, st));
+    TH_TRY(th_copy_back(out_first_owner, d_o, 8 * zk, mem, st));
+    TH_TRY(th_copy_back(out_count, d_c, 8 * zk, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+extern "C" int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int64_t period_us, int64_t t,
+                                       const int64_t *task_uuid, const int64_t *task_owner, int test,
+                                       uint8_t *out_flag_u8, int mem, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_upcoming_owner_flags: snapshot not loaded");
+    TH_REQUIRE(t >= 0 && period_us >= 0, "th_upcoming_owner_flags: negative t or period");
+    TH_REQUIRE(test >= TH_OWNER_ANY && test <= TH_OWNER_SAME, "th_upcoming_owner_flags: bad test %d", test);
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_upcoming_owner_flags: bad mem flag %d", mem);
+    if (t == 0) return TH_OK;
+    TH_REQUIRE(task_uuid && task_owner && out_flag_u8, "th_upcoming_owner_flags: NULL array");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_upcoming_owner_flags: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zt = (size_t)t;
+    const void *d_u, *d_o;
+    void *d_f;
+    TH_TRY(sc.in(task_uuid, 8 * zt, mem, &d_u));
+    TH_TRY(sc.in(task_owner, 8 * zt, mem, &d_o));
+    TH_TRY(sc.out(out_flag_u8, zt, mem, &d_f));
+    k5_owner_flags_kernel<<<th_grid_for(t, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+                                                                               now_us + period_us, t, (const i64 *)d_u,
+                                                                               (const i64 *)d_o, test, (u8 *)d_f);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(out_flag_u8, d_f, zt, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+extern "C" int th_violation_join(const th_snapshot *h, int64_t now_us, int strict, int64_t p, const int64_t *proc_uuid,
+                                 const int64_t *proc_owner, uint8_t *out_flag_u8, int64_t *out_res_id, int mem,
+                                 void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_violation_join: snapshot not loaded");
+    TH_REQUIRE(p >= 0, "th_violation_join: negative p");
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_violation_join: bad mem flag %d", mem);
+    if (p == 0) return TH_OK;
+    TH_REQUIRE(proc_uuid && proc_owner && out_flag_u8 && out_res_id, "th_violation_join: NULL array");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_violation_join: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zp = (size_t)p, zu = (size_t)h->n_uuids;
+    // scratch: the per-uuid "current reservation" table the join probes
+    i64 *cur_res, *cur_owner;
+    TH_TRY(sc.alloc((void **)&cur_res, 8 * (zu ? zu : 1)));
+    TH_TRY(sc.alloc((void **)&cur_owner, 8 * (zu ? zu : 1)));
+    if (h->n_uuids > 0) {
+        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4,
+                                                                                        h->n_uuids, now_us, cur_res,
+                                                                                        cur_owner);
+    }
+    const void *d_u, *d_o;
+    void *d_f, *d_r;
+    TH_TRY(sc.in(proc_uuid, 8 * zp, mem, &d_u));
+    TH_TRY(sc.in(proc_owner, 8 * zp, mem, &d_o));
+    TH_TRY(sc.out(out_flag_u8, zp, mem, &d_f));
+    TH_TRY(sc.out(out_res_id, 8 * zp, mem, &d_r));
+    k5_violation_kernel<<<th_grid_for(p, 256 * 4, 16), 256, 0, st>>>(cur_res, cur_owner, h->n_uuids, strict ? 1 : 0, p,
+                                                                     (const i64 *)d_u, (const i64 *)d_o, (u8 *)d_f,
+                                                                     (i64 *)d_r);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(out_flag_u8, d_f, zp, mem, st));
+    TH_TRY(th_copy_back(out_res_id, d_r, 8 * zp, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}

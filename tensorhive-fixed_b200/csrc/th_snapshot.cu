@@ -1,0 +1,420 @@
+// Snapshot load: upload the `reservations` columns, sort them by (uuid_id, start, id) with K1 and build
+// the per-row index every query kernel probes (segment offsets + running maxima of `end`).
+//
+// Reference: class Reservation columns (tensorhive/models/Reservation.py:14-37).  The reference has no
+// index at all; every predicate is a full table scan inside SQLite.  The index built here lets
+//   - would_interfere (:120-130) be answered by ONE lower-bound search plus one 16-byte probe:
+//       rows with start < qe are a prefix of the uuid's segment; a conflict exists iff the largest `end`
+//       among the non-cancelled rows of that prefix exceeds qs.  `id != self` is handled by keeping the
+//       top-2 maxima with the id of the top one (m1/a1/m2).
+//   - the list-returning predicates walk backwards from the prefix end only while the running maximum
+//     over ALL rows (mall) says a match can still exist.
+#include "th_common.cuh"
+
+void th_snapshot_release_internal(th_snapshot *h);
+
+namespace {
+
+struct LoadStats {
+    i64 min_start, max_start, min_id, max_id, min_uuid, max_uuid;
+    u64 id_inversions;
+};
+
+__global__ void __launch_bounds__(256) ld_stats_kernel(const i64 *__restrict__ id, const i64 *__restrict__ uuid,
+                                                       const i64 *__restrict__ start, i64 n, LoadStats *out) {
+    i64 mn_s = TH_I64_MAX, mx_s = TH_I64_MIN, mn_i = TH_I64_MAX, mx_i = TH_I64_MIN, mn_u = TH_I64_MAX, mx_u = TH_I64_MIN;
+    u64 inv = 0;
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
+        const i64 s = start[i], d = id[i], u = uuid[i];
+        mn_s = s < mn_s ? s : mn_s; mx_s = s > mx_s ? s : mx_s;
+        mn_i = d < mn_i ? d : mn_i; mx_i = d > mx_i ? d : mx_i;
+        mn_u = u < mn_u ? u : mn_u; mx_u = u > mx_u ? u : mx_u;
+        if (i + 1 < n && id[i + 1] <= d) ++inv;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        i64 t;
+        t = __shfl_xor_sync(0xffffffffu, mn_s, o); mn_s = t < mn_s ? t : mn_s;
+        t = __shfl_xor_sync(0xffffffffu, mx_s, o); mx_s = t > mx_s ? t : mx_s;
+        t = __shfl_xor_sync(0xffffffffu, mn_i, o); mn_i = t < mn_i ? t : mn_i;
+        t = __shfl_xor_sync(0xffffffffu, mx_i, o); mx_i = t > mx_i ? t : mx_i;
+        t = __shfl_xor_sync(0xffffffffu, mn_u, o); mn_u = t < mn_u ? t : mn_u;
+        t = __shfl_xor_sync(0xffffffffu, mx_u, o); mx_u = t > mx_u ? t : mx_u;
+        inv += __shfl_xor_sync(0xffffffffu, inv, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&out->min_start, mn_s); atomicMax(&out->max_start, mx_s);
+        atomicMin(&out->min_id, mn_i);    atomicMax(&out->max_id, mx_i);
+        atomicMin(&out->min_uuid, mn_u);  atomicMax(&out->max_uuid, mx_u);
+        if (inv) atomicAdd((u64 *)&out->id_inversions, inv);
+    }
+}
+
+// records keyed by id (only when the caller's rows are not already in ascending-id order)
+__global__ void __launch_bounds__(256) ld_idrec_kernel(const i64 *__restrict__ id, i64 n, i64 min_id, ThRec *rec) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
+        ThRec r;
+        r.k0 = (u64)(id[i] - min_id); r.k1 = 0; r.idx = (u32)i;
+        rec[i] = r;
+    }
+}
+
+// records keyed by (uuid, start - min_start); `order` (optional) gives the ascending-id visiting order
+__global__ void __launch_bounds__(256) ld_keyrec_kernel(const i64 *__restrict__ uuid, const i64 *__restrict__ start,
+                                                        const ThRec *__restrict__ order, i64 n, i64 min_start,
+                                                        ThRec *rec) {
+    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (i64)gridDim.x * blockDim.x) {
+        const u32 i = order ? order[j].idx : (u32)j;
+        ThRec r;
+        r.k0 = (u64)(start[i] - min_start); r.k1 = (u32)uuid[i]; r.idx = i;
+        rec[j] = r;
+    }
+}
+
+// gather the payload columns into snapshot order and derive the segment offsets
+__global__ void __launch_bounds__(256) ld_finalize_kernel(const ThRec *__restrict__ rec, i64 n, i64 n_uuids,
+                                                          i64 min_start, const i64 *__restrict__ id,
+                                                          const i64 *__restrict__ end, const i64 *__restrict__ owner,
+                                                          const u8 *__restrict__ canc, ThP1 *p1, ThP3 *p3, ThP4 *p4,
+                                                          u32 *uuid_out, int *seg) {
+    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (i64)gridDim.x * blockDim.x) {
+        const ThRec r = rec[j];
+        const u32 i = r.idx;
+        p1[j].start = (i64)r.k0 + min_start;
+        ThP3 e;
+        e.end = end[i];
+        e.idc = id[i] | (canc[i] ? TH_I64_MIN : 0);
+        p3[j] = e;
+        p4[j].owner = owner[i];
+        uuid_out[j] = r.k1;
+        const i64 cur = r.k1;
+        const i64 prev = j > 0 ? (i64)rec[j - 1].k1 : -1;
+        for (i64 u = prev + 1; u <= cur; ++u) seg[u] = (int)j;
+        if (j == n - 1)
+            for (i64 u = cur + 1; u <= n_uuids; ++u) seg[u] = (int)n;
+    }
+}
+
+// ---- segmented running maxima ----------------------------------------------------------------------------
+struct St {
+    i64 m1, a1, m2, mall;
+    int flag;   // a segment head lies inside the span this state summarises
+};
+__device__ __forceinline__ St st_identity() {
+    St s; s.m1 = TH_I64_MIN; s.a1 = -1; s.m2 = TH_I64_MIN; s.mall = TH_I64_MIN; s.flag = 0; return s;
+}
+// L covers earlier rows than R.  Ties keep the earlier row as top-1; the later equal value becomes m2.
+__device__ __forceinline__ St st_combine(const St &L, const St &R) {
+    if (R.flag) return R;
+    St o;
+    o.flag = L.flag;
+    o.mall = L.mall > R.mall ? L.mall : R.mall;
+    if (R.m1 > L.m1) {
+        o.m1 = R.m1; o.a1 = R.a1;
+        o.m2 = L.m1 > R.m2 ? L.m1 : R.m2;
+    } else {
+        o.m1 = L.m1; o.a1 = L.a1;
+        o.m2 = L.m2 > R.m1 ? L.m2 : R.m1;
+    }
+    return o;
+}
+__device__ __forceinline__ St st_shfl_up(const St &s, int o) {
+    St t;
+    t.m1 = __shfl_up_sync(0xffffffffu, s.m1, o);
+    t.a1 = __shfl_up_sync(0xffffffffu, s.a1, o);
+    t.m2 = __shfl_up_sync(0xffffffffu, s.m2, o);
+    t.mall = __shfl_up_sync(0xffffffffu, s.mall, o);
+    t.flag = __shfl_up_sync(0xffffffffu, s.flag, o);
+    return t;
+}
+
+constexpr int SC_THREADS = 256;
+constexpr int SC_IPT = 8;
+constexpr int SC_TILE = SC_THREADS * SC_IPT;
+
+// block-wide inclusive scan of one St per thread; returns the thread's EXCLUSIVE prefix and (in *total,
+// valid for every thread) the block aggregate
+__device__ __forceinline__ St st_block_exclusive(const St &agg, St *smem_wtot, St *total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    St inc = agg;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        St t = st_shfl_up(inc, o);
+        if (lane >= o) inc = st_combine(t, inc);
+    }
+    St excl = st_shfl_up(inc, 1);
+    if (lane == 0) excl = st_identity();
+    if (lane == 31) smem_wtot[warp] = inc;
+    __syncthreads();
+    St pre = st_identity();
+    for (int w = 0; w < warp; ++w) pre = st_combine(pre, smem_wtot[w]);
+    St tot = pre;
+    for (int w = warp; w < SC_THREADS / 32; ++w) tot = st_combine(tot, smem_wtot[w]);
+    *total = tot;
+    __syncthreads();
+    return st_combine(pre, excl);
+}
+
+// A: tile-local segmented scan; writes tile-local m1/a1/m2/mall and the tile aggregate
+__global__ void __launch_bounds__(SC_THREADS) sc_local_kernel(const u32 *__restrict__ uuid, const ThP3 *__restrict__ p3,
+                                                              i64 n, ThP1 *p1, ThP2 *p2, ThP4 *p4, St *tile_agg) {
+    __shared__ St wtot[SC_THREADS / 32];
+    const i64 tile_start = (i64)blockIdx.x * SC_TILE;
+    const i64 j0 = tile_start + (i64)threadIdx.x * SC_IPT;
+    St loc[SC_IPT];
+    St run = st_identity();
+    u32 prev_u = (j0 > 0 && j0 < n) ? uuid[j0 - 1] : 0xffffffffu;
+#pragma unroll
+    for (int k = 0; k < SC_IPT; ++k) {
+        const i64 j = j0 + k;
+        if (j < n) {
+            const u32 u = uuid[j];
+            const ThP3 e = p3[j];
+            St x;
+            const bool c = th_idc_cancelled(e.idc);
+            x.m1 = c ? TH_I64_MIN : e.end;
+            x.a1 = c ? -1 : th_idc_id(e.idc);
+            x.m2 = TH_I64_MIN;
+            x.mall = e.end;
+            x.flag = (j == 0 || u != prev_u) ? 1 : 0;
+            run = st_combine(run, x);
+            prev_u = u;
+        }
+        loc[k] = run;
+    }
+    St total;
+    const St excl = st_block_exclusive(run, wtot, &total);
+#pragma unroll
+    for (int k = 0; k < SC_IPT; ++k) {
+        const i64 j = j0 + k;
+        if (j < n) {
+            const St f = st_combine(excl, loc[k]);
+            p1[j].m1 = f.m1;
+            ThP2 q; q.a1 = f.a1; q.m2 = f.m2;
+            p2[j] = q;
+            p4[j].mall = f.mall;
+        }
+    }
+    if (threadIdx.x == 0) tile_agg[blockIdx.x] = total;
+}
+
+// B: exclusive scan of the tile aggregates (one block; each thread walks a contiguous chunk of tiles)
+__global__ void __launch_bounds__(SC_THREADS) sc_carry_kernel(St *tile_agg, i64 tiles) {
+    __shared__ St wtot[SC_THREADS / 32];
+    const i64 chunk = (tiles + SC_THREADS - 1) / SC_THREADS;
+    const i64 t0 = (i64)threadIdx.x * chunk;
+    const i64 t1 = t0 + chunk < tiles ? t0 + chunk : tiles;
+    St run = st_identity();
+    for (i64 t = t0; t < t1; ++t) run = st_combine(run, tile_agg[t]);
+    St total;
+    St excl = st_block_exclusive(run, wtot, &total);
+    for (i64 t = t0; t < t1; ++t) {
+        const St a = tile_agg[t];
+        tile_agg[t] = excl;          // becomes the carry INTO tile t
+        excl = st_combine(excl, a);
+    }
+}
+
+// C: rows whose segment began in an earlier tile fold the carry in
+__global__ void __launch_bounds__(SC_THREADS) sc_fix_kernel(const u32 *__restrict__ uuid, const int *__restrict__ seg,
+                                                            i64 n, const St *__restrict__ carry, ThP1 *p1, ThP2 *p2,
+                                                            ThP4 *p4) {
+    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (i64)gridDim.x * blockDim.x) {
+        const i64 tile = j / SC_TILE;
+        if (tile == 0) continue;
+        const i64 tile_start = tile * SC_TILE;
+        if ((i64)seg[uuid[j]] >= tile_start) continue;
+        St loc;
+        loc.m1 = p1[j].m1;
+        const ThP2 q = p2[j];
+        loc.a1 = q.a1; loc.m2 = q.m2;
+        loc.mall = p4[j].mall;
+        loc.flag = 0;
+        const St f = st_combine(carry[tile], loc);
+        p1[j].m1 = f.m1;
+        ThP2 w; w.a1 = f.a1; w.m2 = f.m2;
+        p2[j] = w;
+        p4[j].mall = f.mall;
+    }
+}
+
+__global__ void __launch_bounds__(256) ex_export_kernel(i64 n, i64 n_uuids, const ThP1 *__restrict__ p1,
+                                                        const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
+                                                        const u32 *__restrict__ uuid, const int *__restrict__ seg,
+                                                        i64 *o_id, i64 *o_uuid, i64 *o_start, i64 *o_end, i64 *o_owner,
+                                                        u8 *o_canc, i64 *o_seg) {
+    const i64 stride = (i64)gridDim.x * blockDim.x;
+    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+        const ThP3 e = p3[j];
+        if (o_id) o_id[j] = th_idc_id(e.idc);
+        if (o_uuid) o_uuid[j] = uuid[j];
+        if (o_start) o_start[j] = p1[j].start;
+        if (o_end) o_end[j] = e.end;
+        if (o_owner) o_owner[j] = p4[j].owner;
+        if (o_canc) o_canc[j] = th_idc_cancelled(e.idc) ? 1 : 0;
+    }
+    if (o_seg)
+        for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u <= n_uuids; u += stride) o_seg[u] = seg[u];
+}
+
+struct DeviceGuard {
+    int prev;
+    bool ok;
+    explicit DeviceGuard(int dev) : prev(0), ok(true) {
+        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
+        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
+                                const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
+                                const uint8_t *cancelled_u8, int mem, void *stream) {
+    TH_REQUIRE(h != nullptr, "th_snapshot_load: handle is NULL");
+    TH_REQUIRE(n >= 0 && n < (1ll << 30), "th_snapshot_load: n=%lld outside [0, 2^30)", (long long)n);
+    TH_REQUIRE(n_uuids >= 0 && n_uuids < (1ll << 31), "th_snapshot_load: n_uuids=%lld outside [0, 2^31)",
+               (long long)n_uuids);
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_snapshot_load: bad mem flag %d", mem);
+    TH_REQUIRE(n == 0 || (id && uuid_id && start_us && end_us && owner && cancelled_u8),
+               "th_snapshot_load: a column pointer is NULL");
+    TH_REQUIRE(n == 0 || n_uuids > 0, "th_snapshot_load: rows given but n_uuids == 0");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_snapshot_load: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+
+    th_snapshot_release_internal(h);
+    h->n_uuids = n_uuids;
+    size_t bytes = 0;
+    TH_CUDA(cudaMalloc((void **)&h->seg, sizeof(int) * (size_t)(n_uuids + 1)));
+    bytes += sizeof(int) * (size_t)(n_uuids + 1);
+    TH_CUDA(cudaMemsetAsync(h->seg, 0, sizeof(int) * (size_t)(n_uuids + 1), st));
+    if (n == 0) {
+        TH_CUDA(cudaStreamSynchronize(st));
+        h->n = 0; h->loaded = 1; h->device_bytes = (i64)bytes; h->radix_passes = 0;
+        return TH_OK;
+    }
+    const size_t zn = (size_t)n;
+    TH_CUDA(cudaMalloc((void **)&h->p1, sizeof(ThP1) * zn));
+    TH_CUDA(cudaMalloc((void **)&h->p2, sizeof(ThP2) * zn));
+    TH_CUDA(cudaMalloc((void **)&h->p3, sizeof(ThP3) * zn));
+    TH_CUDA(cudaMalloc((void **)&h->p4, sizeof(ThP4) * zn));
+    TH_CUDA(cudaMalloc((void **)&h->uuid, sizeof(u32) * zn));
+    bytes += (sizeof(ThP1) * 4 + sizeof(u32)) * zn;
+
+    int rc = TH_OK;
+    {
+        ThScratch sc(st);
+        const void *d_id, *d_uuid, *d_start, *d_end, *d_owner, *d_canc;
+        TH_TRY(sc.in(id, 8 * zn, mem, &d_id));
+        TH_TRY(sc.in(uuid_id, 8 * zn, mem, &d_uuid));
+        TH_TRY(sc.in(start_us, 8 * zn, mem, &d_start));
+        TH_TRY(sc.in(end_us, 8 * zn, mem, &d_end));
+        TH_TRY(sc.in(owner, 8 * zn, mem, &d_owner));
+        TH_TRY(sc.in(cancelled_u8, zn, mem, &d_canc));
+
+        // 1. column statistics decide the digit plan
+        LoadStats *d_stats = nullptr;
+        TH_TRY(sc.alloc((void **)&d_stats, sizeof(LoadStats)));
+        LoadStats init;
+        init.min_start = TH_I64_MAX; init.max_start = TH_I64_MIN; init.min_id = TH_I64_MAX; init.max_id = TH_I64_MIN;
+        init.min_uuid = TH_I64_MAX; init.max_uuid = TH_I64_MIN; init.id_inversions = 0;
+        TH_CUDA(cudaMemcpyAsync(d_stats, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+        const int grid = th_grid_for(n, 256 * 4, 8);
+        ld_stats_kernel<<<grid, 256, 0, st>>>((const i64 *)d_id, (const i64 *)d_uuid, (const i64 *)d_start, n, d_stats);
+        TH_CUDA(cudaGetLastError());
+        LoadStats stats;
+        TH_CUDA(cudaMemcpyAsync(&stats, d_stats, sizeof(stats), cudaMemcpyDeviceToHost, st));
+        TH_CUDA(cudaStreamSynchronize(st));
+        TH_REQUIRE(stats.min_uuid >= 0 && stats.max_uuid < n_uuids,
+                   "th_snapshot_load: uuid_id range [%lld, %lld] outside [0, %lld)", (long long)stats.min_uuid,
+                   (long long)stats.max_uuid, (long long)n_uuids);
+        TH_REQUIRE(stats.min_id >= 0, "th_snapshot_load: negative reservation id %lld", (long long)stats.min_id);
+
+        ThRec *ra = nullptr, *rb = nullptr;
+        TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));
+        TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * zn));
+        int passes_total = 0, passes = 0;
+        const ThRec *order = nullptr;
+        ThRec *sorted = nullptr;
+        ThRec *free_a = ra, *free_b = rb;
+        ThRec *rc_buf = nullptr;
+        if (stats.id_inversions > 0) {
+            // rows are not in ascending-id order: establish it first so that the stable (uuid, start)
+            // sort leaves equal keys in id order (SQLite's scan order for ties).
+            ld_idrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_id, n, stats.min_id, ra);
+            TH_CUDA(cudaGetLastError());
+            TH_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &sorted, &passes, st));
+            passes_total += passes;
+            order = sorted;
+            TH_TRY(sc.alloc((void **)&rc_buf, sizeof(ThRec) * zn));
+            free_a = rc_buf;
+            free_b = (sorted == ra) ? rb : ra;
+        }
+        // 2. (uuid, start) records and the main sort
+        ld_keyrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, order, n, stats.min_start,
+                                               free_a);
+        TH_CUDA(cudaGetLastError());
+        TH_TRY(th_radix_sort(free_a, free_b, n, th_bits_for((u64)(stats.max_start - stats.min_start)),
+                             th_bits_for((u64)stats.max_uuid), &sorted, &passes, st));
+        passes_total += passes;
+
+        // 3. payload gather + segment offsets, 4. running maxima
+        ld_finalize_kernel<<<grid, 256, 0, st>>>(sorted, n, n_uuids, stats.min_start, (const i64 *)d_id,
+                                                 (const i64 *)d_end, (const i64 *)d_owner, (const u8 *)d_canc, h->p1,
+                                                 h->p3, h->p4, h->uuid, h->seg);
+        TH_CUDA(cudaGetLastError());
+        const i64 tiles = (n + SC_TILE - 1) / SC_TILE;
+        St *agg = nullptr;
+        TH_TRY(sc.alloc((void **)&agg, sizeof(St) * (size_t)tiles));
+        sc_local_kernel<<<(unsigned)tiles, SC_THREADS, 0, st>>>(h->uuid, h->p3, n, h->p1, h->p2, h->p4, agg);
+        TH_CUDA(cudaGetLastError());
+        if (tiles > 1) {
+            sc_carry_kernel<<<1, SC_THREADS, 0, st>>>(agg, tiles);
+            sc_fix_kernel<<<grid, SC_THREADS, 0, st>>>(h->uuid, h->seg, n, agg, h->p1, h->p2, h->p4);
+            TH_CUDA(cudaGetLastError());
+        }
+        TH_CUDA(cudaStreamSynchronize(st));
+        h->radix_passes = passes_total;
+    }
+    h->n = n;
+    h->device_bytes = (i64)bytes;
+    h->loaded = 1;
+    return rc;
+}
+
+extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uuid_id, int64_t *start_us,
+                                  int64_t *end_us, int64_t *owner, uint8_t *cancelled_u8, int64_t *seg_offsets,
+                                  int mem, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_snapshot_export: snapshot not loaded");
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_snapshot_export: bad mem flag %d", mem);
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_snapshot_export: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zn = (size_t)h->n, zu = (size_t)h->n_uuids + 1;
+    void *d_id, *d_uuid, *d_start, *d_end, *d_owner, *d_canc, *d_seg;
+    TH_TRY(sc.out(id, 8 * zn, mem, &d_id));
+    TH_TRY(sc.out(uuid_id, 8 * zn, mem, &d_uuid));
+    TH_TRY(sc.out(start_us, 8 * zn, mem, &d_start));
+    TH_TRY(sc.out(end_us, 8 * zn, mem, &d_end));
+    TH_TRY(sc.out(owner, 8 * zn, mem, &d_owner));
+    TH_TRY(sc.out(cancelled_u8, zn, mem, &d_canc));
+    TH_TRY(sc.out(seg_offsets, 8 * zu, mem, &d_seg));
+    const i64 work = h->n > h->n_uuids + 1 ? h->n : h->n_uuids + 1;
+    ex_export_kernel<<<th_grid_for(work, 256 * 4, 8), 256, 0, st>>>(h->n, h->n_uuids, h->p1, h->p3, h->p4, h->uuid,
+                                                                    h->seg, (i64 *)d_id, (i64 *)d_uuid, (i64 *)d_start,
+                                                                    (i64 *)d_end, (i64 *)d_owner, (u8 *)d_canc,
+                                                                    (i64 *)d_seg);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(id, d_id, 8 * zn, mem, st));
+    TH_TRY(th_copy_back(uuid_id, d_uuid, 8 * zn, mem, st));
+    TH_TRY(th_copy_back(start_us, d_start, 8 * zn, mem, st));
+    TH_TRY(th_copy_back(end_us, d_end, 8 * zn, mem, st));
+    TH_TRY(th_copy_back(owner, d_owner, 8 * zn, mem, st));
+    TH_TRY(th_copy_back(cancelled_u8, d_canc, zn, mem, st));
+    TH_TRY(th_copy_back(seg_offsets, d_seg, 8 * zu, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}

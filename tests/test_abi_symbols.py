@@ -1,0 +1,43 @@
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/th_b200.h declares."""
+import ctypes
+import os
+import re
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _declared():
+    text = open(os.path.join(ROOT, 'include', 'th_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(th_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_header_symbols_are_exported(lib_built):
+    lib = ctypes.CDLL(lib_built)
+    names = _declared()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), 'missing export %s' % n
+
+
+def test_binding_covers_header(lib_built):
+    from tensorhive_fixed_b200 import native
+    assert sorted(native.SIGNATURES) == _declared()
+    lib = native.load()
+    assert lib.th_version() == 1
+
+
+def test_library_is_sm100a_only(lib_built):
+    import subprocess
+    out = subprocess.run(['cuobjdump', '-lelf', lib_built], capture_output=True, text=True).stdout
+    archs = set(re.findall(r'sm_(\d+a?)', out))
+    assert archs == {'100a'}, archs
+
+
+def test_argument_errors_do_not_need_a_gpu(lib_built):
+    from tensorhive_fixed_b200 import native
+    lib = native.load()
+    rc = lib.th_snapshot_info(None, None, None, None, None)
+    assert rc == -1
+    assert b'NULL' in lib.th_last_error()
