@@ -1,0 +1,158 @@
+"""Columnar snapshot builder: ORM-ish rows -> int64 columns -> device snapshot.
+
+The reference keeps reservations as SQLAlchemy rows with text datetimes and 40-character resource ids
+(tensorhive/models/Reservation.py:14-37).  The snapshot is what SURVEY.md section 8a row R0 describes:
+``id, uuid_id, start_us, end_us, owner`` as int64 plus a cancelled bit, where
+  * ``uuid_id`` is the dense dictionary code of ``resource_id``,
+  * datetimes become int64 microseconds since the epoch (order-isomorphic to the fixed-width text SQLite
+    compares; the grain of DateUtils.input_date_format, tensorhive/utils/DateUtils.py:9),
+  * ``cancelled`` is ``is_cancelled is not None and is_cancelled`` (Reservation.py:81-83),
+  * ``owner`` is ``user_id``; rows whose user no longer exists (``reservation.user is None``) get -1.
+"""
+from __future__ import annotations
+
+import datetime as _dt
+import threading
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
+
+from .api import Snapshot, MODE_STRICT, MODE_INCLUSIVE, MODE_UPCOMING
+
+EPOCH = _dt.datetime(1970, 1, 1)
+
+
+def dt_to_us(d: _dt.datetime) -> int:
+    delta = d - EPOCH
+    return (delta.days * 86400 + delta.seconds) * 1_000_000 + delta.microseconds
+
+
+def us_to_dt(us: int) -> _dt.datetime:
+    return EPOCH + _dt.timedelta(microseconds=int(us))
+
+
+class UuidDictionary:
+    """resource_id string <-> dense int code.  Unknown strings map to -1 (= "no reservations")."""
+
+    def __init__(self):
+        self.code: Dict[str, int] = {}
+        self.names: List[str] = []
+
+    def add(self, name: str) -> int:
+        c = self.code.get(name)
+        if c is None:
+            c = len(self.names)
+            self.code[name] = c
+            self.names.append(name)
+        return c
+
+    def lookup(self, name: Optional[str]) -> int:
+        if name is None:
+            return -1
+        return self.code.get(name, -1)
+
+    def __len__(self):
+        return len(self.names)
+
+
+class Calendar:
+    """The reservation table as the GPU path sees it.
+
+    ``rows`` are objects (or dicts) exposing ``id, user_id, resource_id, start, end, is_cancelled`` --
+    the attribute names of the reference model -- with ``start``/``end`` as naive-UTC ``datetime`` (or int
+    microseconds).  ``users`` maps ``user_id`` to whatever object the callers want back as
+    ``reservation.user`` (needs ``.username``; ``.email`` for the violation report).
+
+    Thread model: service threads and API greenlets read concurrently while any of
+    them may commit a write.  ``refresh`` builds a NEW device snapshot and swaps it in under a lock; readers
+    keep using the handle they fetched, which stays valid until they drop it.
+    """
+
+    def __init__(self, rows: Iterable = (), users: Optional[Dict[int, object]] = None, device: int = 0,
+                 clock: Callable[[], _dt.datetime] = _dt.datetime.utcnow):
+        self.device = device
+        self.clock = clock
+        self.users = dict(users or {})
+        self._lock = threading.Lock()
+        self.version = 0
+        self._state = None
+        self.refresh(rows)
+
+    # -- building -------------------------------------------------------------------------------------------
+    @staticmethod
+    def _get(row, name):
+        if isinstance(row, dict):
+            return row[name]
+        return getattr(row, name)
+
+    def refresh(self, rows: Iterable, users: Optional[Dict[int, object]] = None) -> None:
+        rows = list(rows)
+        if users is not None:
+            self.users = dict(users)
+        uuids = UuidDictionary()
+        n = len(rows)
+        cid = np.empty(n, np.int64)
+        cuu = np.empty(n, np.int64)
+        cst = np.empty(n, np.int64)
+        cen = np.empty(n, np.int64)
+        cow = np.empty(n, np.int64)
+        cca = np.empty(n, np.uint8)
+        by_id = {}
+        for k, r in enumerate(rows):
+            rid = int(self._get(r, 'id'))
+            cid[k] = rid
+            cuu[k] = uuids.add(self._get(r, 'resource_id'))
+            s, e = self._get(r, 'start'), self._get(r, 'end')
+            cst[k] = dt_to_us(s) if isinstance(s, _dt.datetime) else int(s)
+            cen[k] = dt_to_us(e) if isinstance(e, _dt.datetime) else int(e)
+            uid = self._get(r, 'user_id')
+            cow[k] = int(uid) if (uid is not None and (not self.users or uid in self.users)) else -1
+            raw = self._get(r, 'is_cancelled')
+            cca[k] = 1 if (raw is not None and raw) else 0
+            by_id[rid] = r
+        snap = Snapshot(self.device)
+        snap.load(cid, cuu, cst, cen, cow, cca, n_uuids=max(len(uuids), 1))
+        with self._lock:
+            self._state = (snap, uuids, by_id)
+            self.version += 1
+
+    def state(self):
+        with self._lock:
+            return self._state
+
+    # -- helpers ----------------------------------------------------------------------------------------------
+    def now_us(self) -> int:
+        return dt_to_us(self.clock())
+
+    def usernames(self) -> Dict[str, int]:
+        return {getattr(u, 'username', None): uid for uid, u in self.users.items()}
+
+    def rows_for(self, ids: Sequence[int]) -> List:
+        _snap, _uu, by_id = self.state()
+        return [by_id[int(i)] for i in ids]
+
+    # -- the four predicates, batch form ----------------------------------------------------------------------
+    def would_interfere_batch(self, resource_ids: Sequence[Optional[str]], starts, ends,
+                              self_ids: Sequence[Optional[int]]) -> np.ndarray:
+        snap, uuids, _ = self.state()
+        qu = np.array([uuids.lookup(r) for r in resource_ids], np.int64)
+        qs = np.array([dt_to_us(s) if isinstance(s, _dt.datetime) else int(s) for s in starts], np.int64)
+        qe = np.array([dt_to_us(e) if isinstance(e, _dt.datetime) else int(e) for e in ends], np.int64)
+        qf = np.array([-1 if i is None else int(i) for i in self_ids], np.int64)
+        return snap.conflict_bitmap(qu, qs, qe, qf, MODE_STRICT)
+
+    def sets(self, resource_ids: Sequence[Optional[str]], starts_us, ends_us, mode: int, self_ids=None):
+        snap, uuids, _ = self.state()
+        qu = np.array([uuids.lookup(r) for r in resource_ids], np.int64)
+        qs = np.asarray(starts_us, np.int64)
+        qe = np.asarray(ends_us, np.int64)
+        qf = None if self_ids is None else np.array([-1 if i is None else int(i) for i in self_ids], np.int64)
+        return snap.conflict_sets(qu, qs, qe, qf, mode)
+
+    def all_resource_ids(self) -> List[str]:
+        return list(self.state()[1].names)
+
+    def close(self) -> None:
+        st = self.state()
+        if st:
+            st[0].close()

@@ -1,0 +1,483 @@
+"""The reference's call surface for the hot path, backed by the device snapshot.
+
+Same names, argument meaning, return types and error behaviour as the reference:
+
+  Reservation.would_interfere / current_events / upcoming_events_for_resource /
+  filter_by_uuids_and_time_range              tensorhive/models/Reservation.py:89-148
+  Reservation.check_assertions / save           Reservation.py:42-55, tensorhive/models/CRUDModel.py:21-38
+  avg                                           tensorhive/core/services/UsageLoggingService.py:25-30
+  ProtectionService.do_run / store_violation    tensorhive/core/services/ProtectionService.py:55-120
+  JobSchedulingService.check_current_gpu_slots / interferes_with_reservations
+                                                tensorhive/core/services/JobSchedulingService.py:76-132
+  Scheduler.get_assigned_gpu_uid, GreedyScheduler.schedule_jobs
+                                                tensorhive/core/scheduling.py:19-62
+  ReservationVerifier.update_user_reservations_statuses (the would_interfere half, batched)
+                                                tensorhive/core/utils/ReservationVerifier.py:91-109
+
+The reference reaches its table through a module-global ``db_session``; here the module-global is the
+bound :class:`~.calendar.Calendar` (``bind(calendar)``).  When the reference package is importable the same
+functions can be assigned onto its classes; in this repo they are exercised on plain
+row objects.  All predicate arithmetic happens in libth_b200.so -- this file only converts, orders and
+re-materialises rows by id.
+"""
+from __future__ import annotations
+
+import datetime as _dt
+import logging
+from datetime import timedelta
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import api
+from .api import MODE_STRICT, MODE_INCLUSIVE, MODE_UPCOMING, OWNER_ANY, OWNER_OTHER, OWNER_SAME
+from .calendar import Calendar, dt_to_us, us_to_dt
+
+log = logging.getLogger(__name__)
+
+_calendar: Optional[Calendar] = None
+
+# tensorhive/config.py:259 (the INI section name never matches, so this fallback is what runs)
+SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS = 30
+# tensorhive/core/managers/InfrastructureManager.py:69-78
+IGNORED_PROCESSES = ['Xorg', '/usr/lib/xorg/Xorg', '/usr/bin/X', 'X', 'gnome-shell', '-']
+
+
+def bind(calendar: Calendar) -> None:
+    """Point the module at the live calendar (the analogue of configuring ``db_session``)."""
+    global _calendar
+    _calendar = calendar
+
+
+def _cal() -> Calendar:
+    if _calendar is None:
+        raise RuntimeError('dropin.bind(calendar) has not been called')
+    return _calendar
+
+
+def _period_us(period: timedelta) -> int:
+    return (period.days * 86400 + period.seconds) * 1_000_000 + period.microseconds
+
+
+# =========================================================================================================
+# models/Reservation.py
+# =========================================================================================================
+class Reservation:
+    """Row object with the reference model's attributes and hot-path methods."""
+
+    _min_reservation_time = timedelta(minutes=30)   # Reservation.py:39
+    _max_reservation_time = timedelta(days=8)       # Reservation.py:40
+
+    def __init__(self, user_id=None, title='', description='', resource_id=None, start=None, end=None,
+                 is_cancelled=None, id=None):
+        self.id = id
+        self.user_id = user_id
+        self.title = title
+        self.description = description
+        self.resource_id = resource_id
+        self.start = start
+        self.end = end
+        self._is_cancelled = is_cancelled
+        self.gpu_util_avg = None
+        self.mem_util_avg = None
+
+    # -- plain attributes mirroring the hybrid properties ------------------------------------------------
+    @property
+    def is_cancelled(self):
+        return self._is_cancelled is not None and self._is_cancelled
+
+    @is_cancelled.setter
+    def is_cancelled(self, value):
+        self._is_cancelled = value
+
+    @property
+    def duration(self):
+        return self.end - self.start
+
+    @property
+    def user(self):
+        return _cal().users.get(self.user_id)
+
+    def __repr__(self):
+        return '<Reservation id=%s resource=%s %s..%s cancelled=%s>' % (self.id, self.resource_id, self.start,
+                                                                         self.end, self._is_cancelled)
+
+    # -- Reservation.py:42-55 --------------------------------------------------------------------------------
+    def check_assertions(self):
+        assert self.user_id, 'Reservation owner must be given!'
+        assert self.resource_id, 'Reservation must be related with a resource!'
+        assert self.start, 'Reservation start time is invalid!'
+        assert self.end, 'Reservation end time is invalid!'
+        assert self.duration >= self._min_reservation_time, 'Reservation duration is too short!'
+        assert self.duration <= self._max_reservation_time, 'Reservation duration is too long!'
+        assert 0 < len(self.title) < 60, 'Reservation title length has incorrect length!'
+        assert len(self.description) < 200, 'Reservation description has incorrect length!'
+        assert len(self.resource_id) == 40, 'Protected resource UUID has incorrect length!'
+        collision = self.would_interfere()
+        assert not collision, 'Reservation would interfere with some other reservation!'
+
+    # -- Reservation.py:120-130 ----------------------------------------------------------------------------------
+    def would_interfere(self) -> bool:
+        bits = _cal().would_interfere_batch([self.resource_id], [self.start], [self.end], [self.id])
+        return bool(bits[0])
+
+    @staticmethod
+    def would_interfere_many(reservations: List['Reservation']) -> List[bool]:
+        """Batch form: one kernel launch for any number of candidates."""
+        if not reservations:
+            return []
+        bits = _cal().would_interfere_batch([r.resource_id for r in reservations], [r.start for r in reservations],
+                                            [r.end for r in reservations], [r.id for r in reservations])
+        return [bool(b) for b in bits]
+
+    # -- Reservation.py:89-104 ---------------------------------------------------------------------------------------
+    @classmethod
+    def current_events(cls, resource_id: str = None):
+        cal = _cal()
+        now = cal.now_us()
+        uuids = [resource_id] if resource_id is not None else cal.all_resource_ids()
+        if not uuids:
+            return []
+        k = len(uuids)
+        _off, ids, canc = cal.sets(uuids, [now] * k, [now] * k, MODE_INCLUSIVE)
+        keep = np.asarray(ids)[np.asarray(canc) == 0]
+        if resource_id is None:
+            keep = np.sort(keep)        # one scan over the whole table returns rowid = ascending id order
+        return cal.rows_for(keep)
+
+    # -- Reservation.py:106-118 -------------------------------------------------------------------------------------
+    @classmethod
+    def upcoming_events_for_resource(cls, resource_id: str, period_after: timedelta) -> List['Reservation']:
+        cal = _cal()
+        now = cal.now_us()
+        _off, ids, _canc = cal.sets([resource_id], [now], [now + _period_us(period_after)], MODE_UPCOMING)
+        return cal.rows_for(ids)
+
+    # -- Reservation.py:132-148 ----------------------------------------------------------------------------------------
+    @classmethod
+    def filter_by_uuids_and_time_range(cls, uuids: List[str], start: _dt.datetime, end: _dt.datetime):
+        assertion_failed_msg = 'Argument must be of type datetime.datetime!'
+        assert isinstance(start, _dt.datetime), assertion_failed_msg
+        assert isinstance(end, _dt.datetime), assertion_failed_msg
+        cal = _cal()
+        uu = list(dict.fromkeys(uuids))    # IN (...) is a set test
+        if not uu:
+            return []
+        k = len(uu)
+        _off, ids, _canc = cal.sets(uu, [dt_to_us(start)] * k, [dt_to_us(end)] * k, MODE_INCLUSIVE)
+        return cal.rows_for(np.sort(np.asarray(ids)))
+
+
+# =========================================================================================================
+# core/utils/ReservationVerifier.py:91-109 -- the would_interfere half of the bulk re-validation
+# =========================================================================================================
+def reservations_that_may_be_restored(reservations: List[Reservation], is_allowed) -> List[Reservation]:
+    """For a user whose permissions widened: the cancelled, still-running reservations that
+    ``is_reservation_allowed`` accepts and that would not interfere.  ``is_allowed(reservation)`` is the
+    host-side restriction walk (out of scope); all would_interfere checks go out as ONE batch."""
+    now = _cal().clock()
+    cand = [r for r in reservations if r.end > now and r.is_cancelled and is_allowed(r)]
+    flags = Reservation.would_interfere_many(cand)
+    return [r for r, f in zip(cand, flags) if not f]
+
+
+# =========================================================================================================
+# core/services/UsageLoggingService.py:25-30
+# =========================================================================================================
+def avg(data) -> float:
+    """``sum(data) // len(data)``, ``float(-1)`` when empty -- computed by the K4 kernel (one window)."""
+    data = list(data)
+    if not data:
+        return float(-1)
+    if any(isinstance(x, float) for x in data):
+        # The reference also accepts floats (Union[int, float]); its logs only ever hold ints
+        # (NvidiaSmiParser.py:84-85).  Float lists are outside the int64 device contract.
+        raise TypeError('usage samples are integers in the device path')
+    v = np.asarray(data, np.int64)
+    n = len(v)
+    ts = np.arange(n, dtype=np.int64)
+    _sg, _sm, _c, ag, _am = api.usage_reduce(np.array([0, n], np.int64), ts, v, v, np.array([0], np.int64),
+                                             np.array([0], np.int64), np.array([n], np.int64), device=_cal().device
+                                             if _calendar is not None else 0)
+    return int(ag[0])
+
+
+class UsageLog:
+    """Columnar replacement for the per-reservation JSON logs (UsageLoggingService.py:62-116): samples of
+    all GPUs, grouped by uuid and ts-ascending.  ``averages`` gives what handle_expired_logs (:196-229)
+    writes into gpu_util_avg / mem_util_avg for each expired reservation."""
+
+    def __init__(self, uuid_offsets, ts, gpu, mem, uuid_codes: Dict[str, int]):
+        self.offsets, self.ts, self.gpu, self.mem = uuid_offsets, ts, gpu, mem
+        self.uuid_codes = uuid_codes
+
+    def averages(self, reservations: List[Reservation]):
+        if not reservations:
+            return []
+        wu = np.array([self.uuid_codes.get(r.resource_id, -1) for r in reservations], np.int64)
+        ws = np.array([dt_to_us(r.start) for r in reservations], np.int64)
+        we = np.array([dt_to_us(r.end) for r in reservations], np.int64)
+        _sg, _sm, cnt, ag, am = api.usage_reduce(self.offsets, self.ts, self.gpu, self.mem, wu, ws, we)
+        out = []
+        for j in range(len(reservations)):
+            # avg() returns float(-1) for an empty log, an int otherwise
+            out.append((float(-1), float(-1)) if cnt[j] == 0 else (int(ag[j]), int(am[j])))
+        return out
+
+
+# =========================================================================================================
+# core/managers/InfrastructureManager.py:22-63
+# =========================================================================================================
+def all_nodes_with_gpu_processes(infrastructure: Dict) -> Dict[str, Dict]:
+    out = {}
+    for node in infrastructure:
+        if infrastructure.get(node, {}).get('GPU') is None:
+            out[node] = {}
+            continue
+        node_processes = {}
+        for uuid, gpu_data in infrastructure[node]['GPU'].items():
+            if 'processes' in gpu_data:
+                procs = gpu_data['processes']
+                node_processes[uuid] = ([p for p in procs if p['command'] not in IGNORED_PROCESSES]
+                                        if procs is not None else [])
+        out[node] = node_processes
+    return out
+
+
+# =========================================================================================================
+# core/services/ProtectionService.py
+# =========================================================================================================
+class ProtectionService:
+    """Same constructor and ``do_run`` contract as the reference; the per-GPU ``current_events`` scans and the
+    owner comparison are one K3 + K5 launch over the flattened process table."""
+
+    def __init__(self, handlers, interval=0.0, strict_reservations=False, infrastructure_manager=None,
+                 connection_manager=None):
+        self.interval = interval
+        self.violation_handlers = handlers
+        self.strict_reservations = strict_reservations
+        self.infrastructure_manager = infrastructure_manager
+        self.connection_manager = connection_manager
+
+    def gpu_attr(self, hostname: str, uuid: str, attribute='name') -> str:
+        infrastructure = self.infrastructure_manager.infrastructure if self.infrastructure_manager else {}
+        return infrastructure.get(hostname, {}).get('GPU', {}).get(uuid, {}).get(attribute, '<not available>')
+
+    def collect_violations(self, current_infrastructure: Dict[str, Dict]) -> Dict[str, Dict[str, Dict]]:
+        """{hostname: {intruder: violation_data}} exactly as the nested loops of do_run (:85-102) build it."""
+        cal = _cal()
+        snap, uuids, by_id = cal.state()
+        names = cal.usernames()
+        unknown: Dict[object, int] = {}
+        # flatten in the reference's iteration order
+        where, pu, po = [], [], []
+        for hostname in current_infrastructure:
+            for gpu_id in current_infrastructure[hostname]:
+                processes = current_infrastructure[hostname][gpu_id]
+                if self.strict_reservations or (processes is not None and len(processes)):
+                    code = uuids.lookup(gpu_id)
+                    for process in processes:
+                        owner = process['owner']
+                        if owner in names and owner is not None:
+                            oid = names[owner]
+                        else:
+                            oid = unknown.setdefault(owner, -2 - len(unknown))
+                        where.append((hostname, gpu_id, process))
+                        pu.append(code)
+                        po.append(oid)
+        result = {hostname: {} for hostname in current_infrastructure}
+        if not where:
+            return result
+        flags, res_ids = snap.violation_join(cal.now_us(), self.strict_reservations, np.array(pu, np.int64),
+                                             np.array(po, np.int64))
+        for k, (hostname, gpu_id, process) in enumerate(where):
+            if not flags[k] or hostname is None:
+                continue
+            reservation = by_id[int(res_ids[k])] if res_ids[k] >= 0 else None
+            self.store_violation(result[hostname], process, hostname, reservation, gpu_id)
+        return result
+
+    def store_violation(self, storage, process, hostname, reservation, gpu_id):
+        intruder = process['owner']
+        user = cal_user(reservation) if reservation else None
+        reservation_data = {
+            'OWNER_USERNAME': user.username if reservation else None,
+            'OWNER_EMAIL': getattr(user, 'email', None) if reservation else None,
+            'END': utc2local(_as_dt(reservation.end)) if reservation else None,
+            'GPU_UUID': gpu_id,
+            'GPU_NAME': self.gpu_attr(hostname, gpu_id, attribute='name'),
+            'GPU_ID': self.gpu_attr(hostname, gpu_id, attribute='index'),
+            'HOSTNAME': hostname,
+            'RESERVATION_ID': reservation.id if reservation else None,
+        }
+        if intruder not in storage:
+            storage[intruder] = {
+                'INTRUDER_USERNAME': intruder,
+                'RESERVATIONS': [reservation_data],
+                'VIOLATION_PIDS': {hostname: set([process['pid']])},
+            }
+        else:
+            storage[intruder]['RESERVATIONS'].append(reservation_data)
+            storage[intruder]['VIOLATION_PIDS'][hostname].add(process['pid'])
+
+    def do_run(self):
+        current_infrastructure = self.infrastructure_manager.all_nodes_with_gpu_processes()
+        per_host = self.collect_violations(current_infrastructure)
+        for hostname in current_infrastructure:
+            violations = per_host[hostname]
+            for intruder in violations:
+                violation_data = violations[intruder]
+                reservations = violation_data['RESERVATIONS']
+                hostnames = set([d['HOSTNAME'] for d in reservations])
+                if self.connection_manager is not None:
+                    violation_data['SSH_CONNECTIONS'] = {h: self.connection_manager.single_connection(h)
+                                                         for h in hostnames}
+                violation_data['GPUS'] = ',\n'.join(['{} - GPU{}: {}'.format(d['HOSTNAME'], d['GPU_ID'], d['GPU_NAME'])
+                                                     for d in reservations])
+                violation_data['OWNERS'] = ', '.join(['{} ({})'.format(d['OWNER_USERNAME'], d['OWNER_EMAIL'])
+                                                      for d in reservations])
+                for handler in self.violation_handlers:
+                    try:
+                        handler.trigger_action(violation_data)
+                    except Exception as e:
+                        log.warning('Error in violation handler: {}'.format(e))
+
+
+def cal_user(reservation):
+    return _cal().users.get(reservation.user_id)
+
+
+def _as_dt(x):
+    return x if isinstance(x, _dt.datetime) else us_to_dt(x)
+
+
+def utc2local(utc: _dt.datetime) -> _dt.datetime:
+    # tensorhive/core/utils/time.py:5-9
+    import time
+    epoch = time.mktime(utc.timetuple())
+    offset = _dt.datetime.fromtimestamp(epoch) - _dt.datetime.utcfromtimestamp(epoch)
+    return utc + offset
+
+
+# =========================================================================================================
+# core/scheduling.py + core/services/JobSchedulingService.py
+# =========================================================================================================
+class Scheduler:
+    @staticmethod
+    def get_assigned_gpu_uid(task, hardware_map: Dict[str, Dict]):
+        gpu_ids = list(hardware_map[task.hostname].keys())
+        if task.gpu_id is None or task.gpu_id >= len(gpu_ids):
+            return None
+        return gpu_ids[task.gpu_id]
+
+
+def _owner_id(user) -> int:
+    return -1 if user is None else int(getattr(user, 'id'))
+
+
+class JobSchedulingService:
+    def __init__(self, interval: float = 30.0, stop_attempts_after: float = 5.0):
+        self.interval = interval
+        self.stop_attempts_after = timedelta(minutes=stop_attempts_after)
+        self.considered_future_period = timedelta(minutes=SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS)
+
+    def check_current_gpu_slots(self, hosts_with_gpu_occupation: Dict[str, Dict]) -> Dict[str, Dict]:
+        """JobSchedulingService.py:76-104: minutes until the next reservation per GPU (0 = occupied now,
+        None = nothing upcoming).  One th_upcoming launch for every GPU that is not running a task."""
+        cal = _cal()
+        snap, uuids, _ = cal.state()
+        ret: Dict[str, Dict] = {}
+        ask = []
+        for host in hosts_with_gpu_occupation:
+            ret[host] = {}
+            for gpu_id in hosts_with_gpu_occupation[host]:
+                running = hosts_with_gpu_occupation[host][gpu_id]
+                if running and any('tensorhive_task' in proc.get('command') and proc.get('owner') != 'gdm'
+                                   for proc in running):
+                    ret[host][gpu_id] = 0
+                else:
+                    ret[host][gpu_id] = None
+                    ask.append((host, gpu_id))
+        if not ask:
+            return ret
+        now_dt = cal.clock()
+        now = dt_to_us(now_dt)
+        codes = np.array([uuids.lookup(g) for _h, g in ask], np.int64)
+        _fid, fstart, _fown, count = snap.upcoming(now, _period_us(self.considered_future_period), codes)
+        for k, (host, gpu_id) in enumerate(ask):
+            if count[k] > 0:
+                start = us_to_dt(int(fstart[k]))
+                # the one floating-point operation of the path, done by the reference's own expression (:97-100)
+                ret[host][gpu_id] = (start - now_dt).total_seconds() / 60 if start > now_dt else 0
+        return ret
+
+    @staticmethod
+    def interferes_with_reservations(job, available_hosts_with_gpu_occupation: Dict[str, Dict],
+                                     considered_future_period: timedelta = timedelta(0),
+                                     allow_own: bool = True) -> bool:
+        return JobSchedulingService.interferes_with_reservations_many(
+            [job], available_hosts_with_gpu_occupation, considered_future_period, allow_own)[0]
+
+    @staticmethod
+    def interferes_with_reservations_many(jobs, hosts: Dict[str, Dict],
+                                          considered_future_period: timedelta = timedelta(0),
+                                          allow_own: bool = True) -> List[bool]:
+        """JobSchedulingService.py:117-132 for a whole job list in one launch."""
+        cal = _cal()
+        snap, uuids, _ = cal.state()
+        tu, to, tj = [], [], []
+        for j, job in enumerate(jobs):
+            for task in job.tasks:
+                gpu_id = Scheduler.get_assigned_gpu_uid(task, hosts)
+                tu.append(uuids.lookup(gpu_id))
+                to.append(_owner_id(job.user))
+                tj.append(j)
+        out = [False] * len(jobs)
+        if not tu:
+            return out
+        flags = snap.upcoming_owner_flags(cal.now_us(), _period_us(considered_future_period), np.array(tu, np.int64),
+                                          np.array(to, np.int64), OWNER_OTHER if allow_own else OWNER_ANY)
+        for k, j in enumerate(tj):
+            if flags[k]:
+                out[j] = True
+        return out
+
+
+class GreedyScheduler(Scheduler):
+    def schedule_jobs(self, jobs_to_hardware, hardware_to_slots) -> List:
+        """scheduling.py:29-62.  The per-task "does the job's owner have an upcoming reservation here" test is
+        one batched K5 launch; the taken-hosts pass is sequential by definition and stays on the host."""
+        cal = _cal()
+        snap, uuids, _ = cal.state()
+        jobs = list(jobs_to_hardware)
+        tu, to, index = [], [], {}
+        for j, job in enumerate(jobs):
+            for t, task in enumerate(job.tasks):
+                uid = Scheduler.get_assigned_gpu_uid(task, hardware_to_slots)
+                index[(j, t)] = len(tu)
+                tu.append(uuids.lookup(uid))
+                to.append(_owner_id(job.user))
+        own = np.zeros(0, np.uint8)
+        if tu:
+            own = snap.upcoming_owner_flags(cal.now_us(), SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS * 60 * 1_000_000,
+                                            np.array(tu, np.int64), np.array(to, np.int64), OWNER_SAME)
+        scheduled_jobs, taken_hosts = [], []
+        for j, job in enumerate(jobs):
+            scheduled_tasks = 0
+            for t, task in enumerate(job.tasks):
+                gpu_uid = Scheduler.get_assigned_gpu_uid(task, hardware_to_slots)
+                if (task.hostname, gpu_uid) in taken_hosts:
+                    break
+                if not gpu_uid:
+                    scheduled_tasks += 1
+                    break
+                slot = hardware_to_slots[task.hostname][gpu_uid]
+                if slot is not None and own[index[(j, t)]]:
+                    slot = None
+                if slot is None or slot >= SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS:
+                    scheduled_tasks += 1
+            if scheduled_tasks == len(job.tasks):
+                scheduled_jobs.append(job)
+                taken_hosts.extend([(task.hostname, Scheduler.get_assigned_gpu_uid(task, hardware_to_slots))
+                                    for task in job.tasks])
+        return scheduled_jobs

@@ -95,7 +95,7 @@ cases.append({'name': 'touching/ends at start', 'source': 'Reservation.py:125', 
               'op': 'would_interfere', 'query': {'uuid': GPU, 'start': -60 * M, 'end': 0, 'self_id': None},
               'expect': False})
 cases.append({'name': 'other gpu never interferes', 'source': 'Reservation.py:129', 'pinned': False, 'rows': [base],
-              'op': 'would_interfere', 'query': {'uuid': GPU2, 'start': 5 * M, 'end': 30 * M, 'self_id': None},
+              'op': 'would_interfere', 'query': {'uuid': GPU2, 'start': 5 * M, 'end': 50 * M, 'self_id': None},
               'expect': False})
 
 out = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'reference_kat.json')

@@ -1,0 +1,254 @@
+"""The reference-facing surface (tensorhive_fixed_b200.dropin) against the reference's known answers and
+against the line-by-line service oracle.  These read like the reference's own tests on purpose
+(tests/unit/models/test_reservation_model.py)."""
+import datetime as dt
+from datetime import timedelta
+
+import numpy as np
+import pytest
+
+from helpers import load_kat, kat_rows, EPOCH
+
+pytestmark = pytest.mark.gpu
+
+NOW_US, CASES = load_kat()
+NOW = EPOCH + timedelta(microseconds=NOW_US)
+GPU = 'GPU-d38d4de3-85ee-e837-3d87-e8e2faeb6a63'
+
+
+class User:
+    def __init__(self, uid, username):
+        self.id, self.username, self.email = uid, username, username + '@example.org'
+
+
+@pytest.fixture()
+def dropin(lib_built):
+    from tensorhive_fixed_b200 import dropin
+    return dropin
+
+
+def _calendar(dropin, rows, now_us=NOW_US, users=None):
+    from tensorhive_fixed_b200.calendar import Calendar
+    recs = [dropin.Reservation(id=r[0], resource_id=r[1], start=EPOCH + timedelta(microseconds=r[2]),
+                               end=EPOCH + timedelta(microseconds=r[3]), user_id=r[4], is_cancelled=r[5],
+                               title='TEST TITLE', description='TEST_DESCRIPTION') for r in rows]
+    clock = {'now': EPOCH + timedelta(microseconds=now_us)}
+    cal = Calendar(recs, users=users, clock=lambda: clock['now'])
+    dropin.bind(cal)
+    return cal, clock
+
+
+@pytest.mark.parametrize('case', CASES, ids=[c['name'] for c in CASES])
+def test_reference_known_answers_through_the_dropin(dropin, case):
+    q = case['query']
+    cal, clock = _calendar(dropin, kat_rows(case, NOW_US))
+    sec = lambda s: NOW + timedelta(seconds=s)
+    if case['op'] == 'would_interfere':
+        r = dropin.Reservation(user_id=3, title='TEST TITLE', description='TEST_DESCRIPTION', resource_id=q['uuid'],
+                               start=sec(q['start']), end=sec(q['end']), id=q['self_id'])
+        assert r.would_interfere() is case['expect']
+        if case['expect']:
+            with pytest.raises(AssertionError):
+                r.check_assertions()            # what save() raises in the reference
+        else:
+            r.check_assertions()
+    elif case['op'] == 'current_events':
+        clock['now'] = sec(q['now'])
+        got = [r.id for r in dropin.Reservation.current_events(q['uuid'])]
+        if 'expect' in case:
+            assert got == case['expect']
+        for i in case.get('expect_contains', []):
+            assert i in got
+        for i in case.get('expect_excludes', []):
+            assert i not in got
+    elif case['op'] == 'upcoming':
+        clock['now'] = sec(q['now'])
+        got = [r.id for r in dropin.Reservation.upcoming_events_for_resource(q['uuid'], timedelta(seconds=q['period']))]
+        assert got == case['expect']
+    elif case['op'] == 'range':
+        got = [r.id for r in dropin.Reservation.filter_by_uuids_and_time_range(q['uuids'], sec(q['start']), sec(q['end']))]
+        assert sorted(got) == case['expect']
+    cal.close()
+
+
+def test_invalid_reservation_time_range(dropin):
+    # tests/unit/models/test_reservation_model.py:93-110
+    cal, _ = _calendar(dropin, [])
+    mk = lambda s, e: dropin.Reservation(user_id=1, title='T', description='D', resource_id=GPU, start=s, end=e)
+    with pytest.raises(AssertionError):
+        mk(NOW + timedelta(hours=3), NOW - timedelta(hours=3)).check_assertions()
+    with pytest.raises(AssertionError):
+        mk(NOW, NOW + timedelta(minutes=29, seconds=59)).check_assertions()
+    with pytest.raises(AssertionError):
+        mk(NOW, NOW + timedelta(days=8, seconds=1)).check_assertions()
+    mk(NOW, NOW + timedelta(minutes=30)).check_assertions()
+    with pytest.raises(AssertionError):
+        dropin.Reservation.filter_by_uuids_and_time_range([GPU], '2026-01-01', NOW)
+    cal.close()
+
+
+def test_avg_matches_reference_semantics(dropin):
+    cal, _ = _calendar(dropin, [])
+    assert dropin.avg([1, 2, 4]) == 2 and dropin.avg([100] * 7 + [0]) == 87
+    r = dropin.avg([])
+    assert r == -1 and isinstance(r, float)
+    cal.close()
+
+
+def _world(seed, n=600, u=12, hosts=3):
+    from tensorhive_fixed_b200 import synth
+    from oracle.sql_ref import SqlCalendar
+    from oracle import services_ref as ref
+    rng = np.random.default_rng(seed)
+    cal = synth.make_calendar(n, u, seed=seed)
+    users = {i: User(i, 'user%d' % i) for i in range(1, 1001) if i % 7}     # some owners have no user row
+    rows = [(int(cal['id'][i]), synth.uuid_string(int(cal['uuid_id'][i])), int(cal['start'][i]), int(cal['end'][i]),
+             int(cal['owner'][i]), None if cal['cancelled_raw'][i] < 0 else int(cal['cancelled_raw'][i]))
+            for i in range(n)]
+    now_us = int(np.median(cal['start']))
+    infra = {}
+    for h in range(hosts):
+        gpus = {}
+        for g in range(u // hosts + 1):      # the last GPU of each host is unknown to the calendar
+            code = h * (u // hosts) + g
+            uuid = synth.uuid_string(code if g < u // hosts else 9000 + h)
+            procs = []
+            for _ in range(int(rng.integers(0, 4))):
+                c = rng.random()
+                owner = ('user%d' % rng.integers(1, 1001)) if c < 0.6 else ('ghost%d' % rng.integers(0, 3) if c < 0.8 else None)
+                procs.append({'pid': int(rng.integers(100, 99999)), 'owner': owner,
+                              'command': ['python train.py', 'Xorg', 'tensorhive_task run', '-'][int(rng.integers(0, 4))]})
+            # make some processes belong to the current owner
+            gpus[uuid] = {'name': 'B200', 'index': g, 'processes': procs if rng.random() > 0.1 else None}
+        infra['host%d' % h] = {'GPU': gpus}
+    infra['unreachable'] = {}
+    sql = SqlCalendar(rows)
+    world = ref.World(sql, {k: ref.UserRow(k, v.username, v.email) for k, v in users.items()})
+    # plant owners: for GPUs with a current reservation, make the first process the owner's
+    for h in infra.values():
+        for uuid, data in (h.get('GPU') or {}).items():
+            cur = world.current_events(now_us, uuid)
+            if cur and cur[0].user is not None and data['processes']:
+                data['processes'][0]['owner'] = cur[0].user.username
+    return cal, rows, users, now_us, infra, world
+
+
+class _IM:
+    def __init__(self, infrastructure, dropin):
+        self.infrastructure, self._d = infrastructure, dropin
+
+    def all_nodes_with_gpu_processes(self):
+        return self._d.all_nodes_with_gpu_processes(self.infrastructure)
+
+
+@pytest.mark.parametrize('strict', [False, True])
+@pytest.mark.parametrize('seed', [1, 2, 3])
+def test_protection_service_violations_match_the_reference_loops(dropin, strict, seed):
+    from oracle import services_ref as ref
+    cal, rows, users, now_us, infra, world = _world(seed)
+    c, _clock = _calendar(dropin, rows, now_us=now_us, users=users)
+    want = ref.protection_violations(world, infra, now_us, strict)
+    seen = []
+
+    class Handler:
+        def trigger_action(self, violation_data):
+            seen.append(violation_data)
+
+    svc = dropin.ProtectionService([Handler()], strict_reservations=strict, infrastructure_manager=_IM(infra, dropin))
+    got = svc.collect_violations(svc.infrastructure_manager.all_nodes_with_gpu_processes())
+    assert list(got.keys()) == list(want.keys())
+    total = 0
+    for host in want:
+        assert list(got[host].keys()) == list(want[host].keys()), host      # intruders, in first-seen order
+        for intruder in want[host]:
+            g, w = got[host][intruder], want[host][intruder]
+            assert g['VIOLATION_PIDS'] == w['VIOLATION_PIDS']
+            assert len(g['RESERVATIONS']) == len(w['RESERVATIONS'])
+            for a, b in zip(g['RESERVATIONS'], w['RESERVATIONS']):
+                for key in ('OWNER_USERNAME', 'OWNER_EMAIL', 'GPU_UUID', 'HOSTNAME', 'RESERVATION_ID'):
+                    assert a[key] == b[key], key
+                assert (a['END'] is None) == (b['END'] is None)
+                total += 1
+    assert total > 0
+    svc.do_run()
+    assert len(seen) == sum(len(v) for v in want.values())
+    assert all('GPUS' in v and 'OWNERS' in v for v in seen)
+    c.close()
+
+
+@pytest.mark.parametrize('seed', [4, 5])
+def test_job_scheduling_checks_match_the_reference_loops(dropin, seed):
+    from oracle import services_ref as ref
+    cal, rows, users, now_us, infra, world = _world(seed, n=900, u=12)
+    c, _clock = _calendar(dropin, rows, now_us=now_us, users=users)
+    hosts = dropin.all_nodes_with_gpu_processes(infra)
+    svc = dropin.JobSchedulingService()
+    slots = svc.check_current_gpu_slots(hosts)
+    want_slots = ref.check_current_gpu_slots(world, hosts, now_us)
+    assert slots == want_slots                       # includes the float minutes, same expression
+    kinds = {type(v) for h in slots.values() for v in h.values()}
+    assert type(None) in kinds and (float in kinds or int in kinds)
+
+    rng = np.random.default_rng(seed)
+    host_names = [h for h in hosts if hosts[h]]
+    ulist = list(users.values())
+    jobs, ref_jobs = [], []
+    for j in range(120):
+        user = ulist[int(rng.integers(0, len(ulist)))]
+        tasks = [ref.TaskRow(host_names[int(rng.integers(0, len(host_names)))],
+                             None if rng.random() < 0.05 else int(rng.integers(0, 6))) for _ in range(int(rng.integers(1, 4)))]
+        jobs.append(ref.JobRow(j, user, tasks))
+        ref_jobs.append(ref.JobRow(j, world.users[user.id], tasks))
+    for allow_own in (True, False):
+        for period in (timedelta(0), timedelta(minutes=30), timedelta(days=2)):
+            pus = (period.days * 86400 + period.seconds) * 1_000_000
+            got = [dropin.JobSchedulingService.interferes_with_reservations(j, hosts, period, allow_own) for j in jobs[:25]]
+            got += dropin.JobSchedulingService.interferes_with_reservations_many(jobs[25:], hosts, period, allow_own)
+            want = [ref.interferes_with_reservations(world, j, hosts, now_us, pus, allow_own) for j in ref_jobs]
+            assert got == want
+    got = dropin.GreedyScheduler().schedule_jobs(jobs, slots)
+    want = ref.greedy_schedule(world, ref_jobs, want_slots, now_us)
+    assert [j.id for j in got] == [j.id for j in want]
+    assert 0 < len(want) < len(jobs)
+    c.close()
+
+
+def test_bulk_revalidation_batches_would_interfere(dropin):
+    # ReservationVerifier.update_user_reservations_statuses (ReservationVerifier.py:91-109), widening branch
+    base = [(1, GPU, NOW_US, NOW_US + 3600_000_000, 1, None)]
+    cal, _ = _calendar(dropin, base)
+    mk = lambda i, s, e, c: dropin.Reservation(id=i, user_id=2, title='T', description='D', resource_id=GPU,
+                                               start=NOW + timedelta(minutes=s), end=NOW + timedelta(minutes=e), is_cancelled=c)
+    mine = [mk(10, 30, 90, True),      # overlaps the live row -> stays cancelled
+            mk(11, 60, 120, True),     # touches it -> may be restored
+            mk(12, 200, 260, False),   # not cancelled -> not a candidate
+            mk(13, -500, -400, True)]  # already over -> skipped
+    back = dropin.reservations_that_may_be_restored(mine, is_allowed=lambda r: True)
+    assert [r.id for r in back] == [11]
+    cal.close()
+
+
+def test_usage_log_averages(dropin):
+    from tensorhive_fixed_b200 import synth
+    from oracle import services_ref as ref
+    cal, _ = _calendar(dropin, [])
+    s = synth.make_samples(n_uuids=4, samples_per_uuid=5000, seed=3, cadence_us=60_000_000, jitter_us=2_000_000)
+    codes = {synth.uuid_string(k): k for k in range(4)}
+    log = dropin.UsageLog(s['offsets'], s['ts'], s['gpu'], s['mem'], codes)
+    t0 = EPOCH + timedelta(microseconds=synth.T0_US)
+    res = [dropin.Reservation(id=k, user_id=1, resource_id=synth.uuid_string(k % 4), start=t0 + timedelta(hours=3 * k),
+                              end=t0 + timedelta(hours=3 * k + 2)) for k in range(20)]
+    res.append(dropin.Reservation(id=99, user_id=1, resource_id=synth.uuid_string(1), start=t0 - timedelta(days=3),
+                                  end=t0 - timedelta(days=2)))
+    got = log.averages(res)
+    for r, (ag, am) in zip(res, got):
+        k = codes[r.resource_id]
+        a, b = s['offsets'][k], s['offsets'][k + 1]
+        lo = (r.start - EPOCH) // timedelta(microseconds=1)
+        hi = (r.end - EPOCH) // timedelta(microseconds=1)
+        sel = (s['ts'][a:b] >= lo) & (s['ts'][a:b] <= hi)
+        want_g = ref.avg([int(x) for x in s['gpu'][a:b][sel]])
+        want_m = ref.avg([int(x) for x in s['mem'][a:b][sel]])
+        assert ag == want_g and am == want_m and type(ag) is type(want_g)
+    assert got[-1] == (-1.0, -1.0)
+    cal.close()

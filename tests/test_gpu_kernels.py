@@ -1,0 +1,387 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle -- bit-exact, integer work."""
+import numpy as np
+import pytest
+
+from helpers import csr_to_lists
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def th(lib_built):
+    import tensorhive_fixed_b200 as th
+    return th
+
+
+@pytest.fixture(scope='module')
+def synth():
+    from tensorhive_fixed_b200 import synth
+    return synth
+
+
+@pytest.fixture(scope='module')
+def brute():
+    from oracle import brute
+    return brute
+
+
+def _load(th, cal):
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'],
+              n_uuids=cal['n_uuids'])
+    return snap
+
+
+# ---- K1 --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n', [1, 2, 31, 33, 4095, 4096, 4097, 50_000, 1_000_003])
+def test_sort_pairs_matches_stable_lexsort(th, n):
+    rng = np.random.default_rng(n)
+    hi = rng.integers(0, 300, size=n, dtype=np.int64)
+    lo = rng.integers(-5_000_000_000, 5_000_000_000, size=n, dtype=np.int64)
+    perm = th.sort_pairs(hi, lo)
+    want = np.lexsort((lo, hi))          # lexsort is stable
+    assert np.array_equal(perm, want)
+
+
+@pytest.mark.parametrize('pattern', ['all_equal', 'sorted', 'reversed', 'few_values', 'wide_hi', 'one_bit'])
+def test_sort_pairs_patterns(th, pattern):
+    n = 70_000
+    rng = np.random.default_rng(11)
+    hi = np.zeros(n, np.int64)
+    if pattern == 'all_equal':
+        lo = np.full(n, 42, np.int64)
+    elif pattern == 'sorted':
+        lo = np.arange(n, dtype=np.int64) * 3
+    elif pattern == 'reversed':
+        lo = np.arange(n, dtype=np.int64)[::-1].copy()
+    elif pattern == 'few_values':
+        lo = rng.integers(0, 3, size=n, dtype=np.int64)
+        hi = rng.integers(0, 2, size=n, dtype=np.int64)
+    elif pattern == 'wide_hi':
+        lo = rng.integers(0, 1 << 50, size=n, dtype=np.int64)
+        hi = rng.integers(0, (1 << 32) - 1, size=n, dtype=np.int64)
+    else:
+        lo = (rng.integers(0, 2, size=n, dtype=np.int64)) << 40
+    perm = th.sort_pairs(hi, lo)
+    assert np.array_equal(perm, np.lexsort((lo, hi)))
+
+
+# ---- snapshot load ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n,u,shuffle,skew', [(10_000, 64, True, 0.0), (10_000, 64, False, 0.0),
+                                              (200_000, 500, True, 1.2), (5000, 1, True, 0.0), (7, 3, True, 0.0)])
+def test_snapshot_is_sorted_by_uuid_start_id(th, synth, n, u, shuffle, skew):
+    cal = synth.make_calendar(n, u, seed=n + u, skew=skew, shuffle_ids=shuffle)
+    snap = _load(th, cal)
+    ex = snap.export()
+    order = np.lexsort((cal['id'], cal['start'], cal['uuid_id']))
+    for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled'):
+        assert np.array_equal(ex[k], cal[k][order]), k
+    want_off = np.searchsorted(cal['uuid_id'][order], np.arange(u + 1), side='left')
+    assert np.array_equal(ex['seg_offsets'], want_off)
+    assert snap.info()['n'] == n
+    snap.close()
+
+
+def test_equal_start_rows_keep_id_order(th):
+    n = 5000
+    rng = np.random.default_rng(3)
+    cal = {'id': rng.permutation(np.arange(1, n + 1)).astype(np.int64), 'uuid_id': rng.integers(0, 4, n).astype(np.int64),
+           'start': rng.integers(0, 5, n).astype(np.int64) * 1000, 'owner': np.ones(n, np.int64),
+           'cancelled': np.zeros(n, np.uint8), 'n_uuids': 4}
+    cal['end'] = cal['start'] + 10
+    snap = _load(th, cal)
+    ex = snap.export()
+    order = np.lexsort((cal['id'], cal['start'], cal['uuid_id']))
+    assert np.array_equal(ex['id'], cal['id'][order])
+    snap.close()
+
+
+# ---- K2 bitmap -----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n,u,m,skew', [(10_000, 64, 10_000, 0.0), (100_000, 512, 100_000, 0.0),
+                                        (100_000, 16, 50_000, 1.5), (3000, 1, 3000, 0.0), (50, 64, 1000, 0.0)])
+def test_conflict_bitmap_matches_brute_force(th, synth, brute, n, u, m, skew):
+    cal = synth.make_calendar(n, u, seed=20260101 + n, skew=skew)
+    q = synth.make_queries(cal, m, seed=20260102 + m)
+    snap = _load(th, cal)
+    got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    want = brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, 'first mismatches at %s' % bad[:10]
+    got2 = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], None, th.MODE_INCLUSIVE)
+    want2 = brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'], brute.INCLUSIVE)
+    assert np.array_equal(got2, want2)
+    snap.close()
+
+
+def test_config1_against_the_sql_oracle(th, synth):
+    """BASELINE config 1 (10k reservations, 64 uuids) through the reference's SQL, sampled queries."""
+    from oracle.sql_ref import SqlCalendar
+    cal = synth.make_calendar(10_000, 64, seed=20260101)
+    q = synth.make_queries(cal, 2000, seed=20260102)
+    rows = [(int(cal['id'][i]), synth.uuid_string(int(cal['uuid_id'][i])), int(cal['start'][i]), int(cal['end'][i]),
+             int(cal['owner'][i]), None if cal['cancelled_raw'][i] < 0 else int(cal['cancelled_raw'][i]))
+            for i in range(10_000)]
+    sql = SqlCalendar(rows)
+    snap = _load(th, cal)
+    got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    off, ids, canc = snap.conflict_sets(q['uuid_id'], q['start'], q['end'], q['self_id'], th.MODE_STRICT)
+    lists = csr_to_lists(off, ids)
+    for i in range(2000):
+        sid = None if q['self_id'][i] < 0 else int(q['self_id'][i])
+        r = sql.would_interfere_rows(synth.uuid_string(int(q['uuid_id'][i])), int(q['start'][i]), int(q['end'][i]), sid)
+        assert bool(got[i]) == any(not c for _, c in r), i
+        assert lists[i] == [x[0] for x in r], i
+    snap.close()
+
+
+def test_self_exclusion_uses_second_maximum(th, brute):
+    # two live rows overlap the probe; excluding either one must still report the other
+    cal = {'id': np.array([10, 11, 12], np.int64), 'uuid_id': np.zeros(3, np.int64),
+           'start': np.array([0, 50, 500], np.int64), 'end': np.array([100, 200, 600], np.int64),
+           'owner': np.ones(3, np.int64), 'cancelled': np.zeros(3, np.uint8), 'n_uuids': 1}
+    snap = _load(th, cal)
+    qs = np.array([60, 60, 60, 150, 150, 0], np.int64)
+    qe = np.array([70, 70, 70, 160, 160, 700], np.int64)
+    qf = np.array([-1, 10, 11, 11, 10, 12], np.int64)
+    qu = np.zeros(6, np.int64)
+    got = snap.conflict_bitmap(qu, qs, qe, qf)
+    want = brute.conflict_bits(cal, qu, qs, qe, qf)
+    assert list(got) == list(want) == [True, True, True, False, True, True]
+    snap.close()
+
+
+def test_empty_inputs_and_edge_sizes(th, synth, brute):
+    empty = synth.make_calendar(0, 8, seed=1)
+    snap = _load(th, empty)
+    q = synth.make_queries(empty, 100, seed=2)
+    assert not snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id']).any()
+    off, ids, canc = snap.conflict_sets(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    assert off[-1] == 0 and len(ids) == 0
+    res, own = snap.current_owner(synth.T0_US)
+    assert (res == -1).all() and (own == -1).all()
+    snap.close()
+    cal = synth.make_calendar(1000, 8, seed=3)
+    snap = _load(th, cal)
+    z = np.zeros(0, np.int64)
+    assert snap.conflict_bitmap(z, z, z, z).size == 0
+    off, ids, canc = snap.conflict_sets(z, z, z, z)
+    assert list(off) == [0]
+    # all rows cancelled: nothing ever interferes, but the row lists still carry them
+    cal2 = dict(cal, cancelled=np.ones(1000, np.uint8))
+    snap2 = _load(th, cal2)
+    q = synth.make_queries(cal2, 500, seed=4)
+    assert not snap2.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id']).any()
+    off, ids, canc = snap2.conflict_sets(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    assert csr_to_lists(off, ids) == brute.conflict_sets(cal2, q['uuid_id'], q['start'], q['end'], q['self_id'], brute.STRICT)
+    assert (np.asarray(canc) == 1).all()
+    snap.close(); snap2.close()
+
+
+def test_bad_arguments_are_reported_not_thrown_across_the_abi(th, synth):
+    cal = synth.make_calendar(100, 4, seed=5)
+    snap = th.Snapshot(0)
+    with pytest.raises(th.NativeError) as e:
+        snap.conflict_bitmap(np.zeros(1, np.int64), np.zeros(1, np.int64), np.zeros(1, np.int64), np.zeros(1, np.int64))
+    assert 'not loaded' in str(e.value)
+    bad = dict(cal, uuid_id=cal['uuid_id'] + 100)
+    with pytest.raises(th.NativeError) as e:
+        _load(th, bad)
+    assert e.value.code == -1
+    snap.close()
+
+
+# ---- K2 row lists ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('mode_name', ['STRICT', 'INCLUSIVE', 'UPCOMING'])
+def test_conflict_sets_match_brute_force(th, synth, brute, mode_name):
+    cal = synth.make_calendar(30_000, 40, seed=77, skew=0.8)
+    q = synth.make_queries(cal, 5000, seed=78)
+    mode = getattr(th, 'MODE_' + mode_name)
+    bmode = getattr(brute, mode_name)
+    qs, qe = q['start'].copy(), q['end'].copy()
+    if mode_name != 'STRICT':
+        qe[::3] = qs[::3] + 40 * synth.DAY_US      # long ranges -> long lists (calendar views)
+    qe[::50] = qs[::50] + 2000 * synth.DAY_US      # whole-calendar ranges: lists far longer than a warp
+    snap = _load(th, cal)
+    off, ids, canc = snap.conflict_sets(q['uuid_id'], qs, qe, q['self_id'] if mode_name == 'STRICT' else None, mode)
+    want = brute.conflict_sets(cal, q['uuid_id'], qs, qe, q['self_id'], bmode)
+    got = csr_to_lists(off, ids)
+    assert got == want
+    flag = {int(i): int(c) for i, c in zip(cal['id'], cal['cancelled'])}
+    assert [flag[int(i)] for i in ids] == [int(c) for c in canc]
+    assert max(len(x) for x in want) > 32      # lists longer than a warp are covered
+    snap.close()
+
+
+def test_conflict_sets_capacity_protocol(th, synth):
+    import ctypes as C
+    from tensorhive_fixed_b200 import native
+    cal = synth.make_calendar(2000, 4, seed=9)
+    q = synth.make_queries(cal, 300, seed=10)
+    snap = _load(th, cal)
+    off, ids, canc = snap.conflict_sets(q['uuid_id'], q['start'], q['end'] + 30 * synth.DAY_US, None, th.MODE_INCLUSIVE,
+                                        capacity=1)
+    assert off[-1] == len(ids) > 1
+    lib = native.load()
+    needed = C.c_int64(0)
+    o = np.zeros(301, np.int64)
+    far = np.ascontiguousarray(q['end'] + 30 * synth.DAY_US)
+    rc = lib.th_conflict_sets(snap._h, 300, q['uuid_id'].ctypes.data, q['start'].ctypes.data,
+                              far.ctypes.data, None, 1, o.ctypes.data, None, None, 0,
+                              C.byref(needed), 0, None)
+    assert rc == -5 and needed.value == len(ids) and o[-1] == len(ids)
+    snap.close()
+
+
+# ---- K3 / K5 -----------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n,u,skew', [(20_000, 64, 0.0), (60_000, 8, 1.0), (300, 200, 0.0)])
+def test_current_owner_and_upcoming(th, synth, brute, n, u, skew):
+    cal = synth.make_calendar(n, u, seed=n, skew=skew)
+    snap = _load(th, cal)
+    probes = [int(np.median(cal['start'])), int(cal['start'][3]), int(cal['end'][4]), int(cal['start'].min()) - 5,
+              int(cal['end'].max()) + 5]
+    uu = np.concatenate([np.arange(u), [-1, u, u + 9]]).astype(np.int64)
+    for now in probes:
+        res, own = snap.current_owner(now)
+        wres, wown = brute.current_owner(cal, u, now)
+        assert np.array_equal(res, wres) and np.array_equal(own, wown)
+        for period in (0, 30 * synth.MIN_US, 5 * synth.DAY_US):
+            fid, fst, fow, cnt = snap.upcoming(now, period, uu)
+            wid, wst, wow, wcnt = brute.upcoming_summary(cal, uu, now, period)
+            assert np.array_equal(cnt, wcnt)
+            assert np.array_equal(fid, wid) and np.array_equal(fst, wst) and np.array_equal(fow, wow)
+    snap.close()
+
+
+def test_owner_flags_and_violation_join(th, synth, brute):
+    cal = synth.make_calendar(40_000, 256, seed=41)
+    now = int(np.median(cal['start']))
+    period = 30 * synth.MIN_US
+    snap = _load(th, cal)
+    tasks = synth.make_job_tasks(cal, 3000, seed=42)
+    sets = brute.conflict_sets(cal, tasks['uuid_id'], np.full(len(tasks['uuid_id']), now),
+                               np.full(len(tasks['uuid_id']), now + period), np.full(len(tasks['uuid_id']), -1),
+                               brute.UPCOMING)
+    owner_of = {int(i): int(o) for i, o in zip(cal['id'], cal['owner'])}
+    # make a third of the tasks owned by the reservation's owner so that SAME / OTHER both occur
+    t_owner = tasks['owner'].copy()
+    for k, s in enumerate(sets):
+        if s and k % 3 == 0:
+            t_owner[k] = owner_of[s[0]]
+    for test, fn in ((th.OWNER_ANY, lambda o, s: len(s) > 0),
+                     (th.OWNER_OTHER, lambda o, s: any(owner_of[i] != o for i in s)),
+                     (th.OWNER_SAME, lambda o, s: any(owner_of[i] == o for i in s))):
+        got = snap.upcoming_owner_flags(now, period, tasks['uuid_id'], t_owner, test)
+        want = np.array([fn(int(t_owner[k]), sets[k]) for k in range(len(sets))])
+        assert np.array_equal(got.astype(bool), want), test
+    procs = synth.make_processes(cal, 20_000, now, seed=43)
+    res, own = brute.current_owner(cal, cal['n_uuids'], now)
+    for strict in (False, True):
+        flags, rid = snap.violation_join(now, strict, procs['uuid_id'], procs['owner'])
+        r = res[procs['uuid_id']]
+        o = own[procs['uuid_id']]
+        wflag = np.where(r >= 0, (o >= 0) & (procs['owner'] != o), strict)
+        wrid = np.where((r >= 0) & wflag, r, -1)
+        assert np.array_equal(flags.astype(bool), wflag)
+        assert np.array_equal(rid, wrid)
+        assert 0 < wflag.mean() < 1
+    snap.close()
+
+
+# ---- K4 ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('kw', [dict(n_uuids=16, samples_per_uuid=4000), dict(n_uuids=7, samples_per_uuid=1001, jitter_us=900_000),
+                                dict(n_uuids=40, samples_per_uuid=300, ragged=True, cadence_us=60_000_000, jitter_us=5_000_000),
+                                dict(n_uuids=3, samples_per_uuid=1), dict(n_uuids=2, samples_per_uuid=100_000)])
+def test_usage_reduce_matches_oracle(th, synth, brute, kw):
+    s = synth.make_samples(seed=5, **kw)
+    cad = kw.get('cadence_us', 1_000_000)
+    w = synth.make_windows(s, 3000, seed=6, min_len_us=20 * cad, max_len_us=180 * cad)
+    sg, sm, cnt, ag, am = th.usage_reduce(s['offsets'], s['ts'], s['gpu'], s['mem'], w['uuid_id'], w['start'], w['end'])
+    esg, esm, ecnt = brute.usage_reduce(s['offsets'], s['ts'], s['gpu'], s['mem'], w['uuid_id'], w['start'], w['end'])
+    assert np.array_equal(cnt, ecnt)
+    assert np.array_equal(sg, esg) and np.array_equal(sm, esm)
+    eag = np.array([brute.floor_avg(a, c) for a, c in zip(esg, ecnt)])
+    eam = np.array([brute.floor_avg(a, c) for a, c in zip(esm, ecnt)])
+    # north_star tolerance for usage averages is 1e-6 relative; integer arithmetic gives exact equality
+    assert np.array_equal(ag, eag) and np.array_equal(am, eam)
+    assert (ecnt == 0).any() and (ecnt > 0).any()
+
+
+def test_usage_reduce_touching_windows_share_the_boundary_sample(th):
+    ts = np.arange(10, dtype=np.int64) * 1_000_000
+    gpu = np.arange(10, dtype=np.int64) * 10
+    mem = np.ones(10, np.int64)
+    off = np.array([0, 10], np.int64)
+    wu = np.zeros(3, np.int64)
+    ws = np.array([0, 4_000_000, 9_000_001], np.int64)
+    we = np.array([4_000_000, 9_000_000, 9_500_000], np.int64)
+    sg, sm, cnt, ag, am = th.usage_reduce(off, ts, gpu, mem, wu, ws, we)
+    assert list(cnt) == [5, 6, 0]           # sample at t = 4 s belongs to both
+    assert list(sg) == [100, 390, 0]
+    assert list(ag) == [20, 65, -1] and list(am) == [1, 1, -1]
+
+
+def test_usage_reduce_unaligned_columns_and_negative_values(th, brute):
+    rng = np.random.default_rng(8)
+    n = 5001
+    base_g = rng.integers(-50, 100, size=n + 1, dtype=np.int64)
+    base_m = rng.integers(0, 100, size=n + 1, dtype=np.int64)
+    ts = np.sort(rng.integers(0, 10_000, size=n, dtype=np.int64))
+    off = np.array([0, 2000, 2000, n], np.int64)
+    ts[:2000].sort(); ts[2000:].sort()
+    wu = rng.integers(0, 3, size=400, dtype=np.int64)
+    ws = rng.integers(-100, 10_000, size=400, dtype=np.int64)
+    we = ws + rng.integers(-5, 3000, size=400, dtype=np.int64)
+    import torch
+    dev = torch.device('cuda:0')
+    g = torch.from_numpy(base_g).to(dev)[1:]        # 8-byte aligned but not 16-byte aligned view
+    mm = torch.from_numpy(base_m).to(dev)[1:]
+    outs = th.usage_reduce(torch.from_numpy(off).to(dev), torch.from_numpy(ts).to(dev), g, mm,
+                           torch.from_numpy(wu).to(dev), torch.from_numpy(ws).to(dev), torch.from_numpy(we).to(dev))
+    sg, sm, cnt, ag, am = [o.cpu().numpy() for o in outs]
+    esg, esm, ecnt = brute.usage_reduce(off, ts, base_g[1:], base_m[1:], wu, ws, we)
+    assert np.array_equal(sg, esg) and np.array_equal(sm, esm) and np.array_equal(cnt, ecnt)
+    assert np.array_equal(ag, np.array([brute.floor_avg(a, c) for a, c in zip(esg, ecnt)]))   # floor, not truncation
+
+
+# ---- device-pointer path ----------------------------------------------------------------------------------------------------
+def test_device_pointer_path_equals_host_path(th, synth):
+    import torch
+    dev = torch.device('cuda:0')
+    cal = synth.make_calendar(50_000, 128, seed=91)
+    q = synth.make_queries(cal, 33_333, seed=92)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    snap_h = _load(th, cal)
+    snap_d = th.Snapshot(0)
+    snap_d.load(t(cal['id']), t(cal['uuid_id']), t(cal['start']), t(cal['end']), t(cal['owner']), t(cal['cancelled']),
+                n_uuids=128)
+    a = snap_h.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    words = snap_d.conflict_words(t(q['uuid_id']), t(q['start']), t(q['end']), t(q['self_id']))
+    torch.cuda.synchronize()
+    from tensorhive_fixed_b200.api import unpack_bits
+    b = unpack_bits(words, len(a))
+    assert np.array_equal(a, b)
+    oh = snap_h.conflict_sets(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    od = snap_d.conflict_sets(t(q['uuid_id']), t(q['start']), t(q['end']), t(q['self_id']))
+    for x, y in zip(oh, od):
+        assert np.array_equal(np.asarray(x), y.cpu().numpy())
+    snap_h.close(); snap_d.close()
+
+
+# ---- BASELINE config 2 at full size ---------------------------------------------------------------------------------------------
+def test_config2_full_size_bit_exact(th, synth, brute):
+    """1M reservations x 4096 uuids, 1M candidates: the whole bitmap against the brute-force oracle."""
+    cal = synth.make_calendar(1_000_000, 4096, seed=20260102)
+    q = synth.make_queries(cal, 1_000_000, seed=20260103)
+    snap = _load(th, cal)
+    got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    want = brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])
+    assert np.array_equal(got, want)
+    # size-independent properties: a row always interferes with a copy of itself unless it is the row itself
+    # or cancelled; shrinking a non-conflicting candidate never creates a conflict
+    live = np.nonzero(cal['cancelled'] == 0)[0][:200_000]
+    same = snap.conflict_bitmap(cal['uuid_id'][live], cal['start'][live], cal['end'][live], np.full(live.size, -1, np.int64))
+    assert same.all()
+    free = np.nonzero(~got)[0]
+    shr = snap.conflict_bitmap(q['uuid_id'][free], q['start'][free] + 1, q['end'][free] - 1, q['self_id'][free])
+    assert not shr.any()
+    snap.close()
