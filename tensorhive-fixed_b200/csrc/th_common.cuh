@@ -59,19 +59,42 @@ struct __align__(16) ThP2 { i64 a1;    i64 m2;  };  // a1  = id of the row attai
 struct __align__(16) ThP3 { i64 end;   i64 idc; };  // idc = id | cancelled << 63
 struct __align__(16) ThP4 { i64 owner; i64 mall; }; // mall = max end over ALL rows of the segment prefix
 
+// Row layout of a loaded snapshot: rows sorted by (uuid, start, id); every uuid's segment is PRECEDED by one
+// sentinel row (start = end = m1 = m2 = mall = INT64_MIN, cancelled), so a search prefix is never empty and
+// the hot kernel needs no per-uuid bounds: position seg[u] is the sentinel, real rows are
+// (seg[u], seg[u + 1]).  nt = n + n_uuids positions in total.
+//
+// Time grid: cell (u, b) covers starts in [t0 + (b << shift), t0 + ((b + 1) << shift)) of uuid u (the sentinel
+// counts as bucket 0).  A cell is 16 bytes = ONE probe: the first position of the bucket, how many rows it
+// holds, and the running maximum m1 of everything before it -- so a lower bound that falls into an empty
+// bucket (the common case at ~1 cell per row) is answered without touching the rows at all.
+struct __align__(16) ThCell { int pos; int cnt; i64 m1_before; };
+struct ThGrid {
+    const ThCell *cells;   // [n_uuids * nb]
+    i64 t0;
+    int shift;
+    int nb;
+};
+
 struct th_snapshot {
     int device;
     int loaded;
-    i64 n, n_uuids;
+    i64 n, n_uuids, nt;
     i64 device_bytes;
     i64 radix_passes;
-    int *seg;      // [n_uuids + 1] segment offsets (int32: n < 2^30)
-    ThP1 *p1;      // [n]
-    ThP2 *p2;      // [n]
-    ThP3 *p3;      // [n]
-    ThP4 *p4;      // [n]
-    u32 *uuid;     // [n] uuid of each sorted row (export / rebuild)
+    int *seg;      // [n_uuids + 1] position of each uuid's sentinel (int32: nt < 2^31)
+    ThP1 *p1;      // [nt]
+    ThP2 *p2;      // [nt]
+    ThP3 *p3;      // [nt]
+    ThP4 *p4;      // [nt]
+    u32 *uuid;     // [nt] uuid of each position (export / rebuild)
+    ThCell *grid;  // [n_uuids * nb]
+    i64 grid_t0;
+    int grid_shift, grid_nb;
 };
+static inline ThGrid th_grid_of(const th_snapshot *h) {
+    ThGrid g; g.cells = h->grid; g.t0 = h->grid_t0; g.shift = h->grid_shift; g.nb = h->grid_nb; return g;
+}
 
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ longlong2 th_ld16(const void *p) {

@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(const int *__res
     const i64 wstride = (i64)gridDim.x * LK_WARPS;
     for (i64 u = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); u < n_uuids; u += wstride) {
         i64 id;
-        const int row = lk_current_row(p1, p3, seg[u], seg[u + 1], now, lane, &id);
+        const int row = lk_current_row(p1, p3, seg[u] + 1, seg[u + 1], now, lane, &id);   // seg[u] = sentinel
         if (lane == 0) {
             out_res[u] = row >= 0 ? id : -1;
             out_owner[u] = row >= 0 ? __ldg(&p4[row].owner) : -1;
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(const int *__re
         const i64 u = uuids[q];
         UpAcc a;
         a.count = 0; a.first_row = 0; a.owner_hit = 0;
-        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(p1, p3, p4, seg[u], seg[u + 1], now, later, lane, 0, 0);
+        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(p1, p3, p4, seg[u] + 1, seg[u + 1], now, later, lane, 0, 0);
         if (lane == 0) {
             if (a.count > 0) {
                 const int r = a.first_row;
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(const int *_
         const i64 u = task_uuid[q];
         int flag = 0;
         if (u >= 0 && u < n_uuids) {
-            const UpAcc a = lk_upcoming<true>(p1, p3, p4, seg[u], seg[u + 1], now, later, lane, test, task_owner[q]);
+            const UpAcc a = lk_upcoming<true>(p1, p3, p4, seg[u] + 1, seg[u + 1], now, later, lane, test, task_owner[q]);
             flag = a.owner_hit;
         }
         if (lane == 0) out_flag[q] = (u8)flag;

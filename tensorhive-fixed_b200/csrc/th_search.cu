@@ -42,7 +42,12 @@ __device__ __forceinline__ int th_prefix_end(const ThP1 *__restrict__ p1, int lo
 
 constexpr int BM_THREADS = 256;
 
-__global__ void __launch_bounds__(BM_THREADS) k2_bitmap_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+// One lane per query.  Memory instructions whose 32 lanes touch 32 different cache lines cost 32 L1
+// wavefronts each, and that -- not bytes -- is what bounds this kernel, so the lookup is built to need as
+// few divergent probes as possible: ONE 16-byte grid cell {pos, cnt, m1_before}; only if the candidate's
+// bucket holds rows, a search over those (usually 1-2) 16-byte {start, m1} entries; only for self-updates a
+// third probe for {a1, m2}.  The four query columns are read coalesced.
+__global__ void __launch_bounds__(BM_THREADS) k2_bitmap_kernel(ThGrid g, const ThP1 *__restrict__ p1,
                                                                const ThP2 *__restrict__ p2, const ThP4 *__restrict__ p4,
                                                                i64 n_uuids, i64 m, const i64 *__restrict__ q_uuid,
                                                                const i64 *__restrict__ q_start,
@@ -53,33 +58,37 @@ __global__ void __launch_bounds__(BM_THREADS) k2_bitmap_kernel(const int *__rest
     bool hit = false;
     if (i < m) {
         const i64 u = q_uuid[i];
+        const i64 qs = q_start[i], qe = q_end[i];
+        const i64 self = (mode == TH_MODE_STRICT) ? q_self[i] : -1;
         if (u >= 0 && u < n_uuids) {
-            int lo = seg[u];
-            int hi = seg[u + 1];
-            const int seg_lo = lo;
-            const i64 qs = q_start[i], qe = q_end[i];
+            i64 b = 0;
+            if (qe > g.t0) {
+                const u64 d = ((u64)qe - (u64)g.t0) >> g.shift;
+                b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
+            }
+            const longlong2 c = th_ld16(&g.cells[u * g.nb + b]);   // {pos | cnt << 32, m1_before}
+            int lo = (int)(c.x & 0xffffffffll);
+            int hi = lo + (int)(c.x >> 32);
             if (mode == TH_MODE_STRICT) {
-                i64 m1 = TH_I64_MIN;
+                i64 m1 = c.y;
                 while (lo < hi) {
                     const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
                     const longlong2 e = th_ld16(&p1[mid]);   // {start, m1}
                     if (e.x < qe) { lo = mid + 1; m1 = e.y; } else hi = mid;
                 }
-                if (lo > seg_lo) {
-                    const i64 self = q_self[i];
-                    if (self >= 0) {
-                        const longlong2 t = th_ld16(&p2[lo - 1]);   // {a1, m2}
-                        hit = (t.x == self) ? (t.y > qs) : (m1 > qs);
-                    } else {
-                        hit = m1 > qs;
-                    }
+                // lo - 1 is the last row with start < qe; it is at worst the uuid's sentinel
+                if (self >= 0) {
+                    const longlong2 t = th_ld16(&p2[lo - 1]);   // {a1, m2}
+                    hit = (t.x == self) ? (t.y > qs) : (m1 > qs);
+                } else {
+                    hit = m1 > qs;
                 }
             } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
                 while (lo < hi) {
                     const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
                     if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
                 }
-                if (lo > seg_lo) hit = __ldg(&p4[lo - 1].mall) >= qs;
+                hit = __ldg(&p4[lo - 1].mall) >= qs;
             }
         }
     }
@@ -123,7 +132,7 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
         const i64 u = q_uuid[q];
         int cnt = 0, beg = 0, pend = 0;
         if (u >= 0 && u < n_uuids) {
-            const int lo = v.seg[u], hi = v.seg[u + 1];
+            const int lo = v.seg[u] + 1, hi = v.seg[u + 1];   // position seg[u] is the sentinel
             const i64 qs = q_start[q], qe = q_end[q];
             const i64 self = q_self ? q_self[q] : -1;
             pend = (mode == TH_MODE_STRICT) ? th_prefix_end<true>(v.p1, lo, hi, qe)
@@ -306,7 +315,7 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     if (q_self_id) TH_TRY(sc.in(q_self_id, 8 * zm, mem, &d_f));
     TH_TRY(sc.out(out_bits_u32, 4 * words, mem, &d_bits));
     const unsigned blocks = (unsigned)((m + BM_THREADS - 1) / BM_THREADS);
-    k2_bitmap_kernel<<<blocks, BM_THREADS, 0, st>>>(h->seg, h->p1, h->p2, h->p4, h->n_uuids, m, (const i64 *)d_u,
+    k2_bitmap_kernel<<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m, (const i64 *)d_u,
                                                     (const i64 *)d_s, (const i64 *)d_e, (const i64 *)d_f, mode,
                                                     (u32 *)d_bits);
     TH_CUDA(cudaGetLastError());

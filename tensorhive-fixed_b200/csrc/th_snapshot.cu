@@ -10,6 +10,7 @@
 //   - the list-returning predicates walk backwards from the prefix end only while the running maximum
 //     over ALL rows (mall) says a match can still exist.
 #include "th_common.cuh"
+#include <stdlib.h>
 
 void th_snapshot_release_internal(th_snapshot *h);
 
@@ -71,7 +72,8 @@ __global__ void __launch_bounds__(256) ld_keyrec_kernel(const i64 *__restrict__ 
     }
 }
 
-// gather the payload columns into snapshot order and derive the segment offsets
+// gather the payload columns into snapshot order (row j of uuid u lands at position j + u + 1: one sentinel
+// per uuid precedes its rows) and derive the sentinel positions seg[u] = (#rows with uuid < u) + u
 __global__ void __launch_bounds__(256) ld_finalize_kernel(const ThRec *__restrict__ rec, i64 n, i64 n_uuids,
                                                           i64 min_start, const i64 *__restrict__ id,
                                                           const i64 *__restrict__ end, const i64 *__restrict__ owner,
@@ -80,18 +82,68 @@ __global__ void __launch_bounds__(256) ld_finalize_kernel(const ThRec *__restric
     for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (i64)gridDim.x * blockDim.x) {
         const ThRec r = rec[j];
         const u32 i = r.idx;
-        p1[j].start = (i64)r.k0 + min_start;
+        const i64 cur = r.k1;
+        const i64 pos = j + cur + 1;
+        p1[pos].start = (i64)r.k0 + min_start;
         ThP3 e;
         e.end = end[i];
         e.idc = id[i] | (canc[i] ? TH_I64_MIN : 0);
-        p3[j] = e;
-        p4[j].owner = owner[i];
-        uuid_out[j] = r.k1;
-        const i64 cur = r.k1;
+        p3[pos] = e;
+        p4[pos].owner = owner[i];
+        uuid_out[pos] = r.k1;
         const i64 prev = j > 0 ? (i64)rec[j - 1].k1 : -1;
-        for (i64 u = prev + 1; u <= cur; ++u) seg[u] = (int)j;
+        for (i64 u = prev + 1; u <= cur; ++u) seg[u] = (int)(j + u);
         if (j == n - 1)
-            for (i64 u = cur + 1; u <= n_uuids; ++u) seg[u] = (int)n;
+            for (i64 u = cur + 1; u <= n_uuids; ++u) seg[u] = (int)(n + u);
+    }
+}
+
+// empty table: only sentinels
+__global__ void __launch_bounds__(256) ld_seg_empty_kernel(i64 n_uuids, int *seg) {
+    for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u <= n_uuids; u += (i64)gridDim.x * blockDim.x)
+        seg[u] = (int)u;
+}
+
+__global__ void __launch_bounds__(256) ld_sentinel_kernel(i64 n_uuids, const int *__restrict__ seg, ThP1 *p1, ThP2 *p2,
+                                                          ThP3 *p3, ThP4 *p4, u32 *uuid_out) {
+    for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u < n_uuids; u += (i64)gridDim.x * blockDim.x) {
+        const int pos = seg[u];
+        ThP1 a; a.start = TH_I64_MIN; a.m1 = TH_I64_MIN;
+        ThP2 b; b.a1 = -1; b.m2 = TH_I64_MIN;
+        ThP3 c; c.end = TH_I64_MIN; c.idc = -1;          // cancelled, id = 2^63 - 1: never a real row
+        ThP4 d; d.owner = -1; d.mall = TH_I64_MIN;
+        p1[pos] = a; p2[pos] = b; p3[pos] = c; p4[pos] = d;
+        uuid_out[pos] = (u32)u;
+    }
+}
+
+// time grid: cells[c] = first position whose (uuid, bucket) cell is >= c.  The sentinel sits in bucket 0 of its
+// uuid, so cells[u * nb] = seg[u] and the last bucket of uuid u ends at seg[u + 1].
+__device__ __forceinline__ i64 ld_cell_of(const ThP1 *__restrict__ p1, const u32 *__restrict__ uuid, i64 pos, i64 t0,
+                                          int shift, int nb) {
+    const i64 s = p1[pos].start;
+    const i64 b = s == TH_I64_MIN ? 0 : (i64)(((u64)s - (u64)t0) >> shift);
+    return (i64)uuid[pos] * nb + b;
+}
+__global__ void __launch_bounds__(256) ld_grid_kernel(const ThP1 *__restrict__ p1, const u32 *__restrict__ uuid, i64 nt,
+                                                      i64 n_cells, i64 t0, int shift, int nb, int *first) {
+    for (i64 pos = (i64)blockIdx.x * blockDim.x + threadIdx.x; pos < nt; pos += (i64)gridDim.x * blockDim.x) {
+        const i64 cur = ld_cell_of(p1, uuid, pos, t0, shift, nb);
+        const i64 prev = pos > 0 ? ld_cell_of(p1, uuid, pos - 1, t0, shift, nb) : -1;
+        for (i64 c = prev + 1; c <= cur; ++c) first[c] = (int)pos;
+        if (pos == nt - 1)
+            for (i64 c = cur + 1; c <= n_cells; ++c) first[c] = (int)nt;
+    }
+}
+// first[] -> 16-byte cells {pos, cnt, m1 of the row before the bucket (same uuid) or INT64_MIN}
+__global__ void __launch_bounds__(256) ld_cells_kernel(const int *__restrict__ first, const ThP1 *__restrict__ p1,
+                                                       i64 n_cells, int nb, ThCell *cells) {
+    for (i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x; c < n_cells; c += (i64)gridDim.x * blockDim.x) {
+        ThCell x;
+        x.pos = first[c];
+        x.cnt = first[c + 1] - x.pos;
+        x.m1_before = (c % nb == 0) ? TH_I64_MIN : p1[x.pos - 1].m1;   // bucket 0 starts at the sentinel
+        cells[c] = x;
     }
 }
 
@@ -238,23 +290,26 @@ __global__ void __launch_bounds__(SC_THREADS) sc_fix_kernel(const u32 *__restric
     }
 }
 
-__global__ void __launch_bounds__(256) ex_export_kernel(i64 n, i64 n_uuids, const ThP1 *__restrict__ p1,
+__global__ void __launch_bounds__(256) ex_export_kernel(i64 nt, i64 n_uuids, const ThP1 *__restrict__ p1,
                                                         const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
                                                         const u32 *__restrict__ uuid, const int *__restrict__ seg,
                                                         i64 *o_id, i64 *o_uuid, i64 *o_start, i64 *o_end, i64 *o_owner,
                                                         u8 *o_canc, i64 *o_seg) {
     const i64 stride = (i64)gridDim.x * blockDim.x;
-    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
-        const ThP3 e = p3[j];
+    for (i64 pos = (i64)blockIdx.x * blockDim.x + threadIdx.x; pos < nt; pos += stride) {
+        const i64 u = uuid[pos];
+        if (pos == seg[u]) continue;                   // sentinel
+        const i64 j = pos - (u + 1);
+        const ThP3 e = p3[pos];
         if (o_id) o_id[j] = th_idc_id(e.idc);
-        if (o_uuid) o_uuid[j] = uuid[j];
-        if (o_start) o_start[j] = p1[j].start;
+        if (o_uuid) o_uuid[j] = u;
+        if (o_start) o_start[j] = p1[pos].start;
         if (o_end) o_end[j] = e.end;
-        if (o_owner) o_owner[j] = p4[j].owner;
+        if (o_owner) o_owner[j] = p4[pos].owner;
         if (o_canc) o_canc[j] = th_idc_cancelled(e.idc) ? 1 : 0;
     }
-    if (o_seg)
-        for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u <= n_uuids; u += stride) o_seg[u] = seg[u];
+    if (o_seg)   // offsets in the caller's (sentinel-free) row numbering
+        for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u <= n_uuids; u += stride) o_seg[u] = seg[u] - u;
 }
 
 struct DeviceGuard {
@@ -274,7 +329,7 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
                                 const uint8_t *cancelled_u8, int mem, void *stream) {
     TH_REQUIRE(h != nullptr, "th_snapshot_load: handle is NULL");
     TH_REQUIRE(n >= 0 && n < (1ll << 30), "th_snapshot_load: n=%lld outside [0, 2^30)", (long long)n);
-    TH_REQUIRE(n_uuids >= 0 && n_uuids < (1ll << 31), "th_snapshot_load: n_uuids=%lld outside [0, 2^31)",
+    TH_REQUIRE(n_uuids >= 0 && n_uuids < (1ll << 30), "th_snapshot_load: n_uuids=%lld outside [0, 2^30)",
                (long long)n_uuids);
     TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_snapshot_load: bad mem flag %d", mem);
     TH_REQUIRE(n == 0 || (id && uuid_id && start_us && end_us && owner && cancelled_u8),
@@ -286,26 +341,25 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
 
     th_snapshot_release_internal(h);
     h->n_uuids = n_uuids;
+    const i64 nt = n + n_uuids;
+    const size_t zn = (size_t)n, znt = (size_t)(nt > 0 ? nt : 1);
     size_t bytes = 0;
     TH_CUDA(cudaMalloc((void **)&h->seg, sizeof(int) * (size_t)(n_uuids + 1)));
-    bytes += sizeof(int) * (size_t)(n_uuids + 1);
-    TH_CUDA(cudaMemsetAsync(h->seg, 0, sizeof(int) * (size_t)(n_uuids + 1), st));
-    if (n == 0) {
-        TH_CUDA(cudaStreamSynchronize(st));
-        h->n = 0; h->loaded = 1; h->device_bytes = (i64)bytes; h->radix_passes = 0;
-        return TH_OK;
-    }
-    const size_t zn = (size_t)n;
-    TH_CUDA(cudaMalloc((void **)&h->p1, sizeof(ThP1) * zn));
-    TH_CUDA(cudaMalloc((void **)&h->p2, sizeof(ThP2) * zn));
-    TH_CUDA(cudaMalloc((void **)&h->p3, sizeof(ThP3) * zn));
-    TH_CUDA(cudaMalloc((void **)&h->p4, sizeof(ThP4) * zn));
-    TH_CUDA(cudaMalloc((void **)&h->uuid, sizeof(u32) * zn));
-    bytes += (sizeof(ThP1) * 4 + sizeof(u32)) * zn;
+    TH_CUDA(cudaMalloc((void **)&h->p1, sizeof(ThP1) * znt));
+    TH_CUDA(cudaMalloc((void **)&h->p2, sizeof(ThP2) * znt));
+    TH_CUDA(cudaMalloc((void **)&h->p3, sizeof(ThP3) * znt));
+    TH_CUDA(cudaMalloc((void **)&h->p4, sizeof(ThP4) * znt));
+    TH_CUDA(cudaMalloc((void **)&h->uuid, sizeof(u32) * znt));
+    bytes += sizeof(int) * (size_t)(n_uuids + 1) + (sizeof(ThP1) * 4 + sizeof(u32)) * znt;
 
-    int rc = TH_OK;
-    {
-        ThScratch sc(st);
+    ThScratch sc(st);
+    int passes_total = 0;
+    i64 min_start = 0, max_start = 0;
+    const int ugrid = th_grid_for(n_uuids + 1, 256, 8);
+    if (n == 0) {
+        ld_seg_empty_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg);
+        TH_CUDA(cudaGetLastError());
+    } else {
         const void *d_id, *d_uuid, *d_start, *d_end, *d_owner, *d_canc;
         TH_TRY(sc.in(id, 8 * zn, mem, &d_id));
         TH_TRY(sc.in(uuid_id, 8 * zn, mem, &d_uuid));
@@ -331,15 +385,17 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
                    "th_snapshot_load: uuid_id range [%lld, %lld] outside [0, %lld)", (long long)stats.min_uuid,
                    (long long)stats.max_uuid, (long long)n_uuids);
         TH_REQUIRE(stats.min_id >= 0, "th_snapshot_load: negative reservation id %lld", (long long)stats.min_id);
+        TH_REQUIRE(stats.min_start > TH_I64_MIN, "th_snapshot_load: start_us == INT64_MIN is reserved");
+        min_start = stats.min_start;
+        max_start = stats.max_start;
 
         ThRec *ra = nullptr, *rb = nullptr;
         TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));
         TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * zn));
-        int passes_total = 0, passes = 0;
+        int passes = 0;
         const ThRec *order = nullptr;
         ThRec *sorted = nullptr;
-        ThRec *free_a = ra, *free_b = rb;
-        ThRec *rc_buf = nullptr;
+        ThRec *key_a = ra, *key_b = rb;
         if (stats.id_inversions > 0) {
             // rows are not in ascending-id order: establish it first so that the stable (uuid, start)
             // sort leaves equal keys in id order (SQLite's scan order for ties).
@@ -348,40 +404,68 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
             TH_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &sorted, &passes, st));
             passes_total += passes;
             order = sorted;
+            ThRec *rc_buf = nullptr;
             TH_TRY(sc.alloc((void **)&rc_buf, sizeof(ThRec) * zn));
-            free_a = rc_buf;
-            free_b = (sorted == ra) ? rb : ra;
+            key_a = rc_buf;
+            key_b = (sorted == ra) ? rb : ra;
         }
         // 2. (uuid, start) records and the main sort
         ld_keyrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, order, n, stats.min_start,
-                                               free_a);
+                                               key_a);
         TH_CUDA(cudaGetLastError());
-        TH_TRY(th_radix_sort(free_a, free_b, n, th_bits_for((u64)(stats.max_start - stats.min_start)),
+        TH_TRY(th_radix_sort(key_a, key_b, n, th_bits_for((u64)(stats.max_start - stats.min_start)),
                              th_bits_for((u64)stats.max_uuid), &sorted, &passes, st));
         passes_total += passes;
-
-        // 3. payload gather + segment offsets, 4. running maxima
+        // 3. payload gather + sentinel positions
         ld_finalize_kernel<<<grid, 256, 0, st>>>(sorted, n, n_uuids, stats.min_start, (const i64 *)d_id,
                                                  (const i64 *)d_end, (const i64 *)d_owner, (const u8 *)d_canc, h->p1,
                                                  h->p3, h->p4, h->uuid, h->seg);
         TH_CUDA(cudaGetLastError());
-        const i64 tiles = (n + SC_TILE - 1) / SC_TILE;
+    }
+    if (nt > 0) {
+        ld_sentinel_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, h->p2, h->p3, h->p4, h->uuid);
+        TH_CUDA(cudaGetLastError());
+        // 4. running maxima over every segment (sentinel = head of its segment)
+        const int grid_nt = th_grid_for(nt, 256 * 4, 8);
+        const i64 tiles = (nt + SC_TILE - 1) / SC_TILE;
         St *agg = nullptr;
         TH_TRY(sc.alloc((void **)&agg, sizeof(St) * (size_t)tiles));
-        sc_local_kernel<<<(unsigned)tiles, SC_THREADS, 0, st>>>(h->uuid, h->p3, n, h->p1, h->p2, h->p4, agg);
+        sc_local_kernel<<<(unsigned)tiles, SC_THREADS, 0, st>>>(h->uuid, h->p3, nt, h->p1, h->p2, h->p4, agg);
         TH_CUDA(cudaGetLastError());
         if (tiles > 1) {
             sc_carry_kernel<<<1, SC_THREADS, 0, st>>>(agg, tiles);
-            sc_fix_kernel<<<grid, SC_THREADS, 0, st>>>(h->uuid, h->seg, n, agg, h->p1, h->p2, h->p4);
+            sc_fix_kernel<<<grid_nt, SC_THREADS, 0, st>>>(h->uuid, h->seg, nt, agg, h->p1, h->p2, h->p4);
             TH_CUDA(cudaGetLastError());
         }
-        TH_CUDA(cudaStreamSynchronize(st));
-        h->radix_passes = passes_total;
+        // 5. time grid: power-of-two bucket width chosen for ~1-2 cells per row (TH_GRID_CELLS_PER_ROW_X4 / 4)
+        const u64 span = (u64)max_start - (u64)min_start;
+        i64 x4 = 6;
+        if (const char *env = getenv("TH_GRID_CELLS_PER_ROW_X4")) { x4 = atoll(env); if (x4 < 1) x4 = 1; if (x4 > 64) x4 = 64; }
+        i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
+        if (target < 1) target = 1;
+        int shift = 0;
+        while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
+        const i64 nb = (i64)(span >> shift) + 1;
+        const i64 n_cells = n_uuids * nb;
+        TH_REQUIRE(n_cells < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)", (long long)n_cells);
+        int *first = nullptr;
+        TH_TRY(sc.alloc((void **)&first, sizeof(int) * (size_t)(n_cells + 1)));
+        TH_CUDA(cudaMalloc((void **)&h->grid, sizeof(ThCell) * (size_t)(n_cells > 0 ? n_cells : 1)));
+        bytes += sizeof(ThCell) * (size_t)n_cells;
+        h->grid_t0 = min_start; h->grid_shift = shift; h->grid_nb = (int)nb;
+        ld_grid_kernel<<<grid_nt, 256, 0, st>>>(h->p1, h->uuid, nt, n_cells, min_start, shift, (int)nb, first);
+        ld_cells_kernel<<<th_grid_for(n_cells, 256 * 4, 8), 256, 0, st>>>(first, h->p1, n_cells, (int)nb, h->grid);
+        TH_CUDA(cudaGetLastError());
+    } else {
+        h->grid_t0 = 0; h->grid_shift = 0; h->grid_nb = 1;
     }
+    TH_CUDA(cudaStreamSynchronize(st));
+    h->radix_passes = passes_total;
     h->n = n;
+    h->nt = nt;
     h->device_bytes = (i64)bytes;
     h->loaded = 1;
-    return rc;
+    return TH_OK;
 }
 
 extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uuid_id, int64_t *start_us,
@@ -402,8 +486,8 @@ extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uu
     TH_TRY(sc.out(owner, 8 * zn, mem, &d_owner));
     TH_TRY(sc.out(cancelled_u8, zn, mem, &d_canc));
     TH_TRY(sc.out(seg_offsets, 8 * zu, mem, &d_seg));
-    const i64 work = h->n > h->n_uuids + 1 ? h->n : h->n_uuids + 1;
-    ex_export_kernel<<<th_grid_for(work, 256 * 4, 8), 256, 0, st>>>(h->n, h->n_uuids, h->p1, h->p3, h->p4, h->uuid,
+    const i64 work = h->nt > h->n_uuids + 1 ? h->nt : h->n_uuids + 1;
+    ex_export_kernel<<<th_grid_for(work, 256 * 4, 8), 256, 0, st>>>(h->nt, h->n_uuids, h->p1, h->p3, h->p4, h->uuid,
                                                                     h->seg, (i64 *)d_id, (i64 *)d_uuid, (i64 *)d_start,
                                                                     (i64 *)d_end, (i64 *)d_owner, (u8 *)d_canc,
                                                                     (i64 *)d_seg);

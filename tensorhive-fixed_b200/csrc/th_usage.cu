@@ -6,26 +6,31 @@
 // it was logged while the reservation was in current_events(): start <= ts <= end, both inclusive
 // (tensorhive/models/Reservation.py:96-97), so touching windows share their boundary sample.
 //
-// One warp per window.  Samples of a uuid are ts-sorted, so the window is a contiguous index range
-// [a, b): each end is located by an interpolation guess followed by ONE coalesced 32-wide probe (exact
-// for regular logging cadence, which is what the service produces), with a warp-uniform binary search
-// only when the guess misses.  The range is then summed with 16-byte loads of gpu_util / mem_util.  The ts
-// column is only probed, never streamed.
+// Eight lanes per window, four windows per warp: the range search is the same instruction stream for every
+// lane of a group, so sharing a warp between four windows cuts the issue slots per window by 4 (the first
+// version, one warp per window, was instruction-issue bound at 70 % SM throughput, 36 % DRAM).  Samples of a
+// uuid are ts-sorted, so the window is a contiguous index range [a, b): both ends are located by an
+// interpolation guess followed by ONE coalesced 16-wide probe per end (exact for a regular logging cadence,
+// which is what the service produces; both probes are independent and issued back to back), with a
+// group-uniform binary search only when a guess misses.  The range is then summed with 16-byte loads of
+// gpu_util / mem_util.  The ts column is only probed, never streamed.
 #include "th_common.cuh"
 
 namespace {
 
 constexpr int US_THREADS = 256;
-constexpr int US_WARPS = US_THREADS / 32;
+constexpr int US_GROUP = 8;                              // lanes per window
+constexpr int US_GROUPS_PER_BLOCK = US_THREADS / US_GROUP;
 
 template <bool GE>
 __device__ __forceinline__ bool us_pred(i64 x, i64 key) { return GE ? (x >= key) : (x > key); }
 
 // first index in [lo, hi) whose ts satisfies pred (GE: ts >= key, else ts > key); hi if none.
-// t_lo = ts[lo], t_hi = ts[hi - 1] (ignored when lo >= hi).  Warp-uniform arguments and result.
+// t_lo = ts[lo], t_hi = ts[hi - 1] (ignored when lo >= hi).  Arguments and result are uniform within the
+// 8-lane group `gmask`; gl = lane index inside the group.
 template <bool GE>
 __device__ __forceinline__ i64 us_search(const i64 *__restrict__ ts, i64 lo, i64 hi, i64 key, i64 t_lo, i64 t_hi,
-                                         int lane) {
+                                         int gl, u32 gmask) {
     if (lo >= hi) return lo;
     if (us_pred<GE>(t_lo, key)) return lo;
     if (!us_pred<GE>(t_hi, key)) return hi;
@@ -34,16 +39,17 @@ __device__ __forceinline__ i64 us_search(const i64 *__restrict__ ts, i64 lo, i64
     i64 g = lo + (i64)(frac * (double)(hi - 1 - lo));
     if (g < lo) g = lo;
     if (g > hi - 1) g = hi - 1;
-    i64 w0 = g - 15;
-    if (w0 + 32 > hi) w0 = hi - 32;
+    i64 w0 = g - 7;
+    if (w0 + 16 > hi) w0 = hi - 16;
     if (w0 < lo) w0 = lo;
-    const i64 idx = w0 + lane;
-    const i64 v = idx < hi ? __ldg(&ts[idx]) : TH_I64_MAX;
-    const u32 bal = __ballot_sync(0xffffffffu, idx < hi ? us_pred<GE>(v, key) : true);
+    const i64 i0 = w0 + gl, i1 = w0 + 8 + gl;
+    const bool f0 = i0 < hi ? !us_pred<GE>(__ldg(&ts[i0]), key) : false;
+    const bool f1 = i1 < hi ? !us_pred<GE>(__ldg(&ts[i1]), key) : false;
+    const int nfalse = __popc(__ballot_sync(gmask, f0) & gmask) + __popc(__ballot_sync(gmask, f1) & gmask);
     i64 l, r;   // answer = first true in [l, r], pred(ts[r]) known true
-    if (bal == 0u) { l = w0 + 32; r = hi - 1; }
-    else if (bal == 0xffffffffu && w0 > lo) { l = lo + 1; r = w0; }
-    else return w0 + (__ffs(bal) - 1);
+    if (nfalse == 0) { l = lo + 1; r = w0; }
+    else if (nfalse == 16) { l = w0 + 16; r = hi - 1; }
+    else return w0 + nfalse;
     while (l < r) {
         const i64 mid = l + ((r - l) >> 1);
         if (us_pred<GE>(__ldg(&ts[mid]), key)) r = mid; else l = mid + 1;
@@ -67,8 +73,10 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
                                                               i64 *__restrict__ o_sm, i64 *__restrict__ o_cnt,
                                                               i64 *__restrict__ o_ag, i64 *__restrict__ o_am) {
     const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * US_WARPS;
-    for (i64 q = (i64)blockIdx.x * US_WARPS + (threadIdx.x >> 5); q < w; q += wstride) {
+    const int gl = lane & (US_GROUP - 1);
+    const u32 gmask = 0xffu << (lane & ~(US_GROUP - 1));
+    const i64 gstride = (i64)gridDim.x * US_GROUPS_PER_BLOCK;
+    for (i64 q = (i64)blockIdx.x * US_GROUPS_PER_BLOCK + (threadIdx.x / US_GROUP); q < w; q += gstride) {
         const i64 u = win_uuid[q];
         i64 a = 0, b = 0;
         if (u >= 0 && u < n_uuids) {
@@ -76,18 +84,22 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
             if (lo < hi) {
                 const i64 ws = win_start[q], we = win_end[q];
                 const i64 t_lo = __ldg(&ts[lo]), t_hi = __ldg(&ts[hi - 1]);
-                a = us_search<true>(ts, lo, hi, ws, t_lo, t_hi, lane);
-                b = a;
-                if (a < hi) b = us_search<false>(ts, a, hi, we, __ldg(&ts[a]), t_hi, lane);
+                // the two ends are independent searches over the whole segment: their probes overlap
+                a = us_search<true>(ts, lo, hi, ws, t_lo, t_hi, gl, gmask);
+                b = us_search<false>(ts, lo, hi, we, t_lo, t_hi, gl, gmask);
+                if (b < a) b = a;   // end before start: empty window
             }
         }
         i64 sg = 0, sm = 0;
         if (VEC) {
             // element pairs (2p, 2p + 1): 16-byte aligned because the column bases are
             const i64 p1 = (b + 1) >> 1;
-            for (i64 p = (a >> 1) + lane; p < p1; p += 32) {
+            for (i64 p = (a >> 1) + gl; p < p1; p += 2 * US_GROUP) {
                 const i64 i0 = p << 1;
-                i64 g0, g1 = 0, m0, m1 = 0;
+                const i64 j0 = (p + US_GROUP) << 1;
+                const bool second = p + US_GROUP < p1;
+                i64 g0, g1 = 0, m0, m1 = 0, h0 = 0, h1 = 0, n0 = 0, n1 = 0;
+                // issue every load of the iteration before consuming any
                 if (i0 + 1 < s_total) {
                     const longlong2 g2 = th_ld16(gpu + i0);
                     const longlong2 m2 = th_ld16(mem + i0);
@@ -95,15 +107,31 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
                 } else {
                     g0 = __ldg(&gpu[i0]); m0 = __ldg(&mem[i0]);
                 }
+                if (second) {
+                    if (j0 + 1 < s_total) {
+                        const longlong2 g2 = th_ld16(gpu + j0);
+                        const longlong2 m2 = th_ld16(mem + j0);
+                        h0 = g2.x; h1 = g2.y; n0 = m2.x; n1 = m2.y;
+                    } else {
+                        h0 = __ldg(&gpu[j0]); n0 = __ldg(&mem[j0]);
+                    }
+                }
                 if (i0 >= a && i0 < b) { sg += g0; sm += m0; }
                 if (i0 + 1 >= a && i0 + 1 < b) { sg += g1; sm += m1; }
+                if (second) {
+                    if (j0 < b) { sg += h0; sm += n0; }          // j0 > a always
+                    if (j0 + 1 < b) { sg += h1; sm += n1; }
+                }
             }
         } else {
-            for (i64 i = a + lane; i < b; i += 32) { sg += __ldg(&gpu[i]); sm += __ldg(&mem[i]); }
+            for (i64 i = a + gl; i < b; i += US_GROUP) { sg += __ldg(&gpu[i]); sm += __ldg(&mem[i]); }
         }
-        sg = th_warp_sum(sg);
-        sm = th_warp_sum(sm);
-        if (lane == 0) {
+#pragma unroll
+        for (int o = US_GROUP / 2; o > 0; o >>= 1) {
+            sg += __shfl_xor_sync(gmask, sg, o);
+            sm += __shfl_xor_sync(gmask, sm, o);
+        }
+        if (gl == 0) {
             const i64 c = b - a;
             if (o_sg) o_sg[q] = sg;
             if (o_sm) o_sm[q] = sm;
@@ -151,7 +179,7 @@ extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int
             US_TRY(sc.out(out_avg_gpu, 8 * zw, mem, &d_ag));
             US_TRY(sc.out(out_avg_mem, 8 * zw, mem, &d_am));
             const bool vec = (((uintptr_t)d_g | (uintptr_t)d_m) & 15) == 0;
-            const int grid = th_grid_for(w, US_WARPS, 64);
+            const int grid = th_grid_for(w, US_GROUPS_PER_BLOCK, 64);
             if (vec)
                 k4_usage_kernel<true><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
                                                                    (const i64 *)d_g, (const i64 *)d_m, w,
