@@ -10,8 +10,10 @@ With N ranks every rank owns its own 4096-uuid shard and 1 M routed queries (wea
 The same run also measures K4 (`th_usage_reduce`) on BASELINE config 3 (1 B samples -> 10 M windows,
 generated on the device) and reports it under "usage_reduce".
 
-Timing: CUDA events on the launching stream around every step, L2 flushed (512 MiB memset) between steps
-and outside the events, W >= 3 warm-up steps, barrier + synchronize on both sides, max over ranks.
+Timing: CUDA events on the launching stream around every step, L2 flushed between steps and outside the
+events by READING a 512 MiB buffer (a write-flush leaves L2 full of dirty lines whose write-back is then
+billed to the kernel: +6 us on a 25 us kernel, measured), W >= 3 warm-up steps, barrier + synchronize on both
+sides, max over ranks.
 `--impl reference` times the reference's own CPU path for the same metric: the SQL text of
 Reservation.would_interfere through sqlite3 (SQLAlchemy is not installable here) on every
 host core, each step a bounded sample of the same workload.
@@ -196,7 +198,7 @@ def _config(n_gpus, ref=False):
     return {'workload': 'BASELINE configs[1]: 1M reservations x 4096 GPU UUIDs, 1M candidate conflict queries per GPU',
             'reservations_per_gpu': N_ROWS, 'uuids_per_gpu': N_UUIDS, 'queries_per_step_per_gpu': N_QUERIES,
             'parallelism': 'uuid-sharded x%d, all-gather of bitmap words' % n_gpus if n_gpus > 1 else 'single GPU',
-            'l2': 'n/a (CPU)' if ref else 'flushed between steps (512 MiB memset, outside the timed events)',
+            'l2': 'n/a (CPU)' if ref else 'flushed between steps (512 MiB read sweep, outside the timed events)',
             'seed': SEED}
 
 
@@ -245,7 +247,7 @@ def run_ours(args):
     qd = [tdev(q[k]) for k in ('uuid_id', 'start', 'end', 'self_id')]
     words = torch.empty((N_QUERIES + 31) // 32, dtype=torch.int32, device=dev)
     gathered = torch.empty(world * words.numel(), dtype=torch.int32, device=dev) if world > 1 else None
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    flush = torch.zeros(64 << 20, dtype=torch.int64, device=dev)     # 512 MiB, read to evict L2 with clean lines
     stream = torch.cuda.current_stream(dev)
     import ctypes as C
     sp = C.c_void_p(stream.cuda_stream)
@@ -260,7 +262,7 @@ def run_ours(args):
         """n steps, each bracketed by its own CUDA events; L2 flushed before every step, outside the events."""
         evs = []
         for _ in range(n):
-            flush.fill_(1)
+            flush.sum()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
             step_fn()
@@ -279,7 +281,7 @@ def run_ours(args):
     info = snap.info()
 
     for _ in range(warmup):
-        flush.fill_(1)
+        flush.sum()
         k2_step()
     barrier()
     with ClockSampler(local) as clocks:
@@ -302,13 +304,20 @@ def run_ours(args):
                                             qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
     ktimes = timed(k2_only, max(steps, 10))
     k_ms = float(np.mean(ktimes))
-    warm = []
-    for _ in range(10):      # warm-L2 figure for context (snapshot resident in L2, as between service ticks)
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream); k2_only(); b.record(stream)
-        warm.append((a, b))
+    # warm-L2 figure for context (snapshot resident in L2, as between service ticks): 20 launches inside one
+    # CUDA graph so that no CPU launch latency sits between the two events
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        cap = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for _ in range(20):
+            native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
+                                                qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, cap))
+    graph.replay()
     torch.cuda.synchronize()
-    k_ms_warm = float(np.mean([a.elapsed_time(b) for a, b in warm]))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(); graph.replay(); b.record()
+    torch.cuda.synchronize()
+    k_ms_warm = a.elapsed_time(b) / 20.0
     peak, peak_src = _peaks()
     alg_bytes = N_QUERIES * 32 + N_ROWS * 25 + 8 * (N_UUIDS + 1) + N_QUERIES // 8
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9

@@ -101,6 +101,61 @@ __device__ __forceinline__ longlong2 th_ld16(const void *p) {
     // read-only 128-bit load; the index entries are immutable while a snapshot is live
     return __ldg(reinterpret_cast<const longlong2 *>(p));
 }
+// streaming 64-bit load (read once, do not keep in L1)
+__device__ __forceinline__ i64 th_ld_stream(const i64 *p) {
+    i64 v;
+    asm volatile("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+
+// 16-byte read-only load that executes only when `pred` holds (otherwise `dflt` is returned).  Written as
+// predicated PTX so that several probes can be in flight together: given plain C++ the compiler turns
+// "load A; load B; use A to decide whether B matters" into two DEPENDENT round trips.
+__device__ __forceinline__ longlong2 th_ld16_if(const void *p, bool pred, longlong2 dflt) {
+    longlong2 v = dflt;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.s32 p, %2, 0;\n"
+        "@p ld.global.nc.v2.s64 {%0, %1}, [%3];\n"
+        "}\n"
+        : "+l"(v.x), "+l"(v.y)
+        : "r"((int)pred), "l"(p));
+    return v;
+}
+
+// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS UBLKCP) ---------------------
+__device__ __forceinline__ u32 th_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void th_mbar_init(unsigned long long *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(th_smem_addr(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void th_mbar_expect_tx(unsigned long long *bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(th_smem_addr(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void th_bulk_g2s(void *smem_dst, const void *gmem_src, u32 bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     th_smem_addr(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(th_smem_addr(bar))
+                 : "memory");
+}
+// orders this thread's earlier generic-proxy accesses to shared memory (e.g. reads of a ring stage, made
+// visible to it by __syncwarp / __syncthreads) before later async-proxy (TMA) writes to the same bytes
+__device__ __forceinline__ void th_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void th_mbar_wait(unsigned long long *bar, u32 phase) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "TH_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra TH_DONE_%=;\n"
+        "bra TH_WAIT_%=;\n"
+        "TH_DONE_%=:\n"
+        "}\n" ::"r"(th_smem_addr(bar)),
+        "r"(phase)
+        : "memory");
+}
 __device__ __forceinline__ i64 th_idc_id(i64 idc) { return idc & TH_I64_MAX; }
 __device__ __forceinline__ bool th_idc_cancelled(i64 idc) { return idc < 0; }
 

@@ -6,15 +6,16 @@
 //   current_events :89-104                   -> th_conflict_sets(TH_MODE_INCLUSIVE, qs = qe = now)
 //   upcoming_events_for_resource :106-118    -> th_conflict_sets(TH_MODE_UPCOMING)
 //
-// Bitmap kernel: the rows of a uuid with start < qe are a prefix of its segment, so the verdict is one
-// lower-bound search over 16-byte {start, m1} entries; the last probe that moved the lower bound IS the
-// prefix's last row, so its m1 (running max of non-cancelled `end`) is already in registers.  One lane
-// per query, one ballot per warp = one 32-bit bitmap word per warp, stored coalesced.
+// Bitmap kernel: the rows of a uuid with start < qe are a prefix of its segment, so the verdict is "does the
+// running maximum m1 of non-cancelled `end` over that prefix exceed qs".  The prefix end is found through the
+// snapshot's time grid (th_common.cuh): one 16-byte cell, then at most a handful of 16-byte {start, m1} rows.
+// One lane per query, one ballot per warp = one 32-bit bitmap word per warp, stored coalesced.
 //
 // Set kernels: one warp per query.  The warp walks the candidate prefix backwards 32 rows at a time with
 // 16-byte loads and stops as soon as the running maximum over the remaining prefix says no further row
 // can match; a second pass re-walks the examined range forwards and compacts matches with ballots.
 #include "th_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -41,59 +42,156 @@ __device__ __forceinline__ int th_prefix_end(const ThP1 *__restrict__ p1, int lo
 }
 
 constexpr int BM_THREADS = 256;
+#ifndef BM_MIN_BLOCKS
+#define BM_MIN_BLOCKS 4
+#endif
 
-// One lane per query.  Memory instructions whose 32 lanes touch 32 different cache lines cost 32 L1
-// wavefronts each, and that -- not bytes -- is what bounds this kernel, so the lookup is built to need as
-// few divergent probes as possible: ONE 16-byte grid cell {pos, cnt, m1_before}; only if the candidate's
-// bucket holds rows, a search over those (usually 1-2) 16-byte {start, m1} entries; only for self-updates a
-// third probe for {a1, m2}.  The four query columns are read coalesced.
-__global__ void __launch_bounds__(BM_THREADS) k2_bitmap_kernel(ThGrid g, const ThP1 *__restrict__ p1,
-                                                               const ThP2 *__restrict__ p2, const ThP4 *__restrict__ p4,
-                                                               i64 n_uuids, i64 m, const i64 *__restrict__ q_uuid,
-                                                               const i64 *__restrict__ q_start,
-                                                               const i64 *__restrict__ q_end,
-                                                               const i64 *__restrict__ q_self, int mode,
-                                                               u32 *__restrict__ out_bits) {
-    const i64 i = (i64)blockIdx.x * BM_THREADS + threadIdx.x;
-    bool hit = false;
-    if (i < m) {
-        const i64 u = q_uuid[i];
-        const i64 qs = q_start[i], qe = q_end[i];
-        const i64 self = (mode == TH_MODE_STRICT) ? q_self[i] : -1;
-        if (u >= 0 && u < n_uuids) {
-            i64 b = 0;
-            if (qe > g.t0) {
-                const u64 d = ((u64)qe - (u64)g.t0) >> g.shift;
-                b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
+// One lane per query, persistent warps.  Two things bound this kernel, and neither is bytes: (1) a memory
+// instruction whose 32 lanes touch 32 different cache lines costs 32 L1 wavefronts and 32 L2 sector
+// requests, and (2) every DEPENDENT round trip to L2/HBM adds ~1 us to the warp, whose latency is the maximum
+// over its lanes.  So the lookup is three levels deep, each level issued for all lanes at once with
+// predicated (not looped, not short-circuited) loads, and level 1 runs several tiles ahead:
+//   level 1  a warp tile = 32 queries x 4 columns (1 KB) arrives in shared memory by four TMA bulk copies
+//            (cp.async.bulk -> UBLKCP) issued by lane 0 into a 4-stage ring with one mbarrier per stage;
+//            warps never synchronise with each other;
+//   level 2  ONE 16-byte grid cell {pos, cnt, m1_before}.  m1 only grows along a segment, so if the rows
+//            before the bucket already end after qs the verdict is "conflict" and level 3 is skipped;
+//   level 3  the first four 16-byte {start, m1} rows of the bucket (a bucket holds ~1 row on average) and,
+//            for self-updates only, the {a1, m2} entries of the five rows the answer can land on.
+// Buckets with more than four rows fall back to a binary search over the rest (about 1 % of the lanes).
+constexpr int BM_WARPS = BM_THREADS / 32;
+constexpr int BM_STAGES = 4;
+constexpr int BM_PROBE = 4;
+
+// level 2: the grid cell of (u, qe); a query for an unknown uuid reads cell 0 and is masked later
+__device__ __forceinline__ const ThCell *k2_cell_of(const ThGrid &g, i64 n_uuids, i64 u, i64 qe) {
+    if (u < 0 || u >= n_uuids) return g.cells;
+    i64 b = 0;
+    if (qe > g.t0) {
+        const u64 d = ((u64)qe - (u64)g.t0) >> g.shift;
+        b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
+    }
+    return g.cells + (u * g.nb + b);
+}
+
+// level 3: verdict from the cell and (if needed) the bucket's rows
+template <int MODE>
+__device__ __forceinline__ bool k2_resolve(const longlong2 c, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2,
+                                           const ThP4 *__restrict__ p4, i64 qs, i64 qe, i64 self) {
+    const int pos = (int)(c.x & 0xffffffffll);
+    const int cnt = (int)(c.x >> 32);
+    if (MODE == TH_MODE_STRICT) {
+        const bool ws = self >= 0;
+        if (!ws && c.y > qs) return true;             // decided by the rows before the bucket
+        const longlong2 far = make_longlong2(TH_I64_MAX, 0);          // {start, m1}: never before qe
+        const longlong2 none = make_longlong2(-1, TH_I64_MIN);       // {a1, m2}
+        longlong2 e[BM_PROBE], t[BM_PROBE + 1];
+#pragma unroll
+        for (int k = 0; k < BM_PROBE; ++k) e[k] = th_ld16_if(&p1[pos + k], cnt > k, far);
+        t[0] = th_ld16_if(&p2[pos - 1], ws && pos > 0, none);
+#pragma unroll
+        for (int k = 0; k < BM_PROBE; ++k) t[k + 1] = th_ld16_if(&p2[pos + k], ws && cnt > k, none);
+        // rows are start-sorted, so the ones before qe are a prefix of the bucket
+        int k = 0;
+        i64 m1 = c.y;
+        longlong2 tt = t[0];
+#pragma unroll
+        for (int j = 0; j < BM_PROBE; ++j)
+            if (e[j].x < qe) { k = j + 1; m1 = e[j].y; tt = t[j + 1]; }
+        if (k == BM_PROBE && cnt > BM_PROBE) {        // long bucket: finish with a binary search
+            int lo = pos + BM_PROBE, hi = pos + cnt;
+            while (lo < hi) {
+                const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+                const longlong2 x = th_ld16(&p1[mid]);
+                if (x.x < qe) { lo = mid + 1; m1 = x.y; } else hi = mid;
             }
-            const longlong2 c = th_ld16(&g.cells[u * g.nb + b]);   // {pos | cnt << 32, m1_before}
-            int lo = (int)(c.x & 0xffffffffll);
-            int hi = lo + (int)(c.x >> 32);
-            if (mode == TH_MODE_STRICT) {
-                i64 m1 = c.y;
-                while (lo < hi) {
-                    const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-                    const longlong2 e = th_ld16(&p1[mid]);   // {start, m1}
-                    if (e.x < qe) { lo = mid + 1; m1 = e.y; } else hi = mid;
-                }
-                // lo - 1 is the last row with start < qe; it is at worst the uuid's sentinel
-                if (self >= 0) {
-                    const longlong2 t = th_ld16(&p2[lo - 1]);   // {a1, m2}
-                    hit = (t.x == self) ? (t.y > qs) : (m1 > qs);
-                } else {
-                    hit = m1 > qs;
-                }
-            } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
-                while (lo < hi) {
-                    const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-                    if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
-                }
-                hit = __ldg(&p4[lo - 1].mall) >= qs;
-            }
+            if (ws) tt = th_ld16(&p2[lo - 1]);
+        }
+        // the last row with start < qe is at worst the uuid's sentinel (m1 = INT64_MIN)
+        return (ws && tt.x == self) ? (tt.y > qs) : (m1 > qs);
+    } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
+        int lo = pos, hi = pos + cnt;
+        while (lo < hi) {
+            const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+            if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
+        }
+        // lo >= 1: bucket 0 starts with the sentinel, later buckets are preceded by it
+        return __ldg(&p4[lo - 1].mall) >= qs;
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
+    ThGrid g, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2, const ThP4 *__restrict__ p4, i64 n_uuids, i64 m,
+    const i64 *__restrict__ q_uuid, const i64 *__restrict__ q_start, const i64 *__restrict__ q_end,
+    const i64 *__restrict__ q_self, int cols_aligned16, u32 *__restrict__ out_bits) {
+    __shared__ __align__(128) i64 sq[BM_WARPS][BM_STAGES][4][32];
+    __shared__ __align__(8) unsigned long long bar[BM_WARPS][BM_STAGES];
+    constexpr u32 COL = 32 * sizeof(i64);
+    constexpr u32 NCOL = MODE == TH_MODE_STRICT ? 4 : 3;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const i64 full_tiles = cols_aligned16 ? m / 32 : 0;      // warp tiles that go through TMA
+    const i64 tiles = (m + 31) / 32;
+    const i64 gw = (i64)blockIdx.x * BM_WARPS + warp;
+    const i64 nw = (i64)gridDim.x * BM_WARPS;
+
+    auto issue = [&](i64 tile, int st) {   // lane 0: arm the stage's barrier, start its bulk copies
+        const i64 base = tile * 32;
+        th_mbar_expect_tx(&bar[warp][st], NCOL * COL);
+        th_bulk_g2s(sq[warp][st][0], q_uuid + base, COL, &bar[warp][st]);
+        th_bulk_g2s(sq[warp][st][1], q_end + base, COL, &bar[warp][st]);
+        th_bulk_g2s(sq[warp][st][2], q_start + base, COL, &bar[warp][st]);
+        if (MODE == TH_MODE_STRICT) th_bulk_g2s(sq[warp][st][3], q_self + base, COL, &bar[warp][st]);
+    };
+    // levels 1 + 2 of one tile: query columns out of the ring (or straight from global for the ragged tail),
+    // then the grid cell
+    auto fetch = [&](i64 tile, u32 it, i64 &u, i64 &qs, i64 &qe, i64 &self, longlong2 &cell) {
+        const int st = it % BM_STAGES;
+        if (tile < full_tiles) {
+            th_mbar_wait(&bar[warp][st], (it / BM_STAGES) & 1);
+            u = sq[warp][st][0][lane];
+            qe = sq[warp][st][1][lane];
+            qs = sq[warp][st][2][lane];
+            self = MODE == TH_MODE_STRICT ? sq[warp][st][3][lane] : -1;
+            __syncwarp();                                   // every lane has read the stage: refill it
+            const i64 refill = tile + (i64)BM_STAGES * nw;
+            if (lane == 0 && refill < full_tiles) { th_fence_proxy_async(); issue(refill, st); }
+        } else {   // ragged last tile or unaligned caller buffers
+            const i64 i = tile * 32 + lane;
+            const i64 ic = i < m ? i : m - 1;
+            u = th_ld_stream(&q_uuid[ic]);
+            qe = th_ld_stream(&q_end[ic]);
+            qs = th_ld_stream(&q_start[ic]);
+            self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
+        }
+        cell = th_ld16(k2_cell_of(g, n_uuids, u, qe));
+    };
+
+    if (lane == 0) {
+#pragma unroll
+        for (int st = 0; st < BM_STAGES; ++st) th_mbar_init(&bar[warp][st], 1);
+    }
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+        for (int st = 0; st < BM_STAGES; ++st) {
+            const i64 t = gw + (i64)st * nw;
+            if (t < full_tiles) issue(t, st);
         }
     }
-    const u32 word = __ballot_sync(0xffffffffu, hit);
-    if ((threadIdx.x & 31) == 0 && i < m) out_bits[i >> 5] = word;
+    // Measured on B200 (tools/k2_sweep.py): issuing the cell of tile k + 1 before the rows of tile k did not pay
+    // (26.6 us vs 24.5 us cold at 1 M queries) -- with 32 resident warps per SM the kernel is bound by issue
+    // slots and effective DRAM rate, not by the two-deep dependency -- so each tile runs levels 2 and 3 in turn.
+    u32 it = 0;
+    for (i64 tile = gw; tile < tiles; tile += nw, ++it) {
+        i64 u, qs, qe, self;
+        longlong2 cell;
+        fetch(tile, it, u, qs, qe, self, cell);
+        const i64 i = tile * 32 + lane;
+        const bool hit = (i < m) && (u >= 0 && u < n_uuids) && k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
+        const u32 word = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) out_bits[tile] = word;
+    }
 }
 
 // ---- conflict sets ------------------------------------------------------------------------------------
@@ -314,10 +412,32 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     TH_TRY(sc.in(q_end, 8 * zm, mem, &d_e));
     if (q_self_id) TH_TRY(sc.in(q_self_id, 8 * zm, mem, &d_f));
     TH_TRY(sc.out(out_bits_u32, 4 * words, mem, &d_bits));
-    const unsigned blocks = (unsigned)((m + BM_THREADS - 1) / BM_THREADS);
-    k2_bitmap_kernel<<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m, (const i64 *)d_u,
-                                                    (const i64 *)d_s, (const i64 *)d_e, (const i64 *)d_f, mode,
-                                                    (u32 *)d_bits);
+    const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp a tile
+    // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
+    static int occ[2] = {0, 0};
+    const int oi = mode == TH_MODE_STRICT ? 0 : 1;
+    if (occ[oi] == 0) {
+        int v = 0;
+        if (mode == TH_MODE_STRICT) TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_STRICT>, BM_THREADS, 0));
+        else TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_INCLUSIVE>, BM_THREADS, 0));
+        occ[oi] = v > 0 ? v : 1;
+    }
+    int n_sms = TH_NUM_SMS;
+    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, h->device);
+    const i64 resident = (i64)n_sms * occ[oi];
+    const unsigned blocks = (unsigned)(n_tiles < resident ? n_tiles : resident);
+    int al16 = ((((uintptr_t)d_u | (uintptr_t)d_s | (uintptr_t)d_e | (uintptr_t)d_f) & 15) == 0) ? 1 : 0;
+    if (getenv("TH_K2_DIRECT")) al16 = 0;
+    if (mode == TH_MODE_STRICT)
+        k2_bitmap_kernel<TH_MODE_STRICT><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m,
+                                                                        (const i64 *)d_u, (const i64 *)d_s,
+                                                                        (const i64 *)d_e, (const i64 *)d_f, al16,
+                                                                        (u32 *)d_bits);
+    else
+        k2_bitmap_kernel<TH_MODE_INCLUSIVE><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids,
+                                                                           m, (const i64 *)d_u, (const i64 *)d_s,
+                                                                           (const i64 *)d_e, (const i64 *)d_f, al16,
+                                                                           (u32 *)d_bits);
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_bits_u32, d_bits, 4 * words, mem, st));
     if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
