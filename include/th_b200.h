@@ -134,6 +134,17 @@ int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int64_t period
 int th_violation_join(const th_snapshot *h, int64_t now_us, int strict, int64_t p, const int64_t *proc_uuid,
                       const int64_t *proc_owner, uint8_t *out_flag_u8, int64_t *out_res_id, int mem, void *stream);
 
+/* No counterpart in the reference.  Same join as th_violation_join for callers that must not allocate device
+ * memory (a protection tick on a GPU whose memory a reserved job has filled; a process with a fixed device
+ * footprint): the per-uuid table between the two kernels lives in a fixed 1 MiB array inside the library, so
+ * the snapshot may have at most TH_STATIC_JOIN_MAX_UUIDS uuids (TH_ECAPACITY beyond that).  All pointers are
+ * DEVICE pointers on the snapshot's device; work is only enqueued on `stream`.  The first call on a device
+ * resolves the array's address and should be made outside stream capture.  Every call on a device shares the
+ * array: calls whose kernels could overlap on the GPU must be serialised by the caller. */
+#define TH_STATIC_JOIN_MAX_UUIDS 65536
+int th_violation_join_static(const th_snapshot *h, int64_t now_us, int strict, int64_t p, const int64_t *proc_uuid,
+                             const int64_t *proc_owner, uint8_t *out_flag_u8, int64_t *out_res_id, void *stream);
+
 /* Usage averaging (tensorhive/core/services/UsageLoggingService.py:25-30,85-105,196-229): samples are
  * grouped by uuid (uuid_offsets[n_uuids + 1]) and ascending in ts within a uuid; window j sums the
  * samples of win_uuid[j] with win_start[j] <= ts <= win_end[j].  out_avg_* = sum // count, or -1 when

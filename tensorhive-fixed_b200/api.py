@@ -217,6 +217,30 @@ class Snapshot:
         return flags, res
 
 
+    STATIC_JOIN_MAX_UUIDS = 65536
+
+    def violation_join_static(self, now_us: int, strict: bool, proc_uuid, proc_owner, out_flags, out_res_id) -> None:
+        """The violation join without a single device allocation inside the library: for callers that cannot
+        allocate (the GPU's memory is already full of a reserved user's job, or the process runs with a fixed
+        device footprint).  Every array is a CUDA tensor the caller already owns -- ``out_flags`` uint8[p] and
+        ``out_res_id`` int64[p] included -- and the work is only enqueued on torch's current stream.  Snapshots
+        with more than ``STATIC_JOIN_MAX_UUIDS`` uuids are refused.  Calls on one GPU share one built-in table:
+        do not let two of them run concurrently."""
+        import torch
+        for name, t, dt in (('proc_uuid', proc_uuid, torch.int64), ('proc_owner', proc_owner, torch.int64),
+                            ('out_flags', out_flags, torch.uint8), ('out_res_id', out_res_id, torch.int64)):
+            if not (_is_torch_cuda(t) and t.dtype == dt and t.is_contiguous()):
+                raise TypeError('%s must be a contiguous CUDA tensor of %s' % (name, dt))
+        p = int(proc_uuid.numel())
+        if not (proc_owner.numel() == p and out_flags.numel() == p and out_res_id.numel() == p):
+            raise ValueError('all four arrays must have the same length')
+        stream = C.c_void_p(torch.cuda.current_stream(proc_uuid.device).cuda_stream)
+        native.check(self._lib.th_violation_join_static(self._h, int(now_us), 1 if strict else 0, p,
+                                                        C.c_void_p(proc_uuid.data_ptr()), C.c_void_p(proc_owner.data_ptr()),
+                                                        C.c_void_p(out_flags.data_ptr()), C.c_void_p(out_res_id.data_ptr()),
+                                                        stream))
+
+
 def usage_reduce(uuid_offsets, ts, gpu, mem, win_uuid, win_start, win_end, device: int = 0):
     """(sum_gpu, sum_mem, count, avg_gpu, avg_mem) per window; avg = sum // count or -1
     (tensorhive/core/services/UsageLoggingService.py:25-30)."""

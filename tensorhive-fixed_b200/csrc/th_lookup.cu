@@ -11,6 +11,7 @@
 // warp walks backwards 32 rows per step with 16-byte loads until the running maximum of non-cancelled
 // `end` (m1) proves nothing earlier can still be current.
 #include "th_common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -313,5 +314,87 @@ extern "C" int th_violation_join(const th_snapshot *h, int64_t now_us, int stric
     TH_TRY(th_copy_back(out_flag_u8, d_f, zp, mem, st));
     TH_TRY(th_copy_back(out_res_id, d_r, 8 * zp, mem, st));
     if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// th_violation_join_static -- the violation join for callers that must not allocate device memory.
+//
+// Who that is: a protection tick that runs on a GPU whose HBM a reserved user's job has already filled (an
+// allocation there can fail, or succeed only by evicting someone), and host processes that promised their
+// operator a fixed device footprint after start-up.  th_violation_join needs a per-uuid table of the current
+// reservation (id, owner) between its two kernels and takes it from the stream-ordered allocator; this variant
+// keeps that table in a fixed array that is part of the library image instead.
+//
+// The price is the fixed size: TH_STATIC_JOIN_MAX_UUIDS uuids (1 MiB of device memory on every GPU that loads
+// the library, held until the process exits).  Larger snapshots are refused with TH_ECAPACITY.
+//
+// The array is shared by every call on a device and still holds the previous call's table when the next one
+// starts.  Nothing in it has to be zeroed: the first kernel rewrites entries [0, n_uuids) and the second
+// kernel reads only those.  Two calls whose kernels overlap on the same GPU (different streams, or different
+// threads on the same snapshot) would overwrite each other's table -- serialise them.
+//
+// The device address of the array is looked up the first time a device is used (cudaGetSymbolAddress, with
+// that device current).  Make that first call outside any stream capture.
+static __device__ __align__(256) i64 g_static_join_table[2 * TH_STATIC_JOIN_MAX_UUIDS];   // [res_id | owner]
+
+namespace {
+constexpr int SJ_MAX_DEVICES = 64;
+std::mutex g_sj_mutex;
+i64 *g_sj_ptr[SJ_MAX_DEVICES] = {nullptr};
+
+// device address of g_static_join_table on the CURRENT device; resolved once per device
+int sj_table(int device, i64 **out) {
+    if (device < 0 || device >= SJ_MAX_DEVICES) {
+        th_set_error("th_violation_join_static: device index %d is beyond the %d this entry point tracks", device,
+                     SJ_MAX_DEVICES);
+        return TH_EINVAL;
+    }
+    std::lock_guard<std::mutex> lock(g_sj_mutex);
+    if (g_sj_ptr[device] == nullptr) {
+        // In host code `g_static_join_table` is only a handle for the symbol, not an address a kernel can use.
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_join_table);
+        if (e != cudaSuccess || p == nullptr) {
+            th_set_error("th_violation_join_static: cudaGetSymbolAddress on device %d -> %s", device,
+                         cudaGetErrorString(e));
+            return TH_ECUDA;
+        }
+        g_sj_ptr[device] = (i64 *)p;
+    }
+    *out = g_sj_ptr[device];
+    return TH_OK;
+}
+}  // namespace
+
+extern "C" int th_violation_join_static(const th_snapshot *h, int64_t now_us, int strict, int64_t p,
+                                        const int64_t *proc_uuid, const int64_t *proc_owner, uint8_t *out_flag_u8,
+                                        int64_t *out_res_id, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_violation_join_static: snapshot not loaded");
+    TH_REQUIRE(p >= 0, "th_violation_join_static: negative p");
+    if (h->n_uuids > TH_STATIC_JOIN_MAX_UUIDS) {
+        th_set_error("th_violation_join_static: snapshot has %lld uuids, the built-in table holds %d; use "
+                     "th_violation_join (which allocates) or shard the calendar",
+                     (long long)h->n_uuids, TH_STATIC_JOIN_MAX_UUIDS);
+        return TH_ECAPACITY;
+    }
+    if (p == 0) return TH_OK;
+    TH_REQUIRE(proc_uuid && proc_owner && out_flag_u8 && out_res_id, "th_violation_join_static: NULL array");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_violation_join_static: cannot select device %d", h->device); return TH_ECUDA; }
+    i64 *table = nullptr;
+    TH_TRY(sj_table(h->device, &table));
+    i64 *cur_res = table, *cur_owner = table + TH_STATIC_JOIN_MAX_UUIDS;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (h->n_uuids > 0) {
+        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4,
+                                                                                        h->n_uuids, now_us, cur_res,
+                                                                                        cur_owner);
+    }
+    k5_violation_kernel<<<th_grid_for(p, 256 * 4, 16), 256, 0, st>>>(cur_res, cur_owner, h->n_uuids, strict ? 1 : 0, p,
+                                                                     (const i64 *)proc_uuid, (const i64 *)proc_owner,
+                                                                     (u8 *)out_flag_u8, (i64 *)out_res_id);
+    TH_CUDA(cudaGetLastError());
     return TH_OK;
 }

@@ -34,6 +34,7 @@ SIGNATURES = {
     'th_upcoming': (_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
     'th_upcoming_owner_flags': (_int, [_vp, _i64, _i64, _i64, _vp, _vp, _int, _vp, _int, _vp]),
     'th_violation_join': (_int, [_vp, _i64, _int, _i64, _vp, _vp, _vp, _vp, _int, _vp]),
+    'th_violation_join_static': (_int, [_vp, _i64, _int, _i64, _vp, _vp, _vp, _vp, _vp]),
     'th_usage_reduce': (_int, [_int, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                _int, _vp]),
     'th_sort_pairs': (_int, [_int, _i64, _vp, _vp, _vp, _int, _vp]),
