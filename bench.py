@@ -197,7 +197,8 @@ def run_reference(args):
 def _config(n_gpus, ref=False):
     return {'workload': 'BASELINE configs[1]: 1M reservations x 4096 GPU UUIDs, 1M candidate conflict queries per GPU',
             'reservations_per_gpu': N_ROWS, 'uuids_per_gpu': N_UUIDS, 'queries_per_step_per_gpu': N_QUERIES,
-            'parallelism': 'uuid-sharded x%d, all-gather of bitmap words' % n_gpus if n_gpus > 1 else 'single GPU',
+            'parallelism': ('uuid-sharded x%d, K2 fused with the all-gather of bitmap words over NVLink peer memory' % n_gpus
+                            if n_gpus > 1 else 'single GPU'),
             'l2': 'n/a (CPU)' if ref else 'flushed between steps (512 MiB read sweep, outside the timed events)',
             'seed': SEED}
 
@@ -246,17 +247,21 @@ def run_ours(args):
     d_cal = [tdev(cal[k]) for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')]
     qd = [tdev(q[k]) for k in ('uuid_id', 'start', 'end', 'self_id')]
     words = torch.empty((N_QUERIES + 31) // 32, dtype=torch.int32, device=dev)
-    gathered = torch.empty(world * words.numel(), dtype=torch.int32, device=dev) if world > 1 else None
+    px = None
+    if world > 1:       # K2 fused with the all-gather of its words over peer memory (no NCCL call per step)
+        from tensorhive_fixed_b200 import sharding
+        px = sharding.PeerExchange(local, world, rank, N_QUERIES)
     flush = torch.zeros(64 << 20, dtype=torch.int64, device=dev)     # 512 MiB, read to evict L2 with clean lines
     stream = torch.cuda.current_stream(dev)
     import ctypes as C
     sp = C.c_void_p(stream.cuda_stream)
 
     def k2_step():
-        native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(), qd[2].data_ptr(),
-                                            qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
-        if dist is not None:
-            dist.all_gather_into_tensor(gathered, words)
+        if px is None:
+            native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
+                                                qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+            return words
+        return px.conflict_words(snap, qd[0], qd[1], qd[2], qd[3])      # [world, words] on every rank
 
     def timed(step_fn, n):
         """n steps, each bracketed by its own CUDA events; L2 flushed before every step, outside the events."""
@@ -288,12 +293,14 @@ def run_ours(args):
         barrier()
         times = timed(k2_step, steps)
         barrier()
-        # keep the GPU busy long enough for at least a few clock samples
+        # keep the GPU busy long enough for at least a few clock samples (kernel only: ranks run this loop a
+        # different number of times, so it must not contain a collective)
         t_end = time.perf_counter() + 1.0
-        extra = 0
         while time.perf_counter() < t_end:
-            k2_step(); extra += 1
-        torch.cuda.synchronize()
+            for _ in range(50):
+                native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
+                                                    qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+            torch.cuda.synchronize()
     total_ms = max_over_ranks(float(sum(times)))
     ms_per_step = total_ms / steps
     value = world * N_QUERIES * steps / (total_ms * 1e-3)
@@ -306,18 +313,20 @@ def run_ours(args):
     k_ms = float(np.mean(ktimes))
     # warm-L2 figure for context (snapshot resident in L2, as between service ticks): 20 launches inside one
     # CUDA graph so that no CPU launch latency sits between the two events
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        cap = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        for _ in range(20):
-            native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
-                                                qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, cap))
-    graph.replay()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record(); graph.replay(); b.record()
-    torch.cuda.synchronize()
-    k_ms_warm = a.elapsed_time(b) / 20.0
+    k_ms_warm = None
+    if dist is None:      # (no graph capture next to a live NCCL communicator: its watchdog polls events)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            cap = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            for _ in range(20):
+                native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
+                                                    qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, cap))
+        graph.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); graph.replay(); b.record()
+        torch.cuda.synchronize()
+        k_ms_warm = a.elapsed_time(b) / 20.0
     peak, peak_src = _peaks()
     alg_bytes = N_QUERIES * 32 + N_ROWS * 25 + 8 * (N_UUIDS + 1) + N_QUERIES // 8
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
@@ -327,13 +336,20 @@ def run_ours(args):
     pin_np = [p.numpy() for p in pin]
     out_pin = torch.empty((N_QUERIES + 31) // 32, dtype=torch.int32).pin_memory()
 
+    stage = [torch.empty_like(t) for t in qd] if px is not None else None
+    out_all = torch.empty(world * ((N_QUERIES + 31) // 32), dtype=torch.int32).pin_memory() if px is not None else None
+
     def e2e_step():
-        native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, pin_np[0].ctypes.data, pin_np[1].ctypes.data,
-                                            pin_np[2].ctypes.data, pin_np[3].ctypes.data, 0, out_pin.data_ptr(), 0, sp))
-        if dist is not None:
-            words.copy_(out_pin, non_blocking=True)
-            dist.all_gather_into_tensor(gathered, words)
-            torch.cuda.synchronize()
+        if px is None:
+            native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, pin_np[0].ctypes.data, pin_np[1].ctypes.data,
+                                                pin_np[2].ctypes.data, pin_np[3].ctypes.data, 0, out_pin.data_ptr(), 0,
+                                                sp))
+            return
+        for d, h in zip(stage, pin):                      # pinned host -> device
+            d.copy_(h, non_blocking=True)
+        g = px.conflict_words(snap, stage[0], stage[1], stage[2], stage[3])
+        out_all.copy_(g.reshape(-1), non_blocking=True)   # everybody's verdicts back on the host
+        torch.cuda.synchronize()
 
     for _ in range(3):
         e2e_step()
@@ -347,15 +363,22 @@ def run_ours(args):
     e2e_value = world * N_QUERIES * steps / e2e_s
     # check the last e2e result against the device-resident run (same queries)
     k2_only(); torch.cuda.synchronize()
-    assert np.array_equal(out_pin.numpy(), words.cpu().numpy()), 'host-path and device-path bitmaps differ'
+    if px is None:
+        assert np.array_equal(out_pin.numpy(), words.cpu().numpy()), 'host-path and device-path bitmaps differ'
+    else:
+        px.check()
+        mine = out_all.numpy().reshape(world, -1)[rank]
+        assert np.array_equal(mine, words.cpu().numpy()), 'fused-exchange words differ from the plain kernel'
 
     line = {'metric': 'conflict_queries_per_s', 'value': value, 'unit': 'queries/s', 'n_gpus': world, 'steps': steps,
             'warmup': warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'int64', 'data': 'synthetic', 'config': _config(world),
             'clocks': clocks.summary(),
             'e2e': {'value': e2e_value, 'unit': 'queries/s', 'h2d_bytes_per_step': 32 * N_QUERIES,
-                    'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32), 'ms_per_step': 1e3 * e2e_s / steps,
-                    'api': 'th_conflict_bitmap(TH_MEM_HOST) on pinned buffers'},
+                    'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32) * (world if px is not None else 1),
+                    'ms_per_step': 1e3 * e2e_s / steps,
+                    'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
+                            'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
             'gpu_launches': steps,
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel'), 'peak_source': peak_src,
@@ -375,6 +398,9 @@ def run_ours(args):
         line['cpu_baseline'] = None
     if rank == 0:
         print(json.dumps(line), flush=True)
+    if px is not None:
+        dist.barrier()
+        px.close()
     snap.close()
     if dist is not None:
         dist.destroy_process_group()

@@ -96,6 +96,29 @@ static inline ThGrid th_grid_of(const th_snapshot *h) {
     ThGrid g; g.cells = h->grid; g.t0 = h->grid_t0; g.shift = h->grid_shift; g.nb = h->grid_nb; return g;
 }
 
+// ---- peer exchange (multi-GPU): where a fused kernel deposits its bitmap words on every rank --------------
+#define TH_MAX_PEERS 16
+struct ThPeerOut {
+    int n;                       // 0 = no exchange (single GPU)
+    int rank;
+    u32 epoch;                   // value written to the flags when this launch's words are complete
+    i64 word_off;                // rank * words_per_rank (+ buffer parity offset)
+    u32 *dst[TH_MAX_PEERS];      // gathered-words buffer of every rank (peer-mapped device pointers)
+    u32 *flags[TH_MAX_PEERS];    // flags[p][rank] lives on rank p
+    u32 *done;                   // local counter of finished CTAs (0 between launches)
+};
+struct th_peer {
+    int device, world, rank;
+    i64 words_per_rank;          // capacity per rank and buffer
+    u32 epoch;
+    void *base;                  // local allocation: [2 buffers][world][words_per_rank] u32, then flags[world], done, err
+    void *peer_base[TH_MAX_PEERS];
+    int connected;
+};
+static inline size_t th_peer_bytes(int world, i64 wpr) { return (size_t)2 * world * wpr * 4 + (size_t)(world + 8) * 4; }
+static inline u32 *th_peer_words(void *base, int world, i64 wpr, int parity) { return (u32 *)base + (size_t)parity * world * wpr; }
+static inline u32 *th_peer_flags(void *base, int world, i64 wpr) { return (u32 *)base + (size_t)2 * world * wpr; }
+
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ longlong2 th_ld16(const void *p) {
     // read-only 128-bit load; the index entries are immutable while a snapshot is live

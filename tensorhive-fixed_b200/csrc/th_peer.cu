@@ -1,0 +1,91 @@
+// Peer group for the fused K2 + all-gather (the reference has no multi-GPU path at all).
+//
+// One process per GPU.  Every rank allocates one buffer with cudaMalloc -- two generations of the gathered bitmap
+// words [world][words_per_rank] plus one arrival flag per rank -- exports it as a CUDA IPC handle, and maps the
+// buffers of all other ranks (NVLink peer access is enabled lazily by the mapping).  The handles travel through
+// whatever the host side has (torch.distributed.all_gather_object in sharding.py).
+//
+// Two generations: rank A can run at most one step ahead of rank B (A's wait kernel of step k+1 needs B's flag of
+// step k+1, which B raises only after finishing, in stream order, everything of step k), so step k+2 never
+// overwrites words of step k that somebody still reads.
+#include "th_common.cuh"
+#include <string.h>
+
+extern "C" int th_peer_create(int device, int world, int rank, int64_t words_per_rank, th_peer **out,
+                              void *handle_out_64) {
+    TH_REQUIRE(out && handle_out_64, "th_peer_create: NULL output");
+    TH_REQUIRE(world >= 1 && world <= TH_MAX_PEERS, "th_peer_create: world %d outside [1, %d]", world, TH_MAX_PEERS);
+    TH_REQUIRE(rank >= 0 && rank < world, "th_peer_create: rank %d outside [0, %d)", rank, world);
+    TH_REQUIRE(words_per_rank > 0 && words_per_rank < (1ll << 28), "th_peer_create: bad words_per_rank");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    int prev = 0;
+    TH_CUDA(cudaGetDevice(&prev));
+    if (prev != device) TH_CUDA(cudaSetDevice(device));
+    th_peer *p = new th_peer();
+    memset(p, 0, sizeof(*p));
+    p->device = device; p->world = world; p->rank = rank; p->words_per_rank = words_per_rank;
+    const size_t bytes = th_peer_bytes(world, words_per_rank);
+    cudaError_t e = cudaMalloc(&p->base, bytes);
+    if (e == cudaSuccess) e = cudaMemset(p->base, 0, bytes);
+    cudaIpcMemHandle_t hnd;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hnd, p->base);
+    if (prev != device) cudaSetDevice(prev);
+    if (e != cudaSuccess) {
+        th_set_error("th_peer_create: %s", cudaGetErrorString(e));
+        if (p->base) cudaFree(p->base);
+        delete p;
+        return e == cudaErrorMemoryAllocation ? TH_ENOMEM : TH_ECUDA;
+    }
+    memcpy(handle_out_64, &hnd, 64);
+    *out = p;
+    return TH_OK;
+}
+
+// all_handles: world x 64 bytes in rank order (this rank's own entry is ignored).  With local_ptrs != NULL the
+// entries are device pointers of buffers in THIS process instead (single-process emulation of several ranks for
+// tests; IPC handles cannot be opened by the process that exported them).
+extern "C" int th_peer_connect(th_peer *p, const void *all_handles, void *const *local_ptrs) {
+    TH_REQUIRE(p != nullptr && p->base, "th_peer_connect: peer group not created");
+    TH_REQUIRE(all_handles || local_ptrs, "th_peer_connect: no handles");
+    int prev = 0;
+    TH_CUDA(cudaGetDevice(&prev));
+    if (prev != p->device) TH_CUDA(cudaSetDevice(p->device));
+    int rc = TH_OK;
+    for (int r = 0; r < p->world && rc == TH_OK; ++r) {
+        if (r == p->rank) { p->peer_base[r] = p->base; continue; }
+        if (local_ptrs) { p->peer_base[r] = local_ptrs[r]; continue; }
+        cudaIpcMemHandle_t hnd;
+        memcpy(&hnd, (const char *)all_handles + (size_t)r * 64, 64);
+        void *ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, hnd, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            th_set_error("th_peer_connect: cudaIpcOpenMemHandle(rank %d) -> %s", r, cudaGetErrorString(e));
+            rc = TH_ECUDA;
+        }
+        p->peer_base[r] = ptr;
+    }
+    if (prev != p->device) cudaSetDevice(prev);
+    if (rc == TH_OK) p->connected = local_ptrs ? 2 : 1;
+    return rc;
+}
+
+extern "C" int th_peer_local_base(th_peer *p, void **out) {
+    TH_REQUIRE(p != nullptr && out, "th_peer_local_base: NULL");
+    *out = p->base;
+    return TH_OK;
+}
+
+extern "C" int th_peer_destroy(th_peer *p) {
+    if (!p) return TH_OK;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(p->device);
+    cudaDeviceSynchronize();
+    if (p->connected == 1)
+        for (int r = 0; r < p->world; ++r)
+            if (r != p->rank && p->peer_base[r]) cudaIpcCloseMemHandle(p->peer_base[r]);
+    if (p->base) cudaFree(p->base);
+    cudaSetDevice(prev);
+    delete p;
+    return TH_OK;
+}

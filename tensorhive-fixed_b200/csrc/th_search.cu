@@ -124,7 +124,7 @@ template <int MODE>
 __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     ThGrid g, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2, const ThP4 *__restrict__ p4, i64 n_uuids, i64 m,
     const i64 *__restrict__ q_uuid, const i64 *__restrict__ q_start, const i64 *__restrict__ q_end,
-    const i64 *__restrict__ q_self, int cols_aligned16, u32 *__restrict__ out_bits) {
+    const i64 *__restrict__ q_self, int cols_aligned16, u32 *__restrict__ out_bits, ThPeerOut po) {
     __shared__ __align__(128) i64 sq[BM_WARPS][BM_STAGES][4][32];
     __shared__ __align__(8) unsigned long long bar[BM_WARPS][BM_STAGES];
     constexpr u32 COL = 32 * sizeof(i64);
@@ -190,8 +190,41 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         const i64 i = tile * 32 + lane;
         const bool hit = (i < m) && (u >= 0 && u < n_uuids) && k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
         const u32 word = __ballot_sync(0xffffffffu, hit);
-        if (lane == 0) out_bits[tile] = word;
+        if (lane == 0) {
+            if (out_bits) out_bits[tile] = word;
+            // fused exchange: the word goes straight into every rank's gathered buffer over NVLink (peer stores)
+            for (int p = 0; p < po.n; ++p) po.dst[p][po.word_off + tile] = word;
+        }
     }
+    if (po.n > 0) {
+        // completion: every CTA publishes its peer stores system-wide, the last one to finish raises this
+        // rank's flag on every peer (the receivers' wait kernel polls it)
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const u32 prev = atomicAdd(po.done, 1u);
+            if (prev == gridDim.x - 1) {
+                __threadfence_system();
+                for (int p = 0; p < po.n; ++p) {
+                    volatile u32 *f = po.flags[p] + po.rank;
+                    *f = po.epoch;
+                }
+                __threadfence_system();
+                *po.done = 0;
+            }
+        }
+    }
+}
+
+// receivers: wait until every rank's flag has reached `epoch` (bounded; sets *err on timeout)
+__global__ void k2_wait_flags_kernel(volatile u32 *flags, int world, u32 epoch, int *err) {
+    const int r = threadIdx.x;
+    if (r >= world) return;
+    for (u64 spins = 0; (int)(flags[r] - epoch) < 0; ++spins) {
+        if (spins > (1ull << 24)) { *err = 1; return; }
+        __nanosleep(100);
+    }
+    __threadfence_system();
 }
 
 // ---- conflict sets ------------------------------------------------------------------------------------
@@ -390,6 +423,38 @@ __global__ void __launch_bounds__(XS_THREADS) xs_write_kernel(const int *__restr
 
 }  // namespace
 
+static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d_s, const void *d_e, const void *d_f,
+                     int mode, u32 *d_bits, const ThPeerOut &po, cudaStream_t st) {
+    const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp a tile
+    // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
+    static int occ[2] = {0, 0};
+    const int oi = mode == TH_MODE_STRICT ? 0 : 1;
+    if (occ[oi] == 0) {
+        int v = 0;
+        if (mode == TH_MODE_STRICT) TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_STRICT>, BM_THREADS, 0));
+        else TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_INCLUSIVE>, BM_THREADS, 0));
+        occ[oi] = v > 0 ? v : 1;
+    }
+    int n_sms = TH_NUM_SMS;
+    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, h->device);
+    const i64 resident = (i64)n_sms * occ[oi];
+    const unsigned blocks = (unsigned)(n_tiles < resident ? (n_tiles > 0 ? n_tiles : 1) : resident);
+    int al16 = ((((uintptr_t)d_u | (uintptr_t)d_s | (uintptr_t)d_e | (uintptr_t)d_f) & 15) == 0) ? 1 : 0;
+    if (getenv("TH_K2_DIRECT")) al16 = 0;
+    if (mode == TH_MODE_STRICT)
+        k2_bitmap_kernel<TH_MODE_STRICT><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m,
+                                                                        (const i64 *)d_u, (const i64 *)d_s,
+                                                                        (const i64 *)d_e, (const i64 *)d_f, al16, d_bits,
+                                                                        po);
+    else
+        k2_bitmap_kernel<TH_MODE_INCLUSIVE><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids,
+                                                                           m, (const i64 *)d_u, (const i64 *)d_s,
+                                                                           (const i64 *)d_e, (const i64 *)d_f, al16,
+                                                                           d_bits, po);
+    TH_CUDA(cudaGetLastError());
+    return TH_OK;
+}
+
 extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t *q_uuid, const int64_t *q_start,
                                   const int64_t *q_end, const int64_t *q_self_id, int mode, uint32_t *out_bits_u32,
                                   int mem, void *stream) {
@@ -412,32 +477,9 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     TH_TRY(sc.in(q_end, 8 * zm, mem, &d_e));
     if (q_self_id) TH_TRY(sc.in(q_self_id, 8 * zm, mem, &d_f));
     TH_TRY(sc.out(out_bits_u32, 4 * words, mem, &d_bits));
-    const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp a tile
-    // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
-    static int occ[2] = {0, 0};
-    const int oi = mode == TH_MODE_STRICT ? 0 : 1;
-    if (occ[oi] == 0) {
-        int v = 0;
-        if (mode == TH_MODE_STRICT) TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_STRICT>, BM_THREADS, 0));
-        else TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_INCLUSIVE>, BM_THREADS, 0));
-        occ[oi] = v > 0 ? v : 1;
-    }
-    int n_sms = TH_NUM_SMS;
-    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, h->device);
-    const i64 resident = (i64)n_sms * occ[oi];
-    const unsigned blocks = (unsigned)(n_tiles < resident ? n_tiles : resident);
-    int al16 = ((((uintptr_t)d_u | (uintptr_t)d_s | (uintptr_t)d_e | (uintptr_t)d_f) & 15) == 0) ? 1 : 0;
-    if (getenv("TH_K2_DIRECT")) al16 = 0;
-    if (mode == TH_MODE_STRICT)
-        k2_bitmap_kernel<TH_MODE_STRICT><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m,
-                                                                        (const i64 *)d_u, (const i64 *)d_s,
-                                                                        (const i64 *)d_e, (const i64 *)d_f, al16,
-                                                                        (u32 *)d_bits);
-    else
-        k2_bitmap_kernel<TH_MODE_INCLUSIVE><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids,
-                                                                           m, (const i64 *)d_u, (const i64 *)d_s,
-                                                                           (const i64 *)d_e, (const i64 *)d_f, al16,
-                                                                           (u32 *)d_bits);
+    ThPeerOut none;
+    none.n = 0;
+    TH_TRY(k2_launch(h, m, d_u, d_s, d_e, d_f, mode, (u32 *)d_bits, none, st));
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_bits_u32, d_bits, 4 * words, mem, st));
     if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
@@ -521,5 +563,74 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_TRY(th_copy_back(out_ids, d_ids, 8 * (size_t)total, mem, st));
     TH_TRY(th_copy_back(out_cancelled_u8, d_canc, (size_t)total, mem, st));
     TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+
+// Fused K2 + all-gather: every rank's kernel stores its bitmap words directly into the
+// gathered buffer of every rank (peer-mapped memory over NVLink/NVSwitch) and raises a per-rank flag when its last
+// CTA retires; a one-block wait kernel on the same stream then holds the stream until all ranks' flags for this
+// step have arrived.  No NCCL call, no host round trip.  Device pointers only.
+extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
+                                           const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id,
+                                           int mode, int wait, uint32_t **out_gathered, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_conflict_bitmap_exchange: snapshot not loaded");
+    TH_REQUIRE(peer != nullptr && peer->connected, "th_conflict_bitmap_exchange: peer group not connected");
+    TH_REQUIRE(peer->device == h->device, "th_conflict_bitmap_exchange: peer group and snapshot are on different devices");
+    TH_REQUIRE(m >= 0 && (m + 31) / 32 <= peer->words_per_rank,
+               "th_conflict_bitmap_exchange: %lld queries need %lld words, the peer group was created for %lld per rank",
+               (long long)m, (long long)((m + 31) / 32), (long long)peer->words_per_rank);
+    TH_REQUIRE(mode == TH_MODE_STRICT || mode == TH_MODE_INCLUSIVE, "th_conflict_bitmap_exchange: mode %d not supported", mode);
+    TH_REQUIRE(m == 0 || (q_uuid && q_start && q_end), "th_conflict_bitmap_exchange: NULL array");
+    TH_REQUIRE(mode != TH_MODE_STRICT || m == 0 || q_self_id, "th_conflict_bitmap_exchange: q_self_id is NULL");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_conflict_bitmap_exchange: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const u32 epoch = ++peer->epoch;
+    const int parity = (int)(epoch & 1u);
+    const int world = peer->world;
+    const i64 wpr = peer->words_per_rank;
+    ThPeerOut po;
+    po.n = world; po.rank = peer->rank; po.epoch = epoch;
+    po.word_off = (i64)peer->rank * wpr;
+    for (int p = 0; p < world; ++p) {
+        po.dst[p] = th_peer_words(peer->peer_base[p], world, wpr, parity);
+        po.flags[p] = th_peer_flags(peer->peer_base[p], world, wpr);
+    }
+    u32 *local_flags = th_peer_flags(peer->base, world, wpr);
+    po.done = local_flags + world;
+    int *err = (int *)(local_flags + world + 1);
+    TH_TRY(k2_launch(h, m, q_uuid, q_start, q_end, q_self_id, mode, nullptr, po, st));
+    if (wait) {
+        k2_wait_flags_kernel<<<1, 32, 0, st>>>(local_flags, world, epoch, err);
+        TH_CUDA(cudaGetLastError());
+    }
+    if (out_gathered) *out_gathered = th_peer_words(peer->base, world, wpr, parity);
+    return TH_OK;
+}
+
+// the wait half on its own (for th_conflict_bitmap_exchange(wait = 0)): holds `stream` until every rank's words
+// of the latest step have arrived
+extern "C" int th_peer_wait(th_peer *peer, void *stream) {
+    TH_REQUIRE(peer != nullptr && peer->connected, "th_peer_wait: peer group not connected");
+    int prev = 0;
+    TH_CUDA(cudaGetDevice(&prev));
+    if (prev != peer->device) TH_CUDA(cudaSetDevice(peer->device));
+    u32 *local_flags = th_peer_flags(peer->base, peer->world, peer->words_per_rank);
+    k2_wait_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(local_flags, peer->world, peer->epoch,
+                                                           (int *)(local_flags + peer->world + 1));
+    cudaError_t e = cudaGetLastError();
+    if (prev != peer->device) cudaSetDevice(prev);
+    if (e != cudaSuccess) { th_set_error("th_peer_wait: launch -> %s", cudaGetErrorString(e)); return TH_ECUDA; }
+    return TH_OK;
+}
+
+extern "C" int th_peer_check(th_peer *peer, void *stream) {
+    TH_REQUIRE(peer != nullptr && peer->base, "th_peer_check: peer group not created");
+    int e = 0;
+    u32 *local_flags = th_peer_flags(peer->base, peer->world, peer->words_per_rank);
+    TH_CUDA(cudaMemcpyAsync(&e, local_flags + peer->world + 1, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TH_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    if (e) { th_set_error("th_peer_check: a rank's words did not arrive within the wait kernel's bound"); return TH_EINTERNAL; }
     return TH_OK;
 }

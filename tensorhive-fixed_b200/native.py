@@ -37,6 +37,13 @@ SIGNATURES = {
     'th_violation_join_static': (_int, [_vp, _i64, _int, _i64, _vp, _vp, _vp, _vp, _vp]),
     'th_usage_reduce': (_int, [_int, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                _int, _vp]),
+    'th_peer_create': (_int, [_int, _int, _int, _i64, C.POINTER(_vp), _vp]),
+    'th_peer_connect': (_int, [_vp, _vp, _vp]),
+    'th_peer_local_base': (_int, [_vp, C.POINTER(_vp)]),
+    'th_peer_destroy': (_int, [_vp]),
+    'th_peer_check': (_int, [_vp, _vp]),
+    'th_conflict_bitmap_exchange': (_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _int, _int, C.POINTER(_vp), _vp]),
+    'th_peer_wait': (_int, [_vp, _vp]),
     'th_sort_pairs': (_int, [_int, _i64, _vp, _vp, _vp, _int, _vp]),
     'th_synth_samples': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp]),
     'th_synth_windows': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp]),

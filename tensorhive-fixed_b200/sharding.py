@@ -120,3 +120,87 @@ def shard_rows(cal: dict, bounds: np.ndarray, rank: int) -> dict:
     out['uuid_id'] = out['uuid_id'] - lo
     out['n_uuids'] = max(hi - lo, 1)
     return out
+
+
+class _DevWords:
+    """Library-owned device memory exposed through __cuda_array_interface__ (so torch/cupy can view it)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {'shape': (int(n),), 'typestr': '<i4', 'data': (int(ptr), False), 'version': 2}
+
+
+class PeerExchange:
+    """K2 fused with the all-gather of its bitmap words over peer memory (NVLink / NVSwitch), one process per GPU.
+
+    Every rank creates its gathered-words buffer inside the library, the 64-byte CUDA IPC handles are exchanged once
+    through ``torch.distributed.all_gather_object`` (plumbing), and from then on a step is ONE call:
+    ``words = px.conflict_words(snapshot, q_uuid, q_start, q_end, q_self)`` -- the kernel writes each rank's words
+    into every rank's buffer and the stream resumes when all of them have arrived.  No NCCL call per step.
+    """
+
+    def __init__(self, device: int, world: int, rank: int, max_queries_per_rank: int, connect: bool = True):
+        import ctypes as C
+        from . import native
+        self._C, self._native = C, native
+        self._lib = native.load()
+        self.device, self.world, self.rank = int(device), int(world), int(rank)
+        self.words_per_rank = (int(max_queries_per_rank) + 31) // 32
+        self._h = C.c_void_p(0)
+        self._views = {}
+        self.handle = C.create_string_buffer(64)
+        native.check(self._lib.th_peer_create(self.device, self.world, self.rank, self.words_per_rank,
+                                              C.byref(self._h), self.handle))
+        if connect:
+            self.connect_over_process_group()
+
+    def connect_over_process_group(self):
+        import torch.distributed as dist
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(self.handle.raw))
+        blob = self._C.create_string_buffer(b''.join(handles), 64 * self.world)
+        self._native.check(self._lib.th_peer_connect(self._h, blob, None))
+        dist.barrier()
+
+    def local_base(self) -> int:
+        p = self._C.c_void_p(0)
+        self._native.check(self._lib.th_peer_local_base(self._h, self._C.byref(p)))
+        return int(p.value)
+
+    def connect_local(self, bases):
+        """Single-process emulation: ``bases[r]`` = local_base() of the PeerExchange playing rank r."""
+        arr = (self._C.c_void_p * self.world)(*[self._C.c_void_p(int(b)) for b in bases])
+        self._native.check(self._lib.th_peer_connect(self._h, None, arr))
+
+    def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True):
+        """CUDA int64 tensors in; returns an int32 CUDA tensor view [world, words_per_rank] of the gathered words
+        (rank r's words for its own m queries sit in row r)."""
+        import torch
+        C = self._C
+        m = int(q_uuid.numel())
+        out = C.c_void_p(0)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._native.check(self._lib.th_conflict_bitmap_exchange(
+            snapshot._h, self._h, m, C.c_void_p(q_uuid.data_ptr()), C.c_void_p(q_start.data_ptr()),
+            C.c_void_p(q_end.data_ptr()), C.c_void_p(q_self.data_ptr()) if q_self is not None else None, int(mode),
+            1 if wait else 0, C.byref(out), stream))
+        view = self._views.get(out.value)          # two generations -> two cached views
+        if view is None:
+            view = torch.as_tensor(_DevWords(out.value, self.world * self.words_per_rank),
+                                   device='cuda:%d' % self.device).view(self.world, self.words_per_rank)
+            self._views[out.value] = view
+        return view
+
+    def wait(self):
+        import torch
+        stream = self._C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._native.check(self._lib.th_peer_wait(self._h, stream))
+
+    def check(self):
+        import torch
+        stream = self._C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._native.check(self._lib.th_peer_check(self._h, stream))
+
+    def close(self):
+        if self._h:
+            self._lib.th_peer_destroy(self._h)
+            self._h = self._C.c_void_p(0)

@@ -391,3 +391,51 @@ def test_config2_full_size_bit_exact(th, synth, brute):
     shr = snap.conflict_bitmap(q['uuid_id'][free], q['start'][free] + 1, q['end'][free] - 1, q['self_id'][free])
     assert not shr.any()
     snap.close()
+
+
+# ---- fused K2 + exchange, two ranks emulated on one GPU --------------------------------------------------------------
+def test_fused_exchange_two_ranks_emulated_on_one_gpu(th, synth, brute):
+    """Both ranks live in this process on cuda:0; the kernels are enqueued first (wait = 0) and the wait halves
+    afterwards, on ONE stream, so no kernel ever waits for one that has not been launched."""
+    import torch
+    from tensorhive_fixed_b200 import sharding
+    from tensorhive_fixed_b200.api import unpack_bits
+    dev = torch.device('cuda:0')
+    cal = synth.make_calendar(120_000, 300, seed=55, skew=0.5)
+    bounds = sharding.partition_uuids(np.bincount(cal['uuid_id'], minlength=300), 2)
+    shards = [sharding.shard_rows(cal, bounds, r) for r in range(2)]
+    snaps = []
+    for s in shards:
+        snap = th.Snapshot(0)
+        snap.load(s['id'], s['uuid_id'], s['start'], s['end'], s['owner'], s['cancelled'], n_uuids=s['n_uuids'])
+        snaps.append(snap)
+    px = [sharding.PeerExchange(0, 2, r, max_queries_per_rank=50_000, connect=False) for r in range(2)]
+    bases = [p.local_base() for p in px]
+    for p in px:
+        p.connect_local(bases)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for step in range(3):            # three steps: both buffer generations are reused
+        q = synth.make_queries(cal, 60_000 + 1000 * step, seed=900 + step)
+        router = sharding.Router(q['uuid_id'], bounds)
+        views, counts = [], []
+        for r in range(2):
+            idx = router.local_indices(r)
+            counts.append(idx.size)
+            views.append(px[r].conflict_words(snaps[r], t(router.local_uuid(q['uuid_id'], r)), t(q['start'][idx]),
+                                              t(q['end'][idx]), t(q['self_id'][idx]), wait=False))
+        for r in range(2):
+            px[r].wait()
+        torch.cuda.synchronize()
+        for r in range(2):
+            px[r].check()
+        want = brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])
+        for r in range(2):           # every rank ends up with everybody's words
+            got = np.zeros(len(want), bool)
+            g = views[r].cpu().numpy().view(np.uint32)
+            for src in range(2):
+                got[router.local_indices(src)] = unpack_bits(g[src], counts[src])
+            assert np.array_equal(got, want), (step, r)
+    for p in px:
+        p.close()
+    for s in snaps:
+        s.close()

@@ -36,6 +36,21 @@ def main():
                                            lambda w: sharding.torch_all_gather(w, 'cuda:%d' % local))
     want = brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])
     ok = bool(np.array_equal(got, want))
+    # the same batch through the fused kernel: K2 stores its words into every rank's buffer over NVLink
+    router = sharding.Router(q['uuid_id'], bounds)
+    px = sharding.PeerExchange(local, world, rank, int(router.counts.max()))
+    dev = 'cuda:%d' % local
+    idx = router.local_indices(rank)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    qd = [t(router.local_uuid(q['uuid_id'], rank)), t(q['start'][idx]), t(q['end'][idx]), t(q['self_id'][idx])]
+    for step in range(4):
+        g = px.conflict_words(snap, *qd)
+        torch.cuda.synchronize()
+        px.check()
+        fused = router.decode(g.cpu().numpy())
+        ok = ok and bool(np.array_equal(fused, want))
+    dist.barrier()
+    px.close()
     flag = torch.tensor([1 if ok else 0], device='cuda:%d' % local)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
