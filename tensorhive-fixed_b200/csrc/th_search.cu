@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             qs = th_ld_stream(&q_start[ic]);
             self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
         }
-        cell = th_ld16(k2_cell_of(g, n_uuids, u, qe));
+        cell = th_ld16_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, make_longlong2(0, 0));   // no uuids: no grid
     };
 
     if (lane == 0) {
@@ -179,9 +179,10 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             if (t < full_tiles) issue(t, st);
         }
     }
-    // Measured on B200 (tools/k2_sweep.py): issuing the cell of tile k + 1 before the rows of tile k did not pay
-    // (26.6 us vs 24.5 us cold at 1 M queries) -- with 32 resident warps per SM the kernel is bound by issue
-    // slots and effective DRAM rate, not by the two-deep dependency -- so each tile runs levels 2 and 3 in turn.
+    // Measured on B200 (tools/k2_sweep.py): requesting the cell of tile k + 1 before the rows of tile k did not pay,
+    // neither in plain C++ (ptxas sinks the prefetch again: 26.6 us vs 24.5 us cold at 1 M queries) nor as ordered
+    // volatile PTX (24.8 us; 264 us vs 217 us at 16 M queries).  At ~320 warp instructions per 32 queries the kernel
+    // is bound by issue slots, and the pipelined loop adds instructions; so each tile runs levels 2 and 3 in turn.
     u32 it = 0;
     for (i64 tile = gw; tile < tiles; tile += nw, ++it) {
         i64 u, qs, qe, self;
