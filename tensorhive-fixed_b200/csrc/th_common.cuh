@@ -147,8 +147,17 @@ __device__ __forceinline__ longlong2 th_ld16_if(const void *p, bool pred, longlo
     return v;
 }
 
-// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS UBLKCP) ---------------------
 __device__ __forceinline__ u32 th_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+
+// ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass registers, grouped for multi-stage rings -----
+__device__ __forceinline__ void th_cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(th_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void th_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void th_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS UBLKCP) ---------------------
 __device__ __forceinline__ void th_mbar_init(unsigned long long *bar, u32 count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(th_smem_addr(bar)), "r"(count));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

@@ -51,9 +51,10 @@ constexpr int BM_THREADS = 256;
 // requests, and (2) every DEPENDENT round trip to L2/HBM adds ~1 us to the warp, whose latency is the maximum
 // over its lanes.  So the lookup is three levels deep, each level issued for all lanes at once with
 // predicated (not looped, not short-circuited) loads, and level 1 runs several tiles ahead:
-//   level 1  a warp tile = 32 queries x 4 columns (1 KB) arrives in shared memory by four TMA bulk copies
-//            (cp.async.bulk -> UBLKCP) issued by lane 0 into a 4-stage ring with one mbarrier per stage;
-//            warps never synchronise with each other;
+//   level 1  a warp tile = 32 queries x 4 columns (1 KB) is staged in shared memory by coalesced 16-byte
+//            cp.async copies (two per lane) into a per-warp 4-stage ring; warps never synchronise with each
+//            other.  (TMA bulk copies, one mbarrier per stage, were measured too: same latency hiding but ~80
+//            more warp instructions per tile for issue + barrier handling, and the kernel is issue bound);
 //   level 2  ONE 16-byte grid cell {pos, cnt, m1_before}.  m1 only grows along a segment, so if the rows
 //            before the bucket already end after qs the verdict is "conflict" and level 3 is skipped;
 //   level 3  the first four 16-byte {start, m1} rows of the bucket (a bucket holds ~1 row on average) and,
@@ -126,36 +127,39 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     const i64 *__restrict__ q_uuid, const i64 *__restrict__ q_start, const i64 *__restrict__ q_end,
     const i64 *__restrict__ q_self, int cols_aligned16, u32 *__restrict__ out_bits, ThPeerOut po) {
     __shared__ __align__(128) i64 sq[BM_WARPS][BM_STAGES][4][32];
-    __shared__ __align__(8) unsigned long long bar[BM_WARPS][BM_STAGES];
-    constexpr u32 COL = 32 * sizeof(i64);
-    constexpr u32 NCOL = MODE == TH_MODE_STRICT ? 4 : 3;
+    constexpr int NCOL = MODE == TH_MODE_STRICT ? 4 : 3;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const i64 full_tiles = cols_aligned16 ? m / 32 : 0;      // warp tiles that go through TMA
+    const i64 full_tiles = cols_aligned16 ? m / 32 : 0;      // warp tiles that are staged through shared memory
     const i64 tiles = (m + 31) / 32;
     const i64 gw = (i64)blockIdx.x * BM_WARPS + warp;
     const i64 nw = (i64)gridDim.x * BM_WARPS;
 
-    auto issue = [&](i64 tile, int st) {   // lane 0: arm the stage's barrier, start its bulk copies
-        const i64 base = tile * 32;
-        th_mbar_expect_tx(&bar[warp][st], NCOL * COL);
-        th_bulk_g2s(sq[warp][st][0], q_uuid + base, COL, &bar[warp][st]);
-        th_bulk_g2s(sq[warp][st][1], q_end + base, COL, &bar[warp][st]);
-        th_bulk_g2s(sq[warp][st][2], q_start + base, COL, &bar[warp][st]);
-        if (MODE == TH_MODE_STRICT) th_bulk_g2s(sq[warp][st][3], q_self + base, COL, &bar[warp][st]);
+    // level 1: a warp tile (32 queries x 4 columns = 1 KB = 64 chunks of 16 bytes) is staged with two cp.async per
+    // lane -- coalesced, 16 bytes each, no registers -- into a per-warp 4-stage ring; one commit group per tile, and
+    // an (empty) group is committed even when there is nothing left to prefetch so that "all but the newest
+    // BM_STAGES - 1 groups have landed" always means "this tile has landed".
+    auto stage_in = [&](i64 tile, int st) {
+        if (tile < full_tiles) {
+            const i64 base = tile * 32;
+#pragma unroll
+            for (int c = lane; c < NCOL * 16; c += 32) {
+                const int col = c >> 4, off = (c & 15) * 2;      // 16 chunks per column, 2 elements per chunk
+                const i64 *src = (col == 0 ? q_uuid : col == 1 ? q_end : col == 2 ? q_start : q_self) + base + off;
+                th_cp_async16(&sq[warp][st][col][off], src);
+            }
+        }
+        th_cp_async_commit();
     };
-    // levels 1 + 2 of one tile: query columns out of the ring (or straight from global for the ragged tail),
-    // then the grid cell
     auto fetch = [&](i64 tile, u32 it, i64 &u, i64 &qs, i64 &qe, i64 &self, longlong2 &cell) {
         const int st = it % BM_STAGES;
         if (tile < full_tiles) {
-            th_mbar_wait(&bar[warp][st], (it / BM_STAGES) & 1);
+            th_cp_async_wait<BM_STAGES - 1>();
+            __syncwarp();                                   // the other lanes' chunks are visible too
             u = sq[warp][st][0][lane];
             qe = sq[warp][st][1][lane];
             qs = sq[warp][st][2][lane];
             self = MODE == TH_MODE_STRICT ? sq[warp][st][3][lane] : -1;
             __syncwarp();                                   // every lane has read the stage: refill it
-            const i64 refill = tile + (i64)BM_STAGES * nw;
-            if (lane == 0 && refill < full_tiles) { th_fence_proxy_async(); issue(refill, st); }
         } else {   // ragged last tile or unaligned caller buffers
             const i64 i = tile * 32 + lane;
             const i64 ic = i < m ? i : m - 1;
@@ -164,21 +168,12 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             qs = th_ld_stream(&q_start[ic]);
             self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
         }
+        stage_in(tile + (i64)BM_STAGES * nw, st);
         cell = th_ld16_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, make_longlong2(0, 0));   // no uuids: no grid
     };
 
-    if (lane == 0) {
 #pragma unroll
-        for (int st = 0; st < BM_STAGES; ++st) th_mbar_init(&bar[warp][st], 1);
-    }
-    __syncwarp();
-    if (lane == 0) {
-#pragma unroll
-        for (int st = 0; st < BM_STAGES; ++st) {
-            const i64 t = gw + (i64)st * nw;
-            if (t < full_tiles) issue(t, st);
-        }
-    }
+    for (int st = 0; st < BM_STAGES; ++st) stage_in(gw + (i64)st * nw, st);
     // Measured on B200 (tools/k2_sweep.py): requesting the cell of tile k + 1 before the rows of tile k did not pay,
     // neither in plain C++ (ptxas sinks the prefetch again: 26.6 us vs 24.5 us cold at 1 M queries) nor as ordered
     // volatile PTX (24.8 us; 264 us vs 217 us at 16 M queries).  At ~320 warp instructions per 32 queries the kernel
