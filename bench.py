@@ -387,6 +387,10 @@ def run_ours(args):
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
                               'radix_passes': info['radix_passes'], 'device_bytes': info['device_bytes']}}
 
+    # ---- BASELINE config 4: ProtectionService + job-queue sweep over the same calendar ---------------------------
+    if not args.skip_sweep:
+        line['service_sweep'] = bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak)
+
     # ---- K4 on BASELINE config 3, generated on the device -------------------------------------------------------
     if not args.skip_usage:
         line['usage_reduce'] = bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup, barrier,
@@ -404,6 +408,54 @@ def run_ours(args):
     snap.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
+    """BASELINE configs[3]: 1M live GPU processes joined against the current reservation owners (K3 + K5,
+    ProtectionService.py:84-102) and 100k queued jobs' tasks tested against upcoming reservations (K5,
+    JobSchedulingService.py:117-132), device-resident inputs, cold L2, median of 10."""
+    from tensorhive_fixed_b200 import synth
+    now = int(np.median(cal['start']))
+    period = 30 * synth.MIN_US
+    procs = synth.make_processes(cal, 1_000_000, now, seed=SEED + 7)
+    tasks = synth.make_job_tasks(cal, 100_000, seed=SEED + 8)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    pu, po = t(procs['uuid_id']), t(procs['owner'])
+    tu, to = t(tasks['uuid_id']), t(tasks['owner'])
+    P, T, U, N = int(pu.numel()), int(tu.numel()), N_UUIDS, N_ROWS
+    flags = torch.empty(P, dtype=torch.uint8, device=dev)
+    res = torch.empty(P, dtype=torch.int64, device=dev)
+    tflags = torch.empty(T, dtype=torch.uint8, device=dev)
+    uu = torch.arange(U, dtype=torch.int64, device=dev)
+    up = [torch.empty(U, dtype=torch.int64, device=dev) for _ in range(4)]
+
+    def med(fn):
+        for _ in range(3):
+            fn()
+        ev = []
+        for _ in range(10):
+            flush.sum()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream); fn(); b.record(stream)
+            ev.append((a, b))
+        torch.cuda.synchronize()
+        return float(np.median([a.elapsed_time(b) for a, b in ev]))
+
+    ms_join = med(lambda: native.check(lib.th_violation_join(snap._h, now, 0, P, pu.data_ptr(), po.data_ptr(),
+                                                             flags.data_ptr(), res.data_ptr(), 1, sp)))
+    ms_task = med(lambda: native.check(lib.th_upcoming_owner_flags(snap._h, now, period, T, tu.data_ptr(), to.data_ptr(),
+                                                                   1, tflags.data_ptr(), 1, sp)))
+    ms_up = med(lambda: native.check(lib.th_upcoming(snap._h, now, period, U, uu.data_ptr(), up[0].data_ptr(),
+                                                     up[1].data_ptr(), up[2].data_ptr(), up[3].data_ptr(), 1, sp)))
+    torch.cuda.synchronize()
+    join_bytes = P * 16 + P * 9 + U * 16          # SURVEY 8(d): the K5 join proper
+    return {'workload': 'BASELINE configs[3]: 1M GPU processes + 100k queued jobs (%d tasks) vs the config-2 calendar' % T,
+            'violation_join': {'ms': ms_join, 'processes_per_s': P / (ms_join * 1e-3), 'violations': int(flags.sum().item()),
+                               'algorithmic_bytes': join_bytes, 'achieved_GBs': join_bytes / (ms_join * 1e-3) / 1e9,
+                               'frac_of_peak': join_bytes / (ms_join * 1e-3) / 1e9 / peak,
+                               'note': 'two launches: K3 current-owner table over %d uuids, then the K5 join' % U},
+            'job_tasks': {'ms': ms_task, 'tasks_per_s': T / (ms_task * 1e-3), 'interfering': int(tflags.sum().item())},
+            'gpu_slots': {'ms': ms_up, 'uuids_per_s': U / (ms_up * 1e-3)}}
 
 
 def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup, barrier, max_over_ranks, world, peak,
@@ -459,6 +511,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--skip-usage', action='store_true', help='skip the config-3 usage-reduce measurement')
+    ap.add_argument('--skip-sweep', action='store_true', help='skip the config-4 service sweep measurement')
     ap.add_argument('--skip-cpu', action='store_true', help='skip the single-core CPU baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -191,6 +191,29 @@ __device__ __forceinline__ void th_mbar_wait(unsigned long long *bar, u32 phase)
 __device__ __forceinline__ i64 th_idc_id(i64 idc) { return idc & TH_I64_MAX; }
 __device__ __forceinline__ bool th_idc_cancelled(i64 idc) { return idc < 0; }
 
+// End of the prefix "rows of uuid u that start before `key`" (STRICT: start < key, else start <= key) as an absolute
+// position, found through the time grid: one 16-byte cell, then a search over that bucket's rows only (rows of
+// earlier buckets start before the bucket and hence before key, rows of later buckets after it).  The result is
+// at least seg[u] + 1 because the sentinel (start = -inf) sits in bucket 0.  u must be a valid uuid.
+template <bool STRICT>
+__device__ __forceinline__ int th_grid_prefix_end(const ThGrid &g, const ThP1 *__restrict__ p1, i64 u, i64 key) {
+    i64 b = 0;
+    if (key > g.t0) {
+        const u64 d = ((u64)key - (u64)g.t0) >> g.shift;
+        b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
+    }
+    const longlong2 c = th_ld16(&g.cells[u * g.nb + b]);
+    int lo = (int)(c.x & 0xffffffffll);
+    int hi = lo + (int)(c.x >> 32);
+    while (lo < hi) {
+        const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+        const i64 s = __ldg(&p1[mid].start);
+        const bool left = STRICT ? (s < key) : (s <= key);
+        if (left) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 __device__ __forceinline__ i64 th_warp_min(i64 v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

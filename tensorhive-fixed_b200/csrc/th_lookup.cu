@@ -7,7 +7,7 @@
 //                                                 JobSchedulingService.py:94-102,117-132 and scheduling.py:48-53
 //   ProtectionService.do_run join                 ProtectionService.py:84-102
 //
-// One warp per uuid / task: a warp-uniform binary search finds the end of the candidate prefix, then the
+// One warp per uuid / task: the time grid gives the end of the candidate prefix in two probes, then the
 // warp walks backwards 32 rows per step with 16-byte loads until the running maximum of non-cancelled
 // `end` (m1) proves nothing earlier can still be current.
 #include "th_common.cuh"
@@ -28,21 +28,11 @@ struct DeviceGuard {
 constexpr int LK_THREADS = 256;
 constexpr int LK_WARPS = LK_THREADS / 32;
 
-template <bool STRICT>
-__device__ __forceinline__ int lk_prefix_end(const ThP1 *__restrict__ p1, int lo, int hi, i64 key) {
-    while (lo < hi) {
-        const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-        const i64 s = __ldg(&p1[mid].start);
-        const bool left = STRICT ? (s < key) : (s <= key);
-        if (left) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
 // lowest-id non-cancelled row of segment [lo, hi) with start <= now <= end; returns row index or -1 (all lanes)
-__device__ __forceinline__ int lk_current_row(const ThP1 *__restrict__ p1, const ThP3 *__restrict__ p3, int lo, int hi,
-                                              i64 now, int lane, i64 *best_id_out) {
-    int c1 = lk_prefix_end<false>(p1, lo, hi, now);   // rows with start <= now
+__device__ __forceinline__ int lk_current_row(const ThGrid &g, i64 u, const ThP1 *__restrict__ p1,
+                                              const ThP3 *__restrict__ p3, int lo, i64 now, int lane,
+                                              i64 *best_id_out) {
+    int c1 = th_grid_prefix_end<false>(g, p1, u, now);   // rows with start <= now
     i64 best_id = TH_I64_MAX;
     int best_row = -1;
     while (c1 > lo && __ldg(&p1[c1 - 1].m1) >= now) {
@@ -65,7 +55,7 @@ __device__ __forceinline__ int lk_current_row(const ThP1 *__restrict__ p1, const
     return row;
 }
 
-__global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+__global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(ThGrid g, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
                                                                 const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
                                                                 i64 n_uuids, i64 now, i64 *__restrict__ out_res,
                                                                 i64 *__restrict__ out_owner) {
@@ -73,7 +63,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(const int *__res
     const i64 wstride = (i64)gridDim.x * LK_WARPS;
     for (i64 u = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); u < n_uuids; u += wstride) {
         i64 id;
-        const int row = lk_current_row(p1, p3, seg[u] + 1, seg[u + 1], now, lane, &id);   // seg[u] = sentinel
+        const int row = lk_current_row(g, u, p1, p3, seg[u] + 1, now, lane, &id);   // seg[u] = sentinel
         if (lane == 0) {
             out_res[u] = row >= 0 ? id : -1;
             out_owner[u] = row >= 0 ? __ldg(&p4[row].owner) : -1;
@@ -92,12 +82,12 @@ struct UpAcc {
 };
 
 template <bool WANT_OWNER>
-__device__ __forceinline__ UpAcc lk_upcoming(const ThP1 *__restrict__ p1, const ThP3 *__restrict__ p3,
-                                             const ThP4 *__restrict__ p4, int lo, int hi, i64 now, i64 later, int lane,
-                                             int test, i64 owner) {
+__device__ __forceinline__ UpAcc lk_upcoming(const ThGrid &g, i64 u, const ThP1 *__restrict__ p1,
+                                             const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4, int lo, i64 now,
+                                             i64 later, int lane, int test, i64 owner) {
     UpAcc a;
     a.count = 0; a.first_row = 0x7fffffff; a.owner_hit = 0;
-    int c1 = lk_prefix_end<false>(p1, lo, hi, later);   // rows with start <= now + period
+    int c1 = th_grid_prefix_end<false>(g, p1, u, later);   // rows with start <= now + period
     while (c1 > lo) {
         const longlong2 top = th_ld16(&p1[c1 - 1]);     // {start, m1}
         if (!(top.x >= now || top.y > now)) break;     // earlier rows start before now and none is still running
@@ -125,7 +115,7 @@ __device__ __forceinline__ UpAcc lk_upcoming(const ThP1 *__restrict__ p1, const 
     return a;
 }
 
-__global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+__global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(ThGrid g, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
                                                                  const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
                                                                  i64 n_uuids, i64 now, i64 later, i64 k,
                                                                  const i64 *__restrict__ uuids, i64 *__restrict__ o_id,
@@ -137,7 +127,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(const int *__re
         const i64 u = uuids[q];
         UpAcc a;
         a.count = 0; a.first_row = 0; a.owner_hit = 0;
-        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(p1, p3, p4, seg[u] + 1, seg[u + 1], now, later, lane, 0, 0);
+        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(g, u, p1, p3, p4, seg[u] + 1, now, later, lane, 0, 0);
         if (lane == 0) {
             if (a.count > 0) {
                 const int r = a.first_row;
@@ -152,7 +142,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(const int *__re
     }
 }
 
-__global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+__global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(ThGrid g, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
                                                                     const ThP3 *__restrict__ p3,
                                                                     const ThP4 *__restrict__ p4, i64 n_uuids, i64 now,
                                                                     i64 later, i64 t, const i64 *__restrict__ task_uuid,
@@ -164,7 +154,7 @@ __global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(const int *_
         const i64 u = task_uuid[q];
         int flag = 0;
         if (u >= 0 && u < n_uuids) {
-            const UpAcc a = lk_upcoming<true>(p1, p3, p4, seg[u] + 1, seg[u + 1], now, later, lane, test, task_owner[q]);
+            const UpAcc a = lk_upcoming<true>(g, u, p1, p3, p4, seg[u] + 1, now, later, lane, test, task_owner[q]);
             flag = a.owner_hit;
         }
         if (lane == 0) out_flag[q] = (u8)flag;
@@ -210,7 +200,7 @@ extern "C" int th_current_owner(const th_snapshot *h, int64_t now_us, int64_t *o
     void *d_res, *d_own;
     TH_TRY(sc.out(out_res_id, 8 * zu, mem, &d_res));
     TH_TRY(sc.out(out_owner, 8 * zu, mem, &d_own));
-    k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids,
+    k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids,
                                                                                     now_us, (i64 *)d_res, (i64 *)d_own);
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_res_id, d_res, 8 * zu, mem, st));
@@ -239,7 +229,7 @@ extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_
     TH_TRY(sc.out(out_first_start, 8 * zk, mem, &d_s));
     TH_TRY(sc.out(out_first_owner, 8 * zk, mem, &d_o));
     TH_TRY(sc.out(out_count, 8 * zk, mem, &d_c));
-    k3_upcoming_kernel<<<th_grid_for(k, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+    k3_upcoming_kernel<<<th_grid_for(k, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
                                                                             now_us + period_us, k, (const i64 *)d_u,
                                                                             (i64 *)d_id, (i64 *)d_s, (i64 *)d_o, (i64 *)d_c);
     TH_CUDA(cudaGetLastError());
@@ -270,7 +260,7 @@ extern "C" int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int
     TH_TRY(sc.in(task_uuid, 8 * zt, mem, &d_u));
     TH_TRY(sc.in(task_owner, 8 * zt, mem, &d_o));
     TH_TRY(sc.out(out_flag_u8, zt, mem, &d_f));
-    k5_owner_flags_kernel<<<th_grid_for(t, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+    k5_owner_flags_kernel<<<th_grid_for(t, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
                                                                                now_us + period_us, t, (const i64 *)d_u,
                                                                                (const i64 *)d_o, test, (u8 *)d_f);
     TH_CUDA(cudaGetLastError());
@@ -297,7 +287,7 @@ extern "C" int th_violation_join(const th_snapshot *h, int64_t now_us, int stric
     TH_TRY(sc.alloc((void **)&cur_res, 8 * (zu ? zu : 1)));
     TH_TRY(sc.alloc((void **)&cur_owner, 8 * (zu ? zu : 1)));
     if (h->n_uuids > 0) {
-        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4,
+        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4,
                                                                                         h->n_uuids, now_us, cur_res,
                                                                                         cur_owner);
     }
@@ -388,7 +378,7 @@ extern "C" int th_violation_join_static(const th_snapshot *h, int64_t now_us, in
     i64 *cur_res = table, *cur_owner = table + TH_STATIC_JOIN_MAX_UUIDS;
     cudaStream_t st = (cudaStream_t)stream;
     if (h->n_uuids > 0) {
-        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(h->seg, h->p1, h->p3, h->p4,
+        k3_current_kernel<<<th_grid_for(h->n_uuids, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4,
                                                                                         h->n_uuids, now_us, cur_res,
                                                                                         cur_owner);
     }

@@ -29,18 +29,6 @@ struct DeviceGuard {
     ~DeviceGuard() { cudaSetDevice(prev); }
 };
 
-// number of rows in [lo, hi) with start < key (strict) or start <= key (!strict)
-template <bool STRICT>
-__device__ __forceinline__ int th_prefix_end(const ThP1 *__restrict__ p1, int lo, int hi, i64 key) {
-    while (lo < hi) {
-        const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-        const i64 s = __ldg(&p1[mid].start);
-        const bool left = STRICT ? (s < key) : (s <= key);
-        if (left) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
 constexpr int BM_THREADS = 256;
 #ifndef BM_MIN_BLOCKS
 #define BM_MIN_BLOCKS 4
@@ -228,7 +216,7 @@ constexpr int CS_THREADS = 256;
 constexpr int CS_WARPS = CS_THREADS / 32;
 
 struct RowView {
-    const int *seg; const ThP1 *p1; const ThP3 *p3; const ThP4 *p4;
+    const int *seg; const ThP1 *p1; const ThP3 *p3; const ThP4 *p4; ThGrid g;
 };
 
 // does row j belong to the result list of (qs, qe, self) under `mode`?
@@ -259,11 +247,11 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
         const i64 u = q_uuid[q];
         int cnt = 0, beg = 0, pend = 0;
         if (u >= 0 && u < n_uuids) {
-            const int lo = v.seg[u] + 1, hi = v.seg[u + 1];   // position seg[u] is the sentinel
+            const int lo = v.seg[u] + 1;   // position seg[u] is the sentinel
             const i64 qs = q_start[q], qe = q_end[q];
             const i64 self = q_self ? q_self[q] : -1;
-            pend = (mode == TH_MODE_STRICT) ? th_prefix_end<true>(v.p1, lo, hi, qe)
-                                            : th_prefix_end<false>(v.p1, lo, hi, qe);
+            pend = (mode == TH_MODE_STRICT) ? th_grid_prefix_end<true>(v.g, v.p1, u, qe)
+                                            : th_grid_prefix_end<false>(v.g, v.p1, u, qe);
             int c1 = pend;
             beg = pend;
             while (c1 > lo && cs_more(mode, v, c1, qs)) {
@@ -517,7 +505,7 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_TRY(sc.alloc((void **)&d_beg, 4 * zm));
     TH_TRY(sc.alloc((void **)&d_end, 4 * zm));
     RowView v;
-    v.seg = h->seg; v.p1 = h->p1; v.p3 = h->p3; v.p4 = h->p4;
+    v.seg = h->seg; v.p1 = h->p1; v.p3 = h->p3; v.p4 = h->p4; v.g = th_grid_of(h);
     const int wgrid = th_grid_for(m, CS_WARPS, 16);
     k2_sets_count_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
                                                        (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
