@@ -439,3 +439,15 @@ def test_fused_exchange_two_ranks_emulated_on_one_gpu(th, synth, brute):
         p.close()
     for s in snaps:
         s.close()
+
+
+def test_reloading_one_handle_reuses_or_regrows_its_buffers(th, synth, brute):
+    snap = th.Snapshot(0)
+    for n, u, seed in [(50_000, 64, 1), (3_000, 8, 2), (0, 4, 3), (80_000, 300, 4), (80_000, 300, 5)]:
+        cal = synth.make_calendar(n, u, seed=seed)
+        snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=u)
+        q = synth.make_queries(cal, 5000, seed=seed + 10)
+        got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+        assert np.array_equal(got, brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])), (n, u)
+        assert snap.info()['n'] == n
+    snap.close()
