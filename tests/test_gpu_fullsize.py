@@ -1,0 +1,101 @@
+"""BASELINE-size runs checked through size-independent properties and sampled brute force (the oracle cannot
+finish the full sizes): config 3 (1 B samples -> 10 M windows) and one rank's share of config 5 (12.5 M reservations,
+8192 uuids, 12.5 M candidates = the 100 M-reservation calendar on 8 GPUs)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_config3_full_size_usage_reduce(lib_built):
+    import torch
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import native, synth
+    lib = native.load()
+    free, _total = torch.cuda.mem_get_info(0)
+    if free < 40 << 30:
+        pytest.skip('needs ~26 GB of free device memory')
+    dev = torch.device('cuda:0')
+    U, SPU, W = 65_536, 15_259, 10_000_000
+    S = U * SPU
+    i64 = lambda n: torch.empty(n, dtype=torch.int64, device=dev)
+    off, ts, gpu, mem = i64(U + 1), i64(S), i64(S), i64(S)
+    wu, ws, we = i64(W), i64(W), i64(W)
+    sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    T0 = synth.T0_US
+    native.check(lib.th_synth_samples(0, U, SPU, T0, 11, off.data_ptr(), ts.data_ptr(), gpu.data_ptr(), mem.data_ptr(), sp))
+    native.check(lib.th_synth_windows(0, U, SPU, T0, 12, W, wu.data_ptr(), ws.data_ptr(), we.data_ptr(), sp))
+    sg, sm, cnt, ag, am = th.usage_reduce(off, ts, gpu, mem, wu, ws, we)
+    torch.cuda.synchronize()
+    # (1) counts of ALL windows from first principles: samples sit at T0 + k s, k in [0, SPU)
+    sec = 1_000_000
+    k_lo = torch.clamp(torch.div(ws - T0 + sec - 1, sec, rounding_mode='floor'), min=0)
+    k_hi = torch.clamp(torch.div(we - T0, sec, rounding_mode='floor'), max=SPU - 1)
+    want_cnt = torch.clamp(k_hi - k_lo + 1, min=0)
+    assert torch.equal(cnt, want_cnt)
+    assert int((cnt == 0).sum()) > 50_000 and int(cnt.max()) <= 200          # empty windows exist; U[20 s, 180 s]
+    # (2) averages of ALL windows: floor division, -1 when empty (UsageLoggingService.py:25-30)
+    safe = torch.clamp(cnt, min=1)
+    assert torch.equal(ag, torch.where(cnt > 0, torch.div(sg, safe, rounding_mode='floor'), torch.full_like(sg, -1)))
+    assert torch.equal(am, torch.where(cnt > 0, torch.div(sm, safe, rounding_mode='floor'), torch.full_like(sm, -1)))
+    # (3) sums: exact, for every window of 256 uuids spread over the table, via prefix sums of those uuids' samples
+    for u0 in (0, 20_000, U - 256):
+        sel = torch.nonzero((wu >= u0) & (wu < u0 + 256)).flatten()
+        assert sel.numel() > 10_000
+        a0 = u0 * SPU
+        cg = torch.cumsum(gpu[a0:a0 + 256 * SPU], 0)
+        cm = torch.cumsum(mem[a0:a0 + 256 * SPU], 0)
+        cg = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), cg])
+        cm = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), cm])
+        lo = (wu[sel] - u0) * SPU + k_lo[sel]
+        hi = (wu[sel] - u0) * SPU + k_hi[sel] + 1
+        hi = torch.maximum(hi, lo)
+        assert torch.equal(sg[sel], cg[hi] - cg[lo])
+        assert torch.equal(sm[sel], cm[hi] - cm[lo])
+    # (4) additivity: splitting a window at an arbitrary instant splits its sums and counts exactly
+    pick = torch.arange(0, W, 997, device=dev)
+    cut = ws[pick] + (we[pick] - ws[pick]) // 3
+    l = th.usage_reduce(off, ts, gpu, mem, wu[pick], ws[pick], cut)
+    r = th.usage_reduce(off, ts, gpu, mem, wu[pick], cut + 1, we[pick])
+    torch.cuda.synchronize()
+    assert torch.equal(l[0] + r[0], sg[pick]) and torch.equal(l[1] + r[1], sm[pick]) and torch.equal(l[2] + r[2], cnt[pick])
+
+
+def test_config5_one_rank_share(lib_built):
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    n, u, m = 12_500_000, 8192, 12_500_000
+    cal = synth.make_calendar(n, u, seed=20260105, skew=0.3)
+    q = synth.make_queries(cal, m, seed=20260106)
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=u)
+    got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    # sampled brute force: every query and row of 48 uuids (hot and cold ones)
+    counts = np.bincount(cal['uuid_id'], minlength=u)
+    order = np.argsort(-counts)
+    pick = np.concatenate([order[:8], order[u // 2:u // 2 + 32], order[-8:]])
+    rsel = np.isin(cal['uuid_id'], pick)
+    qsel = np.isin(q['uuid_id'], pick)
+    sub = {k: (v[rsel] if isinstance(v, np.ndarray) and len(v) == n else v) for k, v in cal.items()}
+    want = brute.conflict_bits(sub, q['uuid_id'][qsel], q['start'][qsel], q['end'][qsel], q['self_id'][qsel])
+    assert qsel.sum() > 50_000
+    assert np.array_equal(got[qsel], want)
+    # properties over the whole batch
+    live = np.nonzero(cal['cancelled'] == 0)[0][::5]
+    assert snap.conflict_bitmap(cal['uuid_id'][live], cal['start'][live], cal['end'][live],
+                                np.full(live.size, -1, np.int64)).all()              # a live row conflicts with its copy
+    free = np.nonzero(~got)[0]
+    assert not snap.conflict_bitmap(q['uuid_id'][free], q['start'][free] + 1, q['end'][free] - 1,
+                                    q['self_id'][free]).any()                         # shrinking never creates a conflict
+    unknown = q['uuid_id'] >= u
+    assert unknown.any() and not got[unknown].any()
+    # the same verdicts from the row lists: a conflict <=> some non-cancelled row in the STRICT list
+    some = np.nonzero(qsel)[0][:20_000]
+    off, ids, canc = snap.conflict_sets(q['uuid_id'][some], q['start'][some], q['end'][some], q['self_id'][some])
+    has_live = np.add.reduceat(np.concatenate([(np.asarray(canc) == 0).astype(np.int64), [0]]), np.asarray(off)[:-1]) > 0
+    has_live &= np.diff(np.asarray(off)) > 0
+    assert np.array_equal(has_live, got[some])
+    snap.close()
