@@ -195,7 +195,11 @@ def run_reference(args):
 
 
 def _config(n_gpus, ref=False):
-    return {'workload': 'BASELINE configs[1]: 1M reservations x 4096 GPU UUIDs, 1M candidate conflict queries per GPU',
+    name = ('BASELINE configs[1]: 1M reservations x 4096 GPU UUIDs, 1M candidate conflict queries per GPU'
+            if N_ROWS == 1_000_000 else
+            "one rank's share of BASELINE configs[4]: %d reservations x %d GPU UUIDs, %d candidate conflict queries per GPU"
+            % (N_ROWS, N_UUIDS, N_QUERIES))
+    return {'workload': name,
             'reservations_per_gpu': N_ROWS, 'uuids_per_gpu': N_UUIDS, 'queries_per_step_per_gpu': N_QUERIES,
             'parallelism': ('uuid-sharded x%d, K2 fused with the all-gather of bitmap words over NVLink peer memory' % n_gpus
                             if n_gpus > 1 else 'single GPU'),
@@ -268,6 +272,8 @@ def run_ours(args):
         evs = []
         for _ in range(n):
             flush.sum()
+            if px is not None:
+                px.barrier()      # ranks meet on the device: the step's time is the exchange, not arrival skew
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
             step_fn()
@@ -381,7 +387,8 @@ def run_ours(args):
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
             'gpu_launches': steps,
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel'), 'peak_source': peak_src,
+                         'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,
+                         'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes, 'kernel_ms': k_ms, 'kernel_ms_warm_l2': k_ms_warm,
                          'frac_of_nominal_8TBs': achieved / 8000.0},
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
@@ -505,6 +512,7 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
 
 
 def main():
+    global N_ROWS, N_UUIDS, N_QUERIES
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
@@ -513,7 +521,13 @@ def main():
     ap.add_argument('--skip-usage', action='store_true', help='skip the config-3 usage-reduce measurement')
     ap.add_argument('--skip-sweep', action='store_true', help='skip the config-4 service sweep measurement')
     ap.add_argument('--skip-cpu', action='store_true', help='skip the single-core CPU baseline leg')
+    ap.add_argument('--workload', default='cfg2', choices=['cfg2', 'cfg5'],
+                    help="cfg2 = BASELINE configs[1] (default, the metric's configuration); cfg5 = one rank's share of "
+                         'configs[4]: 12.5M reservations x 8192 uuids, 12.5M queries per GPU (100M calendar on 8 GPUs)')
     args = ap.parse_args()
+    if args.workload == 'cfg5':
+        N_ROWS, N_UUIDS, N_QUERIES = 12_500_000, 8192, 12_500_000
+        args.skip_sweep = True
     if args.impl == 'reference':
         run_reference(args)
     else:

@@ -156,14 +156,15 @@ int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_
                     int64_t *out_count, int64_t *out_avg_gpu, int64_t *out_avg_mem, int mem, void *stream);
 
 /* Multi-GPU exchange (no counterpart in the reference, which is single-process CPU code).
- * One process per GPU; rank r owns a contiguous uuid range.  th_peer_create allocates this rank's gathered-words
- * buffer (two generations x world x words_per_rank u32 + arrival flags) and returns its 64-byte CUDA IPC handle;
- * after the handles have been exchanged (rank order, world x 64 bytes) th_peer_connect maps every peer's buffer.
- * th_conflict_bitmap_exchange is K2 FUSED with the all-gather: the kernel stores each bitmap word into every
- * rank's buffer over NVLink and a wait kernel on `stream` returns control when all ranks' words of this step have
- * landed; *out_gathered is then this rank's [world][words_per_rank] view (valid until the step after next).
- * Device pointers only.  th_peer_check synchronises `stream` and reports a missed arrival as TH_EINTERNAL.
- * With wait = 0 the call only enqueues the kernel; th_peer_wait enqueues the wait half later.
+ * One process per GPU; rank r owns a contiguous uuid range.  th_peer_create allocates this rank's slot buffer (two
+ * generations x world x words_per_rank 8-byte {word, epoch} slots + barrier flags) and returns its 64-byte CUDA IPC
+ * handle; after the handles have been exchanged (rank order, world x 64 bytes) th_peer_connect maps every peer's
+ * buffer.  th_conflict_bitmap_exchange is K2 FUSED with the all-gather: the kernel stores each bitmap word, tagged
+ * with the step's epoch, into every rank's slots over NVLink, and an unpack kernel on `stream` polls the slots and
+ * writes *out_gathered, this rank's compact [world][words_per_rank] words (valid until the step after next).
+ * m_per_rank (HOST array, world entries, or NULL = every rank has m queries) says how much each rank contributes.
+ * Query arrays are DEVICE pointers.  th_peer_check synchronises `stream` and reports a missed arrival as
+ * TH_EINTERNAL.  With wait = 0 the call only enqueues the kernel; th_peer_wait enqueues the receive half later.
  * th_peer_connect(local_ptrs != NULL) wires buffers of the SAME process together (several ranks emulated on one
  * GPU in tests); th_peer_local_base returns the buffer address for that purpose. */
 typedef struct th_peer th_peer;
@@ -174,8 +175,10 @@ int th_peer_destroy(th_peer *p);
 int th_peer_check(th_peer *p, void *stream);
 int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
                                 const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id, int mode,
-                                int wait, uint32_t **out_gathered, void *stream);
+                                const int64_t *m_per_rank, int wait, uint32_t **out_gathered, void *stream);
 int th_peer_wait(th_peer *p, void *stream);
+/* Device-side rendezvous of all ranks on `stream` (no host synchronisation). */
+int th_peer_barrier(th_peer *p, void *stream);
 
 /* Stand-alone K1: stable LSD radix sort of (k_hi, k_lo) pairs carrying their original index.
  * Exposed for tests and for sorting windows / queries on the device; all pointers are device memory.

@@ -98,27 +98,36 @@ static inline ThGrid th_grid_of(const th_snapshot *h) {
 }
 
 // ---- peer exchange (multi-GPU): where a fused kernel deposits its bitmap words on every rank --------------
+// "LL" protocol: every 32-bit bitmap word travels as ONE 8-byte store {word, epoch}.  A naturally aligned 8-byte
+// store is single-copy atomic (also across NVLink), so the receiver knows a word has arrived as soon as its slot
+// shows the current epoch -- no fences, no completion counters, no flag round trip after the data.
 #define TH_MAX_PEERS 16
 struct ThPeerOut {
     int n;                       // 0 = no exchange (single GPU)
     int rank;
-    u32 epoch;                   // value written to the flags when this launch's words are complete
-    i64 word_off;                // rank * words_per_rank (+ buffer parity offset)
-    u32 *dst[TH_MAX_PEERS];      // gathered-words buffer of every rank (peer-mapped device pointers)
-    u32 *flags[TH_MAX_PEERS];    // flags[p][rank] lives on rank p
-    u32 *done;                   // local counter of finished CTAs (0 between launches)
+    u32 epoch;                   // tag written into the high half of every slot of this step
+    i64 word_off;                // rank * words_per_rank
+    u64 *dst[TH_MAX_PEERS];      // slot array (this step's generation) of every rank, peer-mapped
+    u32 *flags[TH_MAX_PEERS];    // th_peer_barrier only: barrier flag array of every rank
 };
+struct ThPeerCounts { i64 words[TH_MAX_PEERS]; };   // bitmap words each rank contributes this step
 struct th_peer {
     int device, world, rank;
-    i64 words_per_rank;          // capacity per rank and buffer
+    i64 words_per_rank;          // capacity per rank
     u32 epoch;
-    void *base;                  // local allocation: [2 buffers][world][words_per_rank] u32, then flags[world], done, err
+    u32 bepoch;                  // generation of th_peer_barrier
+    void *base;                  // IPC-shared: slots [2 generations][world][words_per_rank] u64, then err + barrier flags
+    u32 *out;                    // local: compact words [2 generations][world][words_per_rank]
     void *peer_base[TH_MAX_PEERS];
+    ThPeerCounts counts;         // of the latest step
     int connected;
 };
-static inline size_t th_peer_bytes(int world, i64 wpr) { return (size_t)2 * world * wpr * 4 + (size_t)(world + 8) * 4; }
-static inline u32 *th_peer_words(void *base, int world, i64 wpr, int parity) { return (u32 *)base + (size_t)parity * world * wpr; }
-static inline u32 *th_peer_flags(void *base, int world, i64 wpr) { return (u32 *)base + (size_t)2 * world * wpr; }
+static inline size_t th_peer_bytes(int world, i64 wpr) { return (size_t)2 * world * wpr * 8 + (size_t)(world + 8) * 4; }
+static inline u64 *th_peer_slots(void *base, int world, i64 wpr, int parity) { return (u64 *)base + (size_t)parity * world * wpr; }
+// after the slots: err | 7 spare | barrier_flags[world]
+static inline u32 *th_peer_misc(void *base, int world, i64 wpr) { return (u32 *)((u64 *)base + (size_t)2 * world * wpr); }
+static inline u32 *th_peer_bflags(void *base, int world, i64 wpr) { return th_peer_misc(base, world, wpr) + 8; }
+static inline u32 *th_peer_out(const th_peer *p, int parity) { return p->out + (size_t)parity * p->world * p->words_per_rank; }
 
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ longlong2 th_ld16(const void *p) {

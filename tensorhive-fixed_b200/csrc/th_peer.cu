@@ -1,13 +1,14 @@
 // Peer group for the fused K2 + all-gather (the reference has no multi-GPU path at all).
 //
-// One process per GPU.  Every rank allocates one buffer with cudaMalloc -- two generations of the gathered bitmap
-// words [world][words_per_rank] plus one arrival flag per rank -- exports it as a CUDA IPC handle, and maps the
+// One process per GPU.  Every rank allocates one buffer with cudaMalloc -- two generations of 8-byte slots
+// {bitmap word, epoch} [world][words_per_rank] plus barrier flags -- exports it as a CUDA IPC handle, and maps the
 // buffers of all other ranks (NVLink peer access is enabled lazily by the mapping).  The handles travel through
-// whatever the host side has (torch.distributed.all_gather_object in sharding.py).
+// whatever the host side has (torch.distributed.all_gather_object in sharding.py).  The compact gathered words
+// the caller reads live in a second, private allocation.
 //
-// Two generations: rank A can run at most one step ahead of rank B (A's wait kernel of step k+1 needs B's flag of
-// step k+1, which B raises only after finishing, in stream order, everything of step k), so step k+2 never
-// overwrites words of step k that somebody still reads.
+// Two generations: rank A can run at most one step ahead of rank B (A's unpack kernel of step k+1 needs B's slots
+// of step k+1, which B writes only after finishing, in stream order, everything of step k), so step k+2 never
+// overwrites slots of step k that somebody still polls.
 #include "th_common.cuh"
 #include <string.h>
 
@@ -26,13 +27,16 @@ extern "C" int th_peer_create(int device, int world, int rank, int64_t words_per
     p->device = device; p->world = world; p->rank = rank; p->words_per_rank = words_per_rank;
     const size_t bytes = th_peer_bytes(world, words_per_rank);
     cudaError_t e = cudaMalloc(&p->base, bytes);
-    if (e == cudaSuccess) e = cudaMemset(p->base, 0, bytes);
+    if (e == cudaSuccess) e = cudaMemset(p->base, 0, bytes);     // epoch 0 = "nothing has arrived"
+    if (e == cudaSuccess) e = cudaMalloc((void **)&p->out, (size_t)2 * world * words_per_rank * 4);
+    if (e == cudaSuccess) e = cudaMemset(p->out, 0, (size_t)2 * world * words_per_rank * 4);
     cudaIpcMemHandle_t hnd;
     if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hnd, p->base);
     if (prev != device) cudaSetDevice(prev);
     if (e != cudaSuccess) {
         th_set_error("th_peer_create: %s", cudaGetErrorString(e));
         if (p->base) cudaFree(p->base);
+        if (p->out) cudaFree(p->out);
         delete p;
         return e == cudaErrorMemoryAllocation ? TH_ENOMEM : TH_ECUDA;
     }
@@ -85,6 +89,7 @@ extern "C" int th_peer_destroy(th_peer *p) {
         for (int r = 0; r < p->world; ++r)
             if (r != p->rank && p->peer_base[r]) cudaIpcCloseMemHandle(p->peer_base[r]);
     if (p->base) cudaFree(p->base);
+    if (p->out) cudaFree(p->out);
     cudaSetDevice(prev);
     delete p;
     return TH_OK;

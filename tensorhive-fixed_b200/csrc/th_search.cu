@@ -33,6 +33,7 @@ constexpr int BM_THREADS = 256;
 #ifndef BM_MIN_BLOCKS
 #define BM_MIN_BLOCKS 4
 #endif
+constexpr int BM_MAXW = 2048;   // bitmap words a CTA buffers for the fused exchange (8 KB)
 
 // One lane per query, persistent warps.  Two things bound this kernel, and neither is bytes: (1) a memory
 // instruction whose 32 lanes touch 32 different cache lines costs 32 L1 wavefronts and 32 L2 sector
@@ -119,15 +120,22 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const i64 full_tiles = cols_aligned16 ? m / 32 : 0;      // warp tiles that are staged through shared memory
     const i64 tiles = (m + 31) / 32;
-    const i64 gw = (i64)blockIdx.x * BM_WARPS + warp;
-    const i64 nw = (i64)gridDim.x * BM_WARPS;
+    // Each CTA owns a CONTIGUOUS range of tiles [t_begin, t_end); its 8 warps interleave inside it (warp w takes
+    // t_begin + w, + 8, + 16, ...), so a CTA still reads 8 KB of contiguous query columns per round, and its bitmap
+    // words form one contiguous run that the fused exchange can ship to the peers in 128-byte packets.
+    const i64 per_cta = (tiles + gridDim.x - 1) / gridDim.x;
+    const i64 t_begin = (i64)blockIdx.x * per_cta;
+    const i64 t_end = t_begin + per_cta < tiles ? t_begin + per_cta : tiles;
+    __shared__ u32 swords[BM_MAXW];
+    const bool buffered = po.n > 0 && per_cta <= BM_MAXW;
+    auto tile_of = [&](u32 it) -> i64 { return t_begin + warp + (i64)BM_WARPS * it; };
 
     // level 1: a warp tile (32 queries x 4 columns = 1 KB = 64 chunks of 16 bytes) is staged with two cp.async per
     // lane -- coalesced, 16 bytes each, no registers -- into a per-warp 4-stage ring; one commit group per tile, and
     // an (empty) group is committed even when there is nothing left to prefetch so that "all but the newest
     // BM_STAGES - 1 groups have landed" always means "this tile has landed".
     auto stage_in = [&](i64 tile, int st) {
-        if (tile < full_tiles) {
+        if (tile < t_end && tile < full_tiles) {
             const i64 base = tile * 32;
 #pragma unroll
             for (int c = lane; c < NCOL * 16; c += 32) {
@@ -156,18 +164,18 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             qs = th_ld_stream(&q_start[ic]);
             self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
         }
-        stage_in(tile + (i64)BM_STAGES * nw, st);
+        stage_in(tile_of(it + BM_STAGES), st);
         cell = th_ld16_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, make_longlong2(0, 0));   // no uuids: no grid
     };
 
 #pragma unroll
-    for (int st = 0; st < BM_STAGES; ++st) stage_in(gw + (i64)st * nw, st);
+    for (int st = 0; st < BM_STAGES; ++st) stage_in(tile_of(st), st);
     // Measured on B200 (tools/k2_sweep.py): requesting the cell of tile k + 1 before the rows of tile k did not pay,
     // neither in plain C++ (ptxas sinks the prefetch again: 26.6 us vs 24.5 us cold at 1 M queries) nor as ordered
     // volatile PTX (24.8 us; 264 us vs 217 us at 16 M queries).  At ~320 warp instructions per 32 queries the kernel
     // is bound by issue slots, and the pipelined loop adds instructions; so each tile runs levels 2 and 3 in turn.
     u32 it = 0;
-    for (i64 tile = gw; tile < tiles; tile += nw, ++it) {
+    for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
         longlong2 cell;
         fetch(tile, it, u, qs, qe, self, cell);
@@ -176,39 +184,47 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         const u32 word = __ballot_sync(0xffffffffu, hit);
         if (lane == 0) {
             if (out_bits) out_bits[tile] = word;
-            // fused exchange: the word goes straight into every rank's gathered buffer over NVLink (peer stores)
-            for (int p = 0; p < po.n; ++p) po.dst[p][po.word_off + tile] = word;
+            if (buffered) swords[tile - t_begin] = word;
+            else if (po.n > 0) {                                       // very large batches: one slot store per tile
+                const u64 slot = (u64)word | ((u64)po.epoch << 32);
+                for (int p = 0; p < po.n; ++p) po.dst[p][po.word_off + tile] = slot;
+            }
         }
     }
-    if (po.n > 0) {
-        // completion: every CTA publishes its peer stores system-wide, the last one to finish raises this
-        // rank's flag on every peer (the receivers' wait kernel polls it)
-        __threadfence_system();
+    if (buffered) {
+        // Fused exchange: the CTA's run of words goes straight into every rank's slot array over NVLink as coalesced
+        // 8-byte {word, epoch} stores (256-byte packets; a 4-byte store per word and tile was measured at +3 us per
+        // extra peer on the whole kernel).  Nothing else is needed: the receiver sees each slot turn to this epoch.
         __syncthreads();
-        if (threadIdx.x == 0) {
-            const u32 prev = atomicAdd(po.done, 1u);
-            if (prev == gridDim.x - 1) {
-                __threadfence_system();
-                for (int p = 0; p < po.n; ++p) {
-                    volatile u32 *f = po.flags[p] + po.rank;
-                    *f = po.epoch;
-                }
-                __threadfence_system();
-                *po.done = 0;
-            }
+        const int cnt = (int)(t_end > t_begin ? t_end - t_begin : 0);
+        const u64 tag = (u64)po.epoch << 32;
+        for (int p = 0; p < po.n; ++p) {
+            u64 *dst = po.dst[p] + po.word_off + t_begin;
+            for (int j = threadIdx.x; j < cnt; j += BM_THREADS) dst[j] = (u64)swords[j] | tag;
         }
     }
 }
 
-// receivers: wait until every rank's flag has reached `epoch` (bounded; sets *err on timeout)
-__global__ void k2_wait_flags_kernel(volatile u32 *flags, int world, u32 epoch, int *err) {
-    const int r = threadIdx.x;
-    if (r >= world) return;
-    for (u64 spins = 0; (int)(flags[r] - epoch) < 0; ++spins) {
-        if (spins > (1ull << 24)) { *err = 1; return; }
-        __nanosleep(100);
+// receivers: poll every expected slot until it carries this step's epoch, and write the compact words the caller
+// reads (bounded spin; sets *err on timeout).  Slots a rank does not use this step read as 0.
+__global__ void __launch_bounds__(256) k2_ll_unpack_kernel(const volatile u64 *__restrict__ slots, u32 *__restrict__ out,
+                                                           int world, i64 wpr, ThPeerCounts counts, u32 epoch, int *err) {
+    const i64 total = (i64)world * wpr;
+    for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (i64)gridDim.x * blockDim.x) {
+        const int r = (int)(idx / wpr);
+        const i64 j = idx - (i64)r * wpr;
+        u32 w = 0;
+        if (j < counts.words[r]) {
+            u64 v = slots[idx];
+            for (u64 spins = 0; (u32)(v >> 32) != epoch; ++spins) {
+                if (spins > (1ull << 22)) { *err = 1; break; }
+                __nanosleep(64);
+                v = slots[idx];
+            }
+            w = (u32)v;
+        }
+        out[idx] = w;
     }
-    __threadfence_system();
 }
 
 // ---- conflict sets ------------------------------------------------------------------------------------
@@ -409,7 +425,7 @@ __global__ void __launch_bounds__(XS_THREADS) xs_write_kernel(const int *__restr
 
 static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d_s, const void *d_e, const void *d_f,
                      int mode, u32 *d_bits, const ThPeerOut &po, cudaStream_t st) {
-    const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp a tile
+    const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp at least one tile
     // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
     static int occ[2] = {0, 0};
     const int oi = mode == TH_MODE_STRICT ? 0 : 1;
@@ -551,13 +567,31 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
 }
 
 
-// Fused K2 + all-gather: every rank's kernel stores its bitmap words directly into the
-// gathered buffer of every rank (peer-mapped memory over NVLink/NVSwitch) and raises a per-rank flag when its last
-// CTA retires; a one-block wait kernel on the same stream then holds the stream until all ranks' flags for this
-// step have arrived.  No NCCL call, no host round trip.  Device pointers only.
+// Fused K2 + all-gather: every rank's kernel stores its bitmap words, tagged with the step's
+// epoch, directly into the slot array of every rank (peer-mapped memory over NVLink/NVSwitch); an unpack kernel on the
+// same stream polls the slots it expects and writes the compact [world][words_per_rank] words the caller reads.
+// No NCCL call, no fence, no host round trip.  Device pointers only.  m_per_rank (host, world entries, may be NULL =
+// "every rank has m") tells the receiver how many queries each rank contributes this step.
+static int k2_launch_unpack(th_peer *peer, cudaStream_t st) {
+    const int parity = (int)(peer->epoch & 1u);
+    const i64 total = (i64)peer->world * peer->words_per_rank;
+    i64 used = 0;
+    for (int r = 0; r < peer->world; ++r) used += peer->counts.words[r];
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > TH_NUM_SMS * 4) blocks = TH_NUM_SMS * 4;
+    (void)used;
+    k2_ll_unpack_kernel<<<blocks, 256, 0, st>>>(th_peer_slots(peer->base, peer->world, peer->words_per_rank, parity),
+                                                th_peer_out(peer, parity), peer->world, peer->words_per_rank,
+                                                peer->counts, peer->epoch,
+                                                (int *)th_peer_misc(peer->base, peer->world, peer->words_per_rank));
+    TH_CUDA(cudaGetLastError());
+    return TH_OK;
+}
+
 extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
                                            const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id,
-                                           int mode, int wait, uint32_t **out_gathered, void *stream) {
+                                           int mode, const int64_t *m_per_rank, int wait, uint32_t **out_gathered,
+                                           void *stream) {
     TH_REQUIRE(h != nullptr && h->loaded, "th_conflict_bitmap_exchange: snapshot not loaded");
     TH_REQUIRE(peer != nullptr && peer->connected, "th_conflict_bitmap_exchange: peer group not connected");
     TH_REQUIRE(peer->device == h->device, "th_conflict_bitmap_exchange: peer group and snapshot are on different devices");
@@ -567,54 +601,85 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
     TH_REQUIRE(mode == TH_MODE_STRICT || mode == TH_MODE_INCLUSIVE, "th_conflict_bitmap_exchange: mode %d not supported", mode);
     TH_REQUIRE(m == 0 || (q_uuid && q_start && q_end), "th_conflict_bitmap_exchange: NULL array");
     TH_REQUIRE(mode != TH_MODE_STRICT || m == 0 || q_self_id, "th_conflict_bitmap_exchange: q_self_id is NULL");
+    const int world = peer->world;
+    const i64 wpr = peer->words_per_rank;
+    for (int r = 0; r < world; ++r) {
+        const i64 mr = m_per_rank ? m_per_rank[r] : m;
+        TH_REQUIRE(mr >= 0 && (mr + 31) / 32 <= wpr, "th_conflict_bitmap_exchange: m_per_rank[%d] = %lld does not fit", r,
+                   (long long)mr);
+        peer->counts.words[r] = (mr + 31) / 32;
+    }
+    TH_REQUIRE(peer->counts.words[peer->rank] == (m + 31) / 32, "th_conflict_bitmap_exchange: m_per_rank[rank] != m");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_conflict_bitmap_exchange: cannot select device %d", h->device); return TH_ECUDA; }
     cudaStream_t st = (cudaStream_t)stream;
-    const u32 epoch = ++peer->epoch;
+    const u32 epoch = ++peer->epoch == 0 ? ++peer->epoch : peer->epoch;      // 0 means "empty slot"
     const int parity = (int)(epoch & 1u);
-    const int world = peer->world;
-    const i64 wpr = peer->words_per_rank;
     ThPeerOut po;
     po.n = world; po.rank = peer->rank; po.epoch = epoch;
     po.word_off = (i64)peer->rank * wpr;
     for (int p = 0; p < world; ++p) {
-        po.dst[p] = th_peer_words(peer->peer_base[p], world, wpr, parity);
-        po.flags[p] = th_peer_flags(peer->peer_base[p], world, wpr);
+        po.dst[p] = th_peer_slots(peer->peer_base[p], world, wpr, parity);
+        po.flags[p] = nullptr;
     }
-    u32 *local_flags = th_peer_flags(peer->base, world, wpr);
-    po.done = local_flags + world;
-    int *err = (int *)(local_flags + world + 1);
-    TH_TRY(k2_launch(h, m, q_uuid, q_start, q_end, q_self_id, mode, nullptr, po, st));
-    if (wait) {
-        k2_wait_flags_kernel<<<1, 32, 0, st>>>(local_flags, world, epoch, err);
-        TH_CUDA(cudaGetLastError());
-    }
-    if (out_gathered) *out_gathered = th_peer_words(peer->base, world, wpr, parity);
+    if (m > 0) TH_TRY(k2_launch(h, m, q_uuid, q_start, q_end, q_self_id, mode, nullptr, po, st));
+    if (wait) TH_TRY(k2_launch_unpack(peer, st));
+    if (out_gathered) *out_gathered = th_peer_out(peer, parity);
     return TH_OK;
 }
 
-// the wait half on its own (for th_conflict_bitmap_exchange(wait = 0)): holds `stream` until every rank's words
-// of the latest step have arrived
+// device-side rendezvous of all ranks: raise my barrier flag on every peer, then wait for everybody's
+__global__ void k2_peer_barrier_kernel(ThPeerOut po, volatile u32 *my_bflags, int *err) {
+    const int r = threadIdx.x;
+    if (r >= po.n) return;
+    volatile u32 *f = po.flags[r] + po.rank;
+    *f = po.epoch;
+    __threadfence_system();
+    for (u64 spins = 0; (int)(my_bflags[r] - po.epoch) < 0; ++spins) {
+        if (spins > (1ull << 24)) { *err = 1; return; }
+        __nanosleep(100);
+    }
+}
+
+// All ranks meet on the device (bench.py uses it to line the ranks up before a timed step, so that a step's time
+// is the exchange's latency and not the ranks' arrival skew).  Enqueued on `stream`; no host synchronisation.
+extern "C" int th_peer_barrier(th_peer *peer, void *stream) {
+    TH_REQUIRE(peer != nullptr && peer->connected, "th_peer_barrier: peer group not connected");
+    int prev = 0;
+    TH_CUDA(cudaGetDevice(&prev));
+    if (prev != peer->device) TH_CUDA(cudaSetDevice(peer->device));
+    ThPeerOut po;
+    po.n = peer->world; po.rank = peer->rank; po.epoch = ++peer->bepoch; po.word_off = 0;
+    for (int p = 0; p < peer->world; ++p) {
+        po.dst[p] = nullptr;
+        po.flags[p] = th_peer_bflags(peer->peer_base[p], peer->world, peer->words_per_rank);
+    }
+    k2_peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
+        po, th_peer_bflags(peer->base, peer->world, peer->words_per_rank),
+        (int *)th_peer_misc(peer->base, peer->world, peer->words_per_rank));
+    cudaError_t e = cudaGetLastError();
+    if (prev != peer->device) cudaSetDevice(prev);
+    if (e != cudaSuccess) { th_set_error("th_peer_barrier: launch -> %s", cudaGetErrorString(e)); return TH_ECUDA; }
+    return TH_OK;
+}
+
+// the receive half on its own (for th_conflict_bitmap_exchange(wait = 0)): enqueues the unpack kernel of the latest step
 extern "C" int th_peer_wait(th_peer *peer, void *stream) {
     TH_REQUIRE(peer != nullptr && peer->connected, "th_peer_wait: peer group not connected");
     int prev = 0;
     TH_CUDA(cudaGetDevice(&prev));
     if (prev != peer->device) TH_CUDA(cudaSetDevice(peer->device));
-    u32 *local_flags = th_peer_flags(peer->base, peer->world, peer->words_per_rank);
-    k2_wait_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(local_flags, peer->world, peer->epoch,
-                                                           (int *)(local_flags + peer->world + 1));
-    cudaError_t e = cudaGetLastError();
+    const int rc = k2_launch_unpack(peer, (cudaStream_t)stream);
     if (prev != peer->device) cudaSetDevice(prev);
-    if (e != cudaSuccess) { th_set_error("th_peer_wait: launch -> %s", cudaGetErrorString(e)); return TH_ECUDA; }
-    return TH_OK;
+    return rc;
 }
 
 extern "C" int th_peer_check(th_peer *peer, void *stream) {
     TH_REQUIRE(peer != nullptr && peer->base, "th_peer_check: peer group not created");
     int e = 0;
-    u32 *local_flags = th_peer_flags(peer->base, peer->world, peer->words_per_rank);
-    TH_CUDA(cudaMemcpyAsync(&e, local_flags + peer->world + 1, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TH_CUDA(cudaMemcpyAsync(&e, th_peer_misc(peer->base, peer->world, peer->words_per_rank), sizeof(int),
+                            cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     TH_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-    if (e) { th_set_error("th_peer_check: a rank's words did not arrive within the wait kernel's bound"); return TH_EINTERNAL; }
+    if (e) { th_set_error("th_peer_check: a rank's words did not arrive within the unpack kernel's bound"); return TH_EINTERNAL; }
     return TH_OK;
 }

@@ -132,10 +132,11 @@ class _DevWords:
 class PeerExchange:
     """K2 fused with the all-gather of its bitmap words over peer memory (NVLink / NVSwitch), one process per GPU.
 
-    Every rank creates its gathered-words buffer inside the library, the 64-byte CUDA IPC handles are exchanged once
-    through ``torch.distributed.all_gather_object`` (plumbing), and from then on a step is ONE call:
-    ``words = px.conflict_words(snapshot, q_uuid, q_start, q_end, q_self)`` -- the kernel writes each rank's words
-    into every rank's buffer and the stream resumes when all of them have arrived.  No NCCL call per step.
+    Every rank creates its slot buffer inside the library, the 64-byte CUDA IPC handles are exchanged once through
+    ``torch.distributed.all_gather_object`` (plumbing), and from then on a step is ONE call:
+    ``words = px.conflict_words(snapshot, q_uuid, q_start, q_end, q_self)`` -- the kernel writes each rank's words,
+    tagged with the step number, into every rank's slots and an unpack kernel hands back the compact words once all
+    of them have arrived.  No NCCL call, no fence and no flag round trip per step.
     """
 
     def __init__(self, device: int, world: int, rank: int, max_queries_per_rank: int, connect: bool = True):
@@ -171,18 +172,22 @@ class PeerExchange:
         arr = (self._C.c_void_p * self.world)(*[self._C.c_void_p(int(b)) for b in bases])
         self._native.check(self._lib.th_peer_connect(self._h, None, arr))
 
-    def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True):
+    def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True, counts=None):
         """CUDA int64 tensors in; returns an int32 CUDA tensor view [world, words_per_rank] of the gathered words
-        (rank r's words for its own m queries sit in row r)."""
+        (rank r's words for its own queries sit in row r).  ``counts[r]`` = number of queries rank r contributes
+        this step (``Router.counts``); omit it when every rank has the same number."""
         import torch
         C = self._C
         m = int(q_uuid.numel())
         out = C.c_void_p(0)
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        cnt = None
+        if counts is not None:
+            cnt = (C.c_int64 * self.world)(*[int(c) for c in counts])
         self._native.check(self._lib.th_conflict_bitmap_exchange(
             snapshot._h, self._h, m, C.c_void_p(q_uuid.data_ptr()), C.c_void_p(q_start.data_ptr()),
             C.c_void_p(q_end.data_ptr()), C.c_void_p(q_self.data_ptr()) if q_self is not None else None, int(mode),
-            1 if wait else 0, C.byref(out), stream))
+            cnt, 1 if wait else 0, C.byref(out), stream))
         view = self._views.get(out.value)          # two generations -> two cached views
         if view is None:
             view = torch.as_tensor(_DevWords(out.value, self.world * self.words_per_rank),
@@ -194,6 +199,12 @@ class PeerExchange:
         import torch
         stream = self._C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         self._native.check(self._lib.th_peer_wait(self._h, stream))
+
+    def barrier(self):
+        """All ranks meet on the device (enqueued on the current stream, no host synchronisation)."""
+        import torch
+        stream = self._C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._native.check(self._lib.th_peer_barrier(self._h, stream))
 
     def check(self):
         import torch

@@ -422,7 +422,8 @@ def test_fused_exchange_two_ranks_emulated_on_one_gpu(th, synth, brute):
             idx = router.local_indices(r)
             counts.append(idx.size)
             views.append(px[r].conflict_words(snaps[r], t(router.local_uuid(q['uuid_id'], r)), t(q['start'][idx]),
-                                              t(q['end'][idx]), t(q['self_id'][idx]), wait=False))
+                                              t(q['end'][idx]), t(q['self_id'][idx]), wait=False,
+                                              counts=router.counts))
         for r in range(2):
             px[r].wait()
         torch.cuda.synchronize()

@@ -44,7 +44,7 @@ def main():
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     qd = [t(router.local_uuid(q['uuid_id'], rank)), t(q['start'][idx]), t(q['end'][idx]), t(q['self_id'][idx])]
     for step in range(4):
-        g = px.conflict_words(snap, *qd)
+        g = px.conflict_words(snap, *qd, counts=router.counts)
         torch.cuda.synchronize()
         px.check()
         fused = router.decode(g.cpu().numpy())
