@@ -498,6 +498,29 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
     barrier()
     alg = s_total * 24 + S_WINDOWS * 24 + S_WINDOWS * 24 + 8 * (S_UUIDS + 1)
     gbs = alg / (ms * 1e-3) / 1e9
+    # the narrow log format (uint8 utilisation): same windows, 2 bytes per sample instead of 16 behind the same search
+    g8, m8 = gpu.to(torch.uint8), mem.to(torch.uint8)
+    outs8 = [i64(S_WINDOWS) for _ in range(5)]
+
+    def k4_u8_step():
+        native.check(lib.th_usage_reduce_u8(local, s_total, S_UUIDS, off.data_ptr(), ts.data_ptr(), g8.data_ptr(),
+                                            m8.data_ptr(), S_WINDOWS, wu.data_ptr(), ws.data_ptr(), we.data_ptr(),
+                                            outs8[0].data_ptr(), outs8[1].data_ptr(), outs8[2].data_ptr(),
+                                            outs8[3].data_ptr(), outs8[4].data_ptr(), 1, sp))
+
+    for _ in range(warmup):
+        k4_u8_step()
+    evs8 = []
+    for _ in range(steps):
+        flush.sum()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); k4_u8_step(); b.record(stream)
+        evs8.append((a, b))
+    torch.cuda.synchronize()
+    ms8 = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in evs8])))
+    same = all(bool(torch.equal(x, y)) for x, y in zip(outs, outs8))
+    alg8 = s_total * 2 + S_WINDOWS * 48 + 8 * (S_UUIDS + 1)
+    gbs8 = alg8 / (ms8 * 1e-3) / 1e9
     cnt = outs[2]
     covered = int(cnt.sum().item())
     return {'metric': 'usage_reduce_GB_per_s', 'value': world * gbs, 'unit': 'GB/s', 'ms_per_step': ms,
@@ -508,7 +531,13 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
                        'empty_windows': int((cnt == 0).sum().item())},
             'roofline': {'kernel': 'k4_usage_kernel', 'bound': 'hbm', 'achieved': gbs, 'peak': peak, 'unit': 'GB/s',
                          'frac': gbs / peak, 'traffic': _traffic('k4_usage_kernel'), 'peak_source': peak_src,
-                         'algorithmic_bytes_per_launch': alg, 'frac_of_nominal_8TBs': gbs / 8000.0}}
+                         'algorithmic_bytes_per_launch': alg, 'frac_of_nominal_8TBs': gbs / 8000.0},
+            'narrow_u8': {'ms_per_step': ms8, 'samples_per_s': world * s_total / (ms8 * 1e-3),
+                          'speedup_vs_int64_columns': ms / ms8, 'results_identical_to_int64_path': same,
+                          'roofline': {'kernel': 'k4_usage_u8_kernel', 'bound': 'hbm', 'achieved': gbs8, 'peak': peak,
+                                       'unit': 'GB/s', 'frac': gbs8 / peak, 'algorithmic_bytes_per_launch': alg8,
+                                       'note': 'algorithmic bytes = 2 B/sample (uint8 gpu_util + mem_util) + 48 B/window; '
+                                               'ts is probed, not streamed'}}}
 
 
 def main():

@@ -155,6 +155,14 @@ int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_
                     const int64_t *win_start, const int64_t *win_end, int64_t *out_sum_gpu, int64_t *out_sum_mem,
                     int64_t *out_count, int64_t *out_avg_gpu, int64_t *out_avg_mem, int mem, void *stream);
 
+/* The same reduction over the narrow log format: utilisation percentages stored as one
+ * byte each (lossless for 0..255; the reference's samples are ints 0..100, NvidiaSmiParser.py:84-85), replacing the
+ * per-reservation JSON logs of UsageLoggingService.py:62-116.  2 bytes instead of 16 are read per sample. */
+int th_usage_reduce_u8(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets, const int64_t *ts_us,
+                       const uint8_t *gpu_util_u8, const uint8_t *mem_util_u8, int64_t w, const int64_t *win_uuid,
+                       const int64_t *win_start, const int64_t *win_end, int64_t *out_sum_gpu, int64_t *out_sum_mem,
+                       int64_t *out_count, int64_t *out_avg_gpu, int64_t *out_avg_mem, int mem, void *stream);
+
 /* Multi-GPU exchange (no counterpart in the reference, which is single-process CPU code).
  * One process per GPU; rank r owns a contiguous uuid range.  th_peer_create allocates this rank's slot buffer (two
  * generations x world x words_per_rank 8-byte {word, epoch} slots + barrier flags) and returns its 64-byte CUDA IPC

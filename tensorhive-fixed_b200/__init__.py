@@ -13,8 +13,8 @@ Layers, bottom up:
 Import as ``tensorhive_fixed_b200`` (shim package at the repo root).
 """
 from . import native  # noqa: F401
-from .api import Snapshot, usage_reduce, sort_pairs, MODE_STRICT, MODE_INCLUSIVE, MODE_UPCOMING  # noqa: F401
+from .api import Snapshot, usage_reduce, usage_reduce_u8, sort_pairs, MODE_STRICT, MODE_INCLUSIVE, MODE_UPCOMING  # noqa: F401
 from .api import OWNER_ANY, OWNER_OTHER, OWNER_SAME, NativeError  # noqa: F401
 
-__all__ = ['native', 'Snapshot', 'usage_reduce', 'sort_pairs', 'MODE_STRICT', 'MODE_INCLUSIVE', 'MODE_UPCOMING',
+__all__ = ['native', 'Snapshot', 'usage_reduce', 'usage_reduce_u8', 'sort_pairs', 'MODE_STRICT', 'MODE_INCLUSIVE', 'MODE_UPCOMING',
            'OWNER_ANY', 'OWNER_OTHER', 'OWNER_SAME', 'NativeError']

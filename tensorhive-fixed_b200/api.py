@@ -256,6 +256,20 @@ def usage_reduce(uuid_offsets, ts, gpu, mem, win_uuid, win_start, win_end, devic
     return tuple(o[0] for o in outs)
 
 
+def usage_reduce_u8(uuid_offsets, ts, gpu_u8, mem_u8, win_uuid, win_start, win_end, device: int = 0):
+    """usage_reduce over the narrow log format: utilisation as uint8 columns (2 bytes read per sample, not 16)."""
+    lib = native.load()
+    a = _Args(uuid_offsets, ts, gpu_u8, mem_u8, win_uuid, win_start, win_end)
+    s, w = int(len(ts)), int(len(win_uuid))
+    n_uuids = int(len(uuid_offsets)) - 1
+    outs = [a.out(w) for _ in range(5)]
+    dev = a.device_index if a.device_mode else int(device)
+    native.check(lib.th_usage_reduce_u8(dev, s, n_uuids, a.inp(uuid_offsets), a.inp(ts), a.inp(gpu_u8, np.uint8),
+                                        a.inp(mem_u8, np.uint8), w, a.inp(win_uuid), a.inp(win_start), a.inp(win_end),
+                                        outs[0][1], outs[1][1], outs[2][1], outs[3][1], outs[4][1], a.mem, a.stream()))
+    return tuple(o[0] for o in outs)
+
+
 def sort_pairs(k_hi, k_lo, device: int = 0):
     """Stable argsort of (k_hi, k_lo) pairs by K1 (the onesweep radix sort)."""
     lib = native.load()

@@ -142,13 +142,95 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
     }
 }
 
+
+// ---- narrow sample format: utilisation as uint8 -------------------------------------
+// gpu_util / mem_util are percentages (0..100), so one byte each is lossless; the range sum then reads 2 bytes per
+// sample instead of 16.  Same range search as above (ts stays int64: it is probed, never streamed); the sum loads
+// 16 samples per lane and load (128-bit), masks the bytes outside [a, b) and adds four bytes per __dp4a.
+__device__ __forceinline__ u32 us_mask4(int lo, int hi, int base) {   // 0xff for bytes base..base+3 that lie in [lo, hi)
+    u32 m = 0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+        if (base + t >= lo && base + t < hi) m |= 0xffu << (8 * t);
+    return m;
+}
+__device__ __forceinline__ int us_sum16(const uint4 v, int lo, int hi) {
+    u32 acc = 0;   // unsigned bytes x 1: at most 16 * 255
+    acc = __dp4a(v.x & us_mask4(lo, hi, 0), 0x01010101u, acc);
+    acc = __dp4a(v.y & us_mask4(lo, hi, 4), 0x01010101u, acc);
+    acc = __dp4a(v.z & us_mask4(lo, hi, 8), 0x01010101u, acc);
+    acc = __dp4a(v.w & us_mask4(lo, hi, 12), 0x01010101u, acc);
+    return (int)acc;
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(US_THREADS) k4_usage_u8_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
+                                                                 const i64 *__restrict__ ts, const u8 *__restrict__ gpu,
+                                                                 const u8 *__restrict__ mem, i64 w,
+                                                                 const i64 *__restrict__ win_uuid,
+                                                                 const i64 *__restrict__ win_start,
+                                                                 const i64 *__restrict__ win_end, i64 *__restrict__ o_sg,
+                                                                 i64 *__restrict__ o_sm, i64 *__restrict__ o_cnt,
+                                                                 i64 *__restrict__ o_ag, i64 *__restrict__ o_am) {
+    const int lane = threadIdx.x & 31;
+    const int gl = lane & (US_GROUP - 1);
+    const u32 gmask = 0xffu << (lane & ~(US_GROUP - 1));
+    const i64 gstride = (i64)gridDim.x * US_GROUPS_PER_BLOCK;
+    for (i64 q = (i64)blockIdx.x * US_GROUPS_PER_BLOCK + (threadIdx.x / US_GROUP); q < w; q += gstride) {
+        const i64 u = win_uuid[q];
+        i64 a = 0, b = 0;
+        if (u >= 0 && u < n_uuids) {
+            const i64 lo = off[u], hi = off[u + 1];
+            if (lo < hi) {
+                const i64 ws = win_start[q], we = win_end[q];
+                const i64 t_lo = __ldg(&ts[lo]), t_hi = __ldg(&ts[hi - 1]);
+                a = us_search<true>(ts, lo, hi, ws, t_lo, t_hi, gl, gmask);
+                b = us_search<false>(ts, lo, hi, we, t_lo, t_hi, gl, gmask);
+                if (b < a) b = a;
+            }
+        }
+        i64 sg = 0, sm = 0;
+        if (VEC) {
+            const i64 c1 = (b + 15) >> 4;                       // 16-sample chunks, 16-byte aligned
+            for (i64 c = (a >> 4) + gl; c < c1; c += US_GROUP) {
+                const i64 i0 = c << 4;
+                const int lo = (int)(a > i0 ? a - i0 : 0);
+                const int hi = (int)(b < i0 + 16 ? b - i0 : 16);
+                if (i0 + 16 <= s_total) {
+                    const uint4 g4 = __ldg(reinterpret_cast<const uint4 *>(gpu + i0));
+                    const uint4 m4 = __ldg(reinterpret_cast<const uint4 *>(mem + i0));
+                    sg += us_sum16(g4, lo, hi);
+                    sm += us_sum16(m4, lo, hi);
+                } else {
+                    for (int t = lo; t < hi; ++t) { sg += gpu[i0 + t]; sm += mem[i0 + t]; }
+                }
+            }
+        } else {
+            for (i64 i = a + gl; i < b; i += US_GROUP) { sg += gpu[i]; sm += mem[i]; }
+        }
+#pragma unroll
+        for (int o = US_GROUP / 2; o > 0; o >>= 1) {
+            sg += __shfl_xor_sync(gmask, sg, o);
+            sm += __shfl_xor_sync(gmask, sm, o);
+        }
+        if (gl == 0) {
+            const i64 c = b - a;
+            if (o_sg) o_sg[q] = sg;
+            if (o_sm) o_sm[q] = sm;
+            if (o_cnt) o_cnt[q] = c;
+            if (o_ag) o_ag[q] = c > 0 ? us_floor_div(sg, c) : -1;
+            if (o_am) o_am[q] = c > 0 ? us_floor_div(sm, c) : -1;
+        }
+    }
+}
+
 }  // namespace
 
-extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets,
-                               const int64_t *ts_us, const int64_t *gpu_util, const int64_t *mem_util, int64_t w,
-                               const int64_t *win_uuid, const int64_t *win_start, const int64_t *win_end,
-                               int64_t *out_sum_gpu, int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu,
-                               int64_t *out_avg_mem, int mem, void *stream) {
+static int usage_reduce_impl(int elem, int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets,
+                             const int64_t *ts_us, const void *gpu_util, const void *mem_util, int64_t w,
+                             const int64_t *win_uuid, const int64_t *win_start, const int64_t *win_end,
+                             int64_t *out_sum_gpu, int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu,
+                             int64_t *out_avg_mem, int mem, void *stream) {
     TH_REQUIRE(s >= 0 && w >= 0 && n_uuids >= 0, "th_usage_reduce: negative size");
     TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_usage_reduce: bad mem flag %d", mem);
     if (w == 0) return TH_OK;
@@ -168,8 +250,8 @@ extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int
 #define US_TRY(x) if ((rc = (x)) != TH_OK) break;
             US_TRY(sc.in(uuid_offsets, 8 * zu, mem, &d_off));
             US_TRY(sc.in(ts_us, 8 * zs, mem, &d_ts));
-            US_TRY(sc.in(gpu_util, 8 * zs, mem, &d_g));
-            US_TRY(sc.in(mem_util, 8 * zs, mem, &d_m));
+            US_TRY(sc.in(gpu_util, (size_t)elem * zs, mem, &d_g));
+            US_TRY(sc.in(mem_util, (size_t)elem * zs, mem, &d_m));
             US_TRY(sc.in(win_uuid, 8 * zw, mem, &d_wu));
             US_TRY(sc.in(win_start, 8 * zw, mem, &d_ws));
             US_TRY(sc.in(win_end, 8 * zw, mem, &d_we));
@@ -180,7 +262,19 @@ extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int
             US_TRY(sc.out(out_avg_mem, 8 * zw, mem, &d_am));
             const bool vec = (((uintptr_t)d_g | (uintptr_t)d_m) & 15) == 0;
             const int grid = th_grid_for(w, US_GROUPS_PER_BLOCK, 64);
-            if (vec)
+            if (elem == 1 && vec)
+                k4_usage_u8_kernel<true><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
+                                                                      (const u8 *)d_g, (const u8 *)d_m, w,
+                                                                      (const i64 *)d_wu, (const i64 *)d_ws,
+                                                                      (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
+                                                                      (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
+            else if (elem == 1)
+                k4_usage_u8_kernel<false><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
+                                                                       (const u8 *)d_g, (const u8 *)d_m, w,
+                                                                       (const i64 *)d_wu, (const i64 *)d_ws,
+                                                                       (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
+                                                                       (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
+            else if (vec)
                 k4_usage_kernel<true><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
                                                                    (const i64 *)d_g, (const i64 *)d_m, w,
                                                                    (const i64 *)d_wu, (const i64 *)d_ws,
@@ -208,4 +302,23 @@ extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int
     }
     if (mem == TH_MEM_HOST && prev != device) cudaSetDevice(prev);
     return rc;
+}
+
+
+extern "C" int th_usage_reduce(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets,
+                               const int64_t *ts_us, const int64_t *gpu_util, const int64_t *mem_util, int64_t w,
+                               const int64_t *win_uuid, const int64_t *win_start, const int64_t *win_end,
+                               int64_t *out_sum_gpu, int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu,
+                               int64_t *out_avg_mem, int mem, void *stream) {
+    return usage_reduce_impl(8, device, s, n_uuids, uuid_offsets, ts_us, gpu_util, mem_util, w, win_uuid, win_start, win_end,
+                             out_sum_gpu, out_sum_mem, out_count, out_avg_gpu, out_avg_mem, mem, stream);
+}
+
+extern "C" int th_usage_reduce_u8(int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets,
+                                  const int64_t *ts_us, const uint8_t *gpu_util_u8, const uint8_t *mem_util_u8, int64_t w,
+                                  const int64_t *win_uuid, const int64_t *win_start, const int64_t *win_end,
+                                  int64_t *out_sum_gpu, int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu,
+                                  int64_t *out_avg_mem, int mem, void *stream) {
+    return usage_reduce_impl(1, device, s, n_uuids, uuid_offsets, ts_us, gpu_util_u8, mem_util_u8, w, win_uuid, win_start,
+                             win_end, out_sum_gpu, out_sum_mem, out_count, out_avg_gpu, out_avg_mem, mem, stream);
 }

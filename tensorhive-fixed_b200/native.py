@@ -45,6 +45,8 @@ SIGNATURES = {
     'th_conflict_bitmap_exchange': (_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, C.POINTER(_vp), _vp]),
     'th_peer_wait': (_int, [_vp, _vp]),
     'th_peer_barrier': (_int, [_vp, _vp]),
+    'th_usage_reduce_u8': (_int, [_int, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                  _int, _vp]),
     'th_sort_pairs': (_int, [_int, _i64, _vp, _vp, _vp, _int, _vp]),
     'th_synth_samples': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp]),
     'th_synth_windows': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp]),

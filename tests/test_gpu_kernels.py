@@ -452,3 +452,48 @@ def test_reloading_one_handle_reuses_or_regrows_its_buffers(th, synth, brute):
         assert np.array_equal(got, brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'])), (n, u)
         assert snap.info()['n'] == n
     snap.close()
+
+
+# ---- K4, narrow log format (uint8 utilisation) ---------------------------------------------------------------------------
+@pytest.mark.parametrize('kw', [dict(n_uuids=16, samples_per_uuid=4000), dict(n_uuids=7, samples_per_uuid=1001, jitter_us=900_000),
+                                dict(n_uuids=40, samples_per_uuid=300, ragged=True, cadence_us=60_000_000, jitter_us=5_000_000),
+                                dict(n_uuids=3, samples_per_uuid=1), dict(n_uuids=2, samples_per_uuid=100_003)])
+def test_usage_reduce_u8_matches_oracle(th, synth, brute, kw):
+    s = synth.make_samples(seed=15, **kw)
+    cad = kw.get('cadence_us', 1_000_000)
+    w = synth.make_windows(s, 3000, seed=16, min_len_us=5 * cad, max_len_us=400 * cad)
+    g8, m8 = s['gpu'].astype(np.uint8), (s['mem'] * 2 + 50).astype(np.uint8)        # values up to 250
+    outs = th.usage_reduce_u8(s['offsets'], s['ts'], g8, m8, w['uuid_id'], w['start'], w['end'])
+    esg, esm, ecnt = brute.usage_reduce(s['offsets'], s['ts'], g8.astype(np.int64), m8.astype(np.int64), w['uuid_id'],
+                                        w['start'], w['end'])
+    assert np.array_equal(outs[2], ecnt) and np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm)
+    assert np.array_equal(outs[3], np.array([brute.floor_avg(a, c) for a, c in zip(esg, ecnt)]))
+    assert np.array_equal(outs[4], np.array([brute.floor_avg(a, c) for a, c in zip(esm, ecnt)]))
+    # and it agrees with the wide-format kernel on the same data
+    wide = th.usage_reduce(s['offsets'], s['ts'], g8.astype(np.int64), m8.astype(np.int64), w['uuid_id'], w['start'], w['end'])
+    for a, b in zip(outs, wide):
+        assert np.array_equal(a, b)
+
+
+def test_usage_reduce_u8_unaligned_columns(th, brute):
+    import torch
+    rng = np.random.default_rng(18)
+    n = 70_001
+    base_g = rng.integers(0, 256, size=n + 3, dtype=np.uint8)
+    base_m = rng.integers(0, 101, size=n + 3, dtype=np.uint8)
+    ts = np.sort(rng.integers(0, 1_000_000, size=n, dtype=np.int64))
+    off = np.array([0, 30_000, 30_000, n], np.int64)
+    ts[:30_000].sort(); ts[30_000:].sort()
+    wu = rng.integers(0, 3, size=2000, dtype=np.int64)
+    ws = rng.integers(-1000, 1_000_000, size=2000, dtype=np.int64)
+    we = ws + rng.integers(-5, 60_000, size=2000, dtype=np.int64)
+    dev = torch.device('cuda:0')
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for shift in (0, 3):       # shift 3: the byte columns start 3 bytes off a 16-byte boundary
+        g = t(base_g)[shift:shift + n]
+        mm = t(base_m)[shift:shift + n]
+        outs = th.usage_reduce_u8(t(off), t(ts), g, mm, t(wu), t(ws), t(we))
+        esg, esm, ecnt = brute.usage_reduce(off, ts, base_g[shift:shift + n].astype(np.int64),
+                                            base_m[shift:shift + n].astype(np.int64), wu, ws, we)
+        assert np.array_equal(outs[0].cpu().numpy(), esg) and np.array_equal(outs[1].cpu().numpy(), esm)
+        assert np.array_equal(outs[2].cpu().numpy(), ecnt)
