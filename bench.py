@@ -523,6 +523,21 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
     gbs8 = alg8 / (ms8 * 1e-3) / 1e9
     cnt = outs[2]
     covered = int(cnt.sum().item())
+    cpu = None
+    if world == 1:
+        # the reference's averager on the host: avg(values) = sum(values) // len(values) over Python lists
+        # (UsageLoggingService.py:25-30), on windows of the same length distribution; one core, bounded sample
+        from oracle.services_ref import avg as ref_avg
+        rng = np.random.default_rng(SEED)
+        lists = [[int(v) for v in rng.integers(0, 101, size=int(n))] for n in rng.integers(20, 181, size=100_000)]
+        t0 = time.perf_counter()
+        for v in lists:
+            ref_avg(v); ref_avg(v)          # gpu_util and mem_util
+        dt = time.perf_counter() - t0
+        n_samples = sum(len(v) for v in lists)
+        cpu = {'value': n_samples / dt, 'unit': 'samples/s', 'cores': 1, 'kind': 'port',
+               'sample': '%d windows (%d samples) of in-memory Python lists; the reference additionally re-reads and '
+                         're-writes each JSON log on every tick' % (len(lists), n_samples)}
     return {'metric': 'usage_reduce_GB_per_s', 'value': world * gbs, 'unit': 'GB/s', 'ms_per_step': ms,
             'samples_per_s': world * s_total / (ms * 1e-3),
             'config': {'workload': 'BASELINE configs[2]: 1B samples (1 s cadence) -> 10M reservation windows per GPU',
@@ -532,6 +547,7 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
             'roofline': {'kernel': 'k4_usage_kernel', 'bound': 'hbm', 'achieved': gbs, 'peak': peak, 'unit': 'GB/s',
                          'frac': gbs / peak, 'traffic': _traffic('k4_usage_kernel'), 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg, 'frac_of_nominal_8TBs': gbs / 8000.0},
+            'cpu_baseline': cpu,
             'narrow_u8': {'ms_per_step': ms8, 'samples_per_s': world * s_total / (ms8 * 1e-3),
                           'speedup_vs_int64_columns': ms / ms8, 'results_identical_to_int64_path': same,
                           'roofline': {'kernel': 'k4_usage_u8_kernel', 'bound': 'hbm', 'achieved': gbs8, 'peak': peak,

@@ -81,18 +81,21 @@ struct UpAcc {
     int owner_hit;   // any matching row whose owner passes the test
 };
 
-template <bool WANT_OWNER>
+// G lanes cooperate on one uuid / task (G = 8: four tasks per warp -- the matching rows are few, so 32 lanes per
+// task left most issue slots empty; measured 57 us -> see bench service_sweep).  gl = lane index in the group,
+// gmask = the group's lanes in the warp.
+template <bool WANT_OWNER, int G>
 __device__ __forceinline__ UpAcc lk_upcoming(const ThGrid &g, i64 u, const ThP1 *__restrict__ p1,
                                              const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4, int lo, i64 now,
-                                             i64 later, int lane, int test, i64 owner) {
+                                             i64 later, int gl, u32 gmask, int gbase, int test, i64 owner) {
     UpAcc a;
     a.count = 0; a.first_row = 0x7fffffff; a.owner_hit = 0;
     int c1 = th_grid_prefix_end<false>(g, p1, u, later);   // rows with start <= now + period
     while (c1 > lo) {
         const longlong2 top = th_ld16(&p1[c1 - 1]);     // {start, m1}
         if (!(top.x >= now || top.y > now)) break;     // earlier rows start before now and none is still running
-        const int c0 = c1 - 32 > lo ? c1 - 32 : lo;
-        const int j = c0 + lane;
+        const int c0 = c1 - G > lo ? c1 - G : lo;
+        const int j = c0 + gl;
         bool mt = false;
         if (j < c1) {
             const longlong2 e = th_ld16(&p3[j]);        // {end, idc}
@@ -104,16 +107,19 @@ __device__ __forceinline__ UpAcc lk_upcoming(const ThGrid &g, i64 u, const ThP1 
             const i64 o = __ldg(&p4[j].owner);
             oh = test == TH_OWNER_ANY ? true : (test == TH_OWNER_OTHER ? (o != owner) : (o == owner));
         }
-        const u32 bal = __ballot_sync(0xffffffffu, mt);
+        const u32 bal = __ballot_sync(gmask, mt) & gmask;
         if (bal) {
             a.count += __popc(bal);
-            a.first_row = c0 + (__ffs(bal) - 1);        // chunks go downwards, so the last one seen wins
+            a.first_row = c0 + (__ffs(bal) - 1 - gbase);   // chunks go downwards, so the last one seen wins
         }
-        if (WANT_OWNER && __any_sync(0xffffffffu, oh)) a.owner_hit = 1;
+        if (WANT_OWNER && (__ballot_sync(gmask, oh) & gmask)) a.owner_hit = 1;
         c1 = c0;
     }
     return a;
 }
+
+constexpr int LK_GROUP = 8;
+constexpr int LK_GROUPS_PER_BLOCK = LK_THREADS / LK_GROUP;
 
 __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(ThGrid g, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
                                                                  const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
@@ -122,13 +128,16 @@ __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(ThGrid g, const
                                                                  i64 *__restrict__ o_start, i64 *__restrict__ o_owner,
                                                                  i64 *__restrict__ o_count) {
     const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * LK_WARPS;
-    for (i64 q = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); q < k; q += wstride) {
+    const int gl = lane & (LK_GROUP - 1), gbase = lane & ~(LK_GROUP - 1);
+    const u32 gmask = ((1u << LK_GROUP) - 1) << gbase;
+    const i64 gstride = (i64)gridDim.x * LK_GROUPS_PER_BLOCK;
+    for (i64 q = (i64)blockIdx.x * LK_GROUPS_PER_BLOCK + (threadIdx.x / LK_GROUP); q < k; q += gstride) {
         const i64 u = uuids[q];
         UpAcc a;
         a.count = 0; a.first_row = 0; a.owner_hit = 0;
-        if (u >= 0 && u < n_uuids) a = lk_upcoming<false>(g, u, p1, p3, p4, seg[u] + 1, now, later, lane, 0, 0);
-        if (lane == 0) {
+        if (u >= 0 && u < n_uuids)
+            a = lk_upcoming<false, LK_GROUP>(g, u, p1, p3, p4, seg[u] + 1, now, later, gl, gmask, gbase, 0, 0);
+        if (gl == 0) {
             if (a.count > 0) {
                 const int r = a.first_row;
                 o_id[q] = th_idc_id(__ldg(&p3[r].idc));
@@ -149,15 +158,18 @@ __global__ void __launch_bounds__(LK_THREADS) k5_owner_flags_kernel(ThGrid g, co
                                                                     const i64 *__restrict__ task_owner, int test,
                                                                     u8 *__restrict__ out_flag) {
     const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * LK_WARPS;
-    for (i64 q = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); q < t; q += wstride) {
+    const int gl = lane & (LK_GROUP - 1), gbase = lane & ~(LK_GROUP - 1);
+    const u32 gmask = ((1u << LK_GROUP) - 1) << gbase;
+    const i64 gstride = (i64)gridDim.x * LK_GROUPS_PER_BLOCK;
+    for (i64 q = (i64)blockIdx.x * LK_GROUPS_PER_BLOCK + (threadIdx.x / LK_GROUP); q < t; q += gstride) {
         const i64 u = task_uuid[q];
         int flag = 0;
         if (u >= 0 && u < n_uuids) {
-            const UpAcc a = lk_upcoming<true>(g, u, p1, p3, p4, seg[u] + 1, now, later, lane, test, task_owner[q]);
+            const UpAcc a = lk_upcoming<true, LK_GROUP>(g, u, p1, p3, p4, seg[u] + 1, now, later, gl, gmask, gbase, test,
+                                                        task_owner[q]);
             flag = a.owner_hit;
         }
-        if (lane == 0) out_flag[q] = (u8)flag;
+        if (gl == 0) out_flag[q] = (u8)flag;
     }
 }
 
@@ -229,7 +241,7 @@ extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_
     TH_TRY(sc.out(out_first_start, 8 * zk, mem, &d_s));
     TH_TRY(sc.out(out_first_owner, 8 * zk, mem, &d_o));
     TH_TRY(sc.out(out_count, 8 * zk, mem, &d_c));
-    k3_upcoming_kernel<<<th_grid_for(k, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+    k3_upcoming_kernel<<<th_grid_for(k, LK_GROUPS_PER_BLOCK, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
                                                                             now_us + period_us, k, (const i64 *)d_u,
                                                                             (i64 *)d_id, (i64 *)d_s, (i64 *)d_o, (i64 *)d_c);
     TH_CUDA(cudaGetLastError());
@@ -260,7 +272,7 @@ extern "C" int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int
     TH_TRY(sc.in(task_uuid, 8 * zt, mem, &d_u));
     TH_TRY(sc.in(task_owner, 8 * zt, mem, &d_o));
     TH_TRY(sc.out(out_flag_u8, zt, mem, &d_f));
-    k5_owner_flags_kernel<<<th_grid_for(t, LK_WARPS, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
+    k5_owner_flags_kernel<<<th_grid_for(t, LK_GROUPS_PER_BLOCK, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
                                                                                now_us + period_us, t, (const i64 *)d_u,
                                                                                (const i64 *)d_o, test, (u8 *)d_f);
     TH_CUDA(cudaGetLastError());
