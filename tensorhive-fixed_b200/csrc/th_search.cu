@@ -174,6 +174,9 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // neither in plain C++ (ptxas sinks the prefetch again: 26.6 us vs 24.5 us cold at 1 M queries) nor as ordered
     // volatile PTX (24.8 us; 264 us vs 217 us at 16 M queries).  At ~320 warp instructions per 32 queries the kernel
     // is bound by issue slots, and the pipelined loop adds instructions; so each tile runs levels 2 and 3 in turn.
+    // Also measured and dropped: pulling the index (cells, P1, P2 = 44 MB) into L2 with cp.async.bulk.prefetch.L2 at
+    // kernel start -- 26.8 us vs 24.6 us cold: the prefetch competes with the query stream for HBM and the probes'
+    // HBM latency was not what the warps were waiting for.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
