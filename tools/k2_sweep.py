@@ -19,6 +19,11 @@ U = int(os.environ.get('TH_SWEEP_U', '4096'))
 M = int(os.environ.get('TH_SWEEP_M', '1000000'))
 cal = synth.make_calendar(N, U, seed=20260102)
 q = synth.make_queries(cal, M, seed=20260103)
+if os.environ.get('TH_SWEEP_NOSELF'):
+    q['self_id'][:] = -1
+if os.environ.get('TH_SWEEP_SORTED'):      # queries grouped by uuid: what a caller iterating a calendar would send
+    o = np.lexsort((q['end'], q['uuid_id']))
+    q = {k: v[o] for k, v in q.items()}
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 cols = [t(cal[k]) for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')]
 qd = [t(q[k]) for k in ('uuid_id', 'start', 'end', 'self_id')]
