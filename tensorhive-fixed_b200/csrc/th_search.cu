@@ -183,7 +183,9 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         longlong2 cell;
         fetch(tile, it, u, qs, qe, self, cell);
         const i64 i = tile * 32 + lane;
-        const bool hit = (i < m) && (u >= 0 && u < n_uuids) && k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
+        // (qe = INT64_MIN cannot lie after any start, not even the sentinel's: no row, no conflict)
+        const bool hit = (i < m) && (u >= 0 && u < n_uuids) && qe > TH_I64_MIN &&
+                         k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
         const u32 word = __ballot_sync(0xffffffffu, hit);
         if (lane == 0) {
             if (out_bits) out_bits[tile] = word;

@@ -43,7 +43,22 @@ __global__ void __launch_bounds__(256) ld_stats_kernel(const i64 *__restrict__ i
         t = __shfl_xor_sync(0xffffffffu, mx_u, o); mx_u = t > mx_u ? t : mx_u;
         inv += __shfl_xor_sync(0xffffffffu, inv, o);
     }
+    // one set of atomics per CTA, not per warp: thousands of same-address atomics serialise in L2
+    __shared__ i64 sh[6][8];
+    __shared__ u64 sh_inv[8];
+    const int warp = threadIdx.x >> 5;
     if ((threadIdx.x & 31) == 0) {
+        sh[0][warp] = mn_s; sh[1][warp] = mx_s; sh[2][warp] = mn_i; sh[3][warp] = mx_i; sh[4][warp] = mn_u; sh[5][warp] = mx_u;
+        sh_inv[warp] = inv;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) {
+            mn_s = sh[0][w] < mn_s ? sh[0][w] : mn_s; mx_s = sh[1][w] > mx_s ? sh[1][w] : mx_s;
+            mn_i = sh[2][w] < mn_i ? sh[2][w] : mn_i; mx_i = sh[3][w] > mx_i ? sh[3][w] : mx_i;
+            mn_u = sh[4][w] < mn_u ? sh[4][w] : mn_u; mx_u = sh[5][w] > mx_u ? sh[5][w] : mx_u;
+            inv += sh_inv[w];
+        }
         atomicMin(&out->min_start, mn_s); atomicMax(&out->max_start, mx_s);
         atomicMin(&out->min_id, mn_i);    atomicMax(&out->max_id, mx_i);
         atomicMin(&out->min_uuid, mn_u);  atomicMax(&out->max_uuid, mx_u);

@@ -268,7 +268,8 @@ int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **s
 #define RS_CK(x) if ((e = (x)) != cudaSuccess) { rc = TH_ECUDA; th_set_error("th_radix_sort: %s -> %s", #x, cudaGetErrorString(e)); break; }
         RS_CK(cudaMemsetAsync(ghist, 0, ghist_bytes, st));
         RS_CK(cudaMemsetAsync(err_dev, 0, sizeof(int), st));
-        rs_hist_kernel<<<th_grid_for(n, RS_THREADS * 8, 8), RS_THREADS, 0, st>>>(a, (u32)n, plan, ghist);
+        // two CTAs per SM at most: every CTA ends with up to npass x 256 global atomics
+        rs_hist_kernel<<<th_grid_for(n, RS_THREADS * 8, 2), RS_THREADS, 0, st>>>(a, (u32)n, plan, ghist);
         rs_scan_kernel<<<plan.npass, RS_RADIX, 0, st>>>(ghist);
         RS_CK(cudaGetLastError());
         ThRec *src = a, *dst = b;
