@@ -385,7 +385,7 @@ def run_ours(args):
                     'ms_per_step': 1e3 * e2e_s / steps,
                     'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
-            'gpu_launches': steps,
+            'gpu_launches': steps * (2 if px is not None else 1),      # K2 (+ the unpack kernel of the fused exchange)
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,
                          'peak_source': peak_src,
@@ -415,6 +415,10 @@ def run_ours(args):
     snap.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def th_snapshot_wrapper(snap):
+    return snap
 
 
 def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
@@ -454,6 +458,14 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
                                                                    1, tflags.data_ptr(), 1, sp)))
     ms_up = med(lambda: native.check(lib.th_upcoming(snap._h, now, period, U, uu.data_ptr(), up[0].data_ptr(),
                                                      up[1].data_ptr(), up[2].data_ptr(), up[3].data_ptr(), 1, sp)))
+    # calendar view (controllers/reservation.py:31-55 -> filter_by_uuids_and_time_range): one 30-day range per uuid,
+    # row lists through th_conflict_sets(TH_MODE_INCLUSIVE) on the host path (two passes + D2H of the CSR)
+    r_s = np.full(U, now, np.int64)
+    r_e = r_s + 30 * synth.DAY_US
+    snapshot = th_snapshot_wrapper(snap)
+    t0 = time.perf_counter()
+    off, ids, canc = snapshot.conflict_sets(np.arange(U, dtype=np.int64), r_s, r_e, None, 1)
+    ms_range = 1e3 * (time.perf_counter() - t0)
     torch.cuda.synchronize()
     join_bytes = P * 16 + P * 9 + U * 16          # the K5 join proper
     return {'workload': 'BASELINE configs[3]: 1M GPU processes + 100k queued jobs (%d tasks) vs the config-2 calendar' % T,
@@ -462,7 +474,9 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
                                'frac_of_peak': join_bytes / (ms_join * 1e-3) / 1e9 / peak,
                                'note': 'two launches: K3 current-owner table over %d uuids, then the K5 join' % U},
             'job_tasks': {'ms': ms_task, 'tasks_per_s': T / (ms_task * 1e-3), 'interfering': int(tflags.sum().item())},
-            'gpu_slots': {'ms': ms_up, 'uuids_per_s': U / (ms_up * 1e-3)}}
+            'gpu_slots': {'ms': ms_up, 'uuids_per_s': U / (ms_up * 1e-3)},
+            'calendar_range': {'ms_host_call': ms_range, 'ranges': U, 'rows_returned': int(len(ids)),
+                               'note': 'th_conflict_sets(TH_MODE_INCLUSIVE), host arrays, wall clock incl. copies'}}
 
 
 def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup, barrier, max_over_ranks, world, peak,

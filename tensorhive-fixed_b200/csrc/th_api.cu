@@ -14,6 +14,35 @@ void th_set_error(const char *fmt, ...) {
 extern "C" const char *th_last_error(void) { return g_th_err; }
 extern "C" int th_version(void) { return TH_ABI_VERSION; }
 
+// ---- the library's stream-ordered pool ------------------------------------------------------------------
+#include <mutex>
+static std::mutex g_pool_mutex;
+static cudaMemPool_t g_pools[64] = {nullptr};
+
+cudaError_t th_malloc_async(void **p, size_t bytes, cudaStream_t st) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaMallocAsync(p, bytes, st);
+    cudaMemPool_t pool;
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mutex);
+        if (g_pools[dev] == nullptr) {
+            cudaMemPoolProps props = {};
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = dev;
+            e = cudaMemPoolCreate(&g_pools[dev], &props);
+            if (e != cudaSuccess) { g_pools[dev] = nullptr; return e; }
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(g_pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        pool = g_pools[dev];
+    }
+    return cudaMallocFromPoolAsync(p, bytes, pool, st);
+}
+
 // ---- ThScratch ---------------------------------------------------------------------------------------
 int ThScratch::alloc(void **out, size_t bytes) {
     if (count >= (int)(sizeof(ptrs) / sizeof(ptrs[0]))) {
@@ -22,9 +51,9 @@ int ThScratch::alloc(void **out, size_t bytes) {
     }
     if (bytes == 0) bytes = 16;
     void *p = nullptr;
-    cudaError_t e = cudaMallocAsync(&p, bytes, st);
+    cudaError_t e = th_malloc_async(&p, bytes, st);
     if (e != cudaSuccess) {
-        th_set_error("cudaMallocAsync(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
+        th_set_error("th_malloc_async(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
         return TH_ENOMEM;
     }
     ptrs[count++] = p;

@@ -254,6 +254,10 @@ struct ThScratch {
     int out(void *dst, size_t bytes, int mem, void **out_dev);
 };
 int th_copy_back(void *host_dst, const void *dev_src, size_t bytes, int mem, cudaStream_t st);
+// Stream-ordered scratch from the library's own memory pool on the CURRENT device.  The pool keeps what it has
+// allocated (release threshold = unlimited): with the device's default pool every stream synchronisation hands the
+// staging buffers back to the driver, and the next TH_MEM_HOST call pays for mapping them again.
+cudaError_t th_malloc_async(void **p, size_t bytes, cudaStream_t st);
 
 // ---- K1 internal entry (th_sort.cu) ----------------------------------------------------------------------
 // Sorts n records by (k1, k0) ascending, stable, using only the low k0_bits / k1_bits of each word.

@@ -61,8 +61,16 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const ThRec *__rest
         for (int p = 0; p < plan.npass; ++p) {
             const u32 mask = (1u << plan.bits[p]) - 1;
             const u32 d = valid ? rs_digit(r, plan.word[p], plan.shift[p], mask) : RS_RADIX;
-            const u32 peers = __match_any_sync(0xffffffffu, d);
-            if (valid && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&h[p * RS_RADIX + d], (u32)__popc(peers));
+            // High digits of a timestamp are the same for the whole warp: one atomic for all 32 lanes.  Otherwise
+            // the digits are spread out and plain shared-memory atomics rarely collide.  (__match_any_sync on every
+            // digit of every record made this kernel 3x the cost of a full sort pass.)
+            int same = 0;
+            __match_all_sync(0xffffffffu, d, &same);
+            if (same) {
+                if (lane == 0 && valid) atomicAdd(&h[p * RS_RADIX + d], 32u);
+            } else if (valid) {
+                atomicAdd(&h[p * RS_RADIX + d], 1u);
+            }
         }
     }
     __syncthreads();
@@ -165,22 +173,39 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const ThRec *__
     const u32 ds = wpre + inc - cnt;
     s.dstart[b] = ds;
 
-    // decoupled look-back over earlier tiles for digit b
+    // decoupled look-back over earlier tiles for digit b.  The walk is inherently sequential (stop at the first
+    // tile whose inclusive prefix is known), but the loads are not: eight predecessors are requested at once and
+    // then consumed in order, so a tile that starts in a wave of ~450 resident tiles pays ~1/8 of the round trips.
     u32 excl = 0;
     if (tile > 0) {
-        u32 t = tile - 1, spins = 0;
-        while (true) {
-            const u32 v = lookback[(size_t)t * RS_RADIX + b];
-            const u32 f = v >> 30;
-            if (f == 0) {
+        i64 t = (i64)tile - 1;
+        u32 spins = 0;
+        bool done = false;
+        while (!done) {
+            u32 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const i64 idx = t - k;
+                v[k] = RS_FLAG_INC + 0u;
+                if (idx >= 0) v[k] = lookback[(size_t)idx * RS_RADIX + b];
+            }
+            int used = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                if (done || used < k) continue;        // stop consuming after a not-ready or an inclusive entry
+                const u32 f = v[k] >> 30;
+                if (f == 0) continue;                  // not published yet: retry from here
+                excl += v[k] & RS_VAL_MASK;
+                used = k + 1;
+                if (f == 2) done = true;
+            }
+            t -= used;
+            if (!done && used < 8) {                   // hit an unpublished tile
                 if (++spins > RS_SPIN_LIMIT) { *err = 1; break; }
                 __nanosleep(40);
-                continue;
+            } else {
+                spins = 0;
             }
-            excl += v & RS_VAL_MASK;
-            if (f == 2) break;
-            --t;
-            spins = 0;
         }
         lookback[(size_t)tile * RS_RADIX + b] = RS_FLAG_INC | ((excl + cnt) & RS_VAL_MASK);
     }
@@ -252,15 +277,15 @@ int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **s
     const size_t ghist_bytes = (size_t)plan.npass * RS_RADIX * sizeof(u32);
     const size_t look_bytes = ((size_t)tiles * RS_RADIX + 4) * sizeof(u32);   // + ticket + err + pad
     u32 *ghist = nullptr, *look = nullptr;
-    TH_CUDA(cudaMallocAsync((void **)&ghist, ghist_bytes, st));
-    cudaError_t e = cudaMallocAsync((void **)&look, look_bytes, st);
+    TH_CUDA(th_malloc_async((void **)&ghist, ghist_bytes, st));
+    cudaError_t e = th_malloc_async((void **)&look, look_bytes, st);
     if (e != cudaSuccess) {
         cudaFreeAsync(ghist, st);
-        th_set_error("th_radix_sort: cudaMallocAsync(%zu) -> %s", look_bytes, cudaGetErrorString(e));
+        th_set_error("th_radix_sort: th_malloc_async(%zu) -> %s", look_bytes, cudaGetErrorString(e));
         return TH_ENOMEM;
     }
     int *err_dev = nullptr;
-    e = cudaMallocAsync((void **)&err_dev, sizeof(int), st);
+    e = th_malloc_async((void **)&err_dev, sizeof(int), st);
     int rc = TH_OK;
     int err_host = 0;
     do {
