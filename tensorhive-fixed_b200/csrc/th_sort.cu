@@ -107,7 +107,7 @@ struct RsSmem {
     u32 tile;
 };
 
-__global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const ThRec *__restrict__ in, ThRec *__restrict__ out,
+__global__ void __launch_bounds__(RS_THREADS, 3) rs_onesweep_kernel(const ThRec *__restrict__ in, ThRec *__restrict__ out,
                                                                  u32 n, int word, int shift, u32 mask,
                                                                  const u32 *__restrict__ ghist_excl, u32 *tile_counter,
                                                                  volatile u32 *lookback, int *err) {
@@ -174,24 +174,24 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const ThRec *__
     s.dstart[b] = ds;
 
     // decoupled look-back over earlier tiles for digit b.  The walk is inherently sequential (stop at the first
-    // tile whose inclusive prefix is known), but the loads are not: eight predecessors are requested at once and
-    // then consumed in order, so a tile that starts in a wave of ~450 resident tiles pays ~1/8 of the round trips.
+    // tile whose inclusive prefix is known), but the loads are not: four predecessors are requested at once and
+    // then consumed in order, so a tile that starts in a wave of ~450 resident tiles pays ~1/4 of the round trips.
     u32 excl = 0;
     if (tile > 0) {
         i64 t = (i64)tile - 1;
         u32 spins = 0;
         bool done = false;
         while (!done) {
-            u32 v[8];
+            u32 v[4];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < 4; ++k) {
                 const i64 idx = t - k;
                 v[k] = RS_FLAG_INC + 0u;
                 if (idx >= 0) v[k] = lookback[(size_t)idx * RS_RADIX + b];
             }
             int used = 0;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < 4; ++k) {
                 if (done || used < k) continue;        // stop consuming after a not-ready or an inclusive entry
                 const u32 f = v[k] >> 30;
                 if (f == 0) continue;                  // not published yet: retry from here
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const ThRec *__
                 if (f == 2) done = true;
             }
             t -= used;
-            if (!done && used < 8) {                   // hit an unpublished tile
+            if (!done && used < 4) {                   // hit an unpublished tile
                 if (++spins > RS_SPIN_LIMIT) { *err = 1; break; }
                 __nanosleep(40);
             } else {
