@@ -91,6 +91,7 @@ struct th_snapshot {
     ThCell *grid;  // [n_uuids * nb]
     i64 grid_t0;
     int grid_shift, grid_nb;
+    i64 max_id;                         // largest reservation id (bounds the digit plan when lists are id-sorted)
     i64 cap_nt, cap_uuids, cap_cells;   // allocated capacities: a reload that fits reuses the buffers
 };
 static inline ThGrid th_grid_of(const th_snapshot *h) {

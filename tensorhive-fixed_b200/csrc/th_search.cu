@@ -374,16 +374,44 @@ __device__ __forceinline__ i64 xs_block_exclusive(i64 v, i64 *wtot, i64 *total) 
     return pre + inc - v;
 }
 
-__global__ void __launch_bounds__(XS_THREADS) xs_tile_sum_kernel(const int *__restrict__ cnt, i64 m, i64 *tile_sum) {
+__global__ void __launch_bounds__(XS_THREADS) xs_tile_sum_kernel(const int *__restrict__ cnt, i64 m, i64 *tile_sum,
+                                                                 i64 *max_cnt) {
     __shared__ i64 wtot[XS_THREADS / 32];
     const i64 j0 = (i64)blockIdx.x * XS_TILE + (i64)threadIdx.x * XS_IPT;
     i64 s = 0;
+    int mx = 0;
 #pragma unroll
     for (int k = 0; k < XS_IPT; ++k)
-        if (j0 + k < m) s += cnt[j0 + k];
+        if (j0 + k < m) { const int c = cnt[j0 + k]; s += c; mx = c > mx ? c : mx; }
     i64 total;
     xs_block_exclusive(s, wtot, &total);
     if (threadIdx.x == 0) tile_sum[blockIdx.x] = total;
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(max_cnt, (i64)mx);     // longest single list (picks the id-ordering path)
+}
+
+// long lists: records {k0 = id, k1 = query, idx = slot} for K1, and the scatter back in sorted order
+__global__ void __launch_bounds__(256) k2_sets_rec_kernel(i64 m, const i64 *__restrict__ offsets,
+                                                         const i64 *__restrict__ tmp_ids, ThRec *__restrict__ rec) {
+    const int lane = threadIdx.x & 31;
+    const i64 wstride = (i64)gridDim.x * (blockDim.x / 32);
+    for (i64 q = (i64)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5); q < m; q += wstride) {
+        const i64 o0 = offsets[q], o1 = offsets[q + 1];
+        for (i64 k = o0 + lane; k < o1; k += 32) {
+            ThRec r;
+            r.k0 = (u64)tmp_ids[k]; r.k1 = (u32)q; r.idx = (u32)k;
+            rec[k] = r;
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k2_sets_unrec_kernel(i64 total, const ThRec *__restrict__ rec,
+                                                           const u8 *__restrict__ tmp_canc, i64 *__restrict__ out_ids,
+                                                           u8 *__restrict__ out_canc) {
+    for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (i64)gridDim.x * blockDim.x) {
+        const ThRec r = rec[k];          // sorted by (query, id): position k of the CSR
+        out_ids[k] = (i64)r.k0;
+        out_canc[k] = tmp_canc[r.idx];
+    }
 }
 
 __global__ void __launch_bounds__(XS_THREADS) xs_carry_kernel(i64 *tile_sum, i64 tiles, i64 *grand_total) {
@@ -534,15 +562,17 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     const i64 tiles = (m + XS_TILE - 1) / XS_TILE;
     i64 *d_tile, *d_total;
     TH_TRY(sc.alloc((void **)&d_tile, 8 * (size_t)tiles));
-    TH_TRY(sc.alloc((void **)&d_total, 8));
-    xs_tile_sum_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile);
+    TH_TRY(sc.alloc((void **)&d_total, 16));       // [0] = total rows, [1] = longest list
+    TH_CUDA(cudaMemsetAsync(d_total, 0, 16, st));
+    xs_tile_sum_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_total + 1);
     xs_carry_kernel<<<1, XS_THREADS, 0, st>>>(d_tile, tiles, d_total);
     xs_write_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_total, (i64 *)d_off);
     TH_CUDA(cudaGetLastError());
-    i64 total = 0;
-    TH_CUDA(cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, st));
+    i64 tot2[2] = {0, 0};
+    TH_CUDA(cudaMemcpyAsync(tot2, d_total, 16, cudaMemcpyDeviceToHost, st));
     TH_TRY(th_copy_back(out_offsets, d_off, 8 * (zm + 1), mem, st));
     TH_CUDA(cudaStreamSynchronize(st));
+    const i64 total = tot2[0], longest = tot2[1];
     *out_needed = total;
     if (total > capacity) {
         th_set_error("th_conflict_sets: %lld result rows exceed capacity %lld", (long long)total, (long long)capacity);
@@ -561,8 +591,22 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
         TH_TRY(sc.alloc((void **)&t_canc, (size_t)total));
         k2_sets_fill_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
                                                           (const i64 *)d_off, t_ids, t_canc);
-        k2_sets_order_kernel<<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
-                                                           (u8 *)d_canc);
+        if (longest <= 64 || total >= (1ll << 30) || m >= (1ll << 32)) {
+            // short lists: rank by counting inside the warp (c^2 / 32 compares per list)
+            k2_sets_order_kernel<<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
+                                                               (u8 *)d_canc);
+        } else {
+            // calendar views return thousands of rows per uuid: sort all of them by (query, id) with K1 instead
+            ThRec *ra, *rb, *sorted;
+            TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * (size_t)total));
+            TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * (size_t)total));
+            k2_sets_rec_kernel<<<wgrid, 256, 0, st>>>(m, (const i64 *)d_off, t_ids, ra);
+            TH_CUDA(cudaGetLastError());
+            int passes = 0;
+            TH_TRY(th_radix_sort(ra, rb, total, th_bits_for((u64)h->max_id), th_bits_for((u64)(m - 1)), &sorted, &passes, st));
+            k2_sets_unrec_kernel<<<th_grid_for(total, 256 * 4, 8), 256, 0, st>>>(total, sorted, t_canc, (i64 *)d_ids,
+                                                                                 (u8 *)d_canc);
+        }
     }
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_ids, d_ids, 8 * (size_t)total, mem, st));

@@ -371,6 +371,7 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
         h->cap_uuids = n_uuids + 1;
     }
     h->n_uuids = n_uuids;
+    h->max_id = 0;
     size_t bytes = sizeof(int) * (size_t)h->cap_uuids + (sizeof(ThP1) * 4 + sizeof(u32)) * (size_t)h->cap_nt;
 
     ThScratch sc(st);
@@ -409,6 +410,7 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
         TH_REQUIRE(stats.min_start > TH_I64_MIN, "th_snapshot_load: start_us == INT64_MIN is reserved");
         min_start = stats.min_start;
         max_start = stats.max_start;
+        h->max_id = stats.max_id;
 
         ThRec *ra = nullptr, *rb = nullptr;
         TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));

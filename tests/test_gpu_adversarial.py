@@ -1,0 +1,140 @@
+"""Every entry point against the SQL oracle (the reference's WHERE clauses through sqlite3) on small, deliberately
+nasty calendars: timestamps drawn from a tiny set (ties and touching boundaries everywhere), nested and duplicate
+intervals, zero-length rows, NULL/0/1 cancel flags, ids with gaps and in random order, uuids without rows."""
+import datetime as dt
+
+import numpy as np
+import pytest
+
+from helpers import csr_to_lists
+
+pytestmark = pytest.mark.gpu
+
+
+def _world(seed):
+    from tensorhive_fixed_b200 import synth
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(0, 120))
+    u = int(rng.integers(1, 6))
+    grid = synth.T0_US + np.arange(12) * 1000
+    ids = rng.permutation(np.arange(1, 4 * n + 1))[:n].astype(np.int64)
+    uu = rng.integers(0, u, size=n).astype(np.int64)
+    a = rng.choice(grid, size=n)
+    b = rng.choice(grid, size=n)
+    s, e = np.minimum(a, b), np.maximum(a, b)          # zero-length rows allowed
+    raw = rng.choice([-1, 0, 1], size=n, p=[0.4, 0.3, 0.3])
+    owner = rng.integers(1, 5, size=n).astype(np.int64)
+    cal = {'id': ids, 'uuid_id': uu, 'start': s.astype(np.int64), 'end': e.astype(np.int64), 'owner': owner,
+           'cancelled': (raw == 1).astype(np.uint8), 'cancelled_raw': raw, 'n_uuids': u}
+    return cal, grid, rng
+
+
+def _sql(cal):
+    from oracle.sql_ref import SqlCalendar
+    from tensorhive_fixed_b200 import synth
+    rows = [(int(cal['id'][i]), synth.uuid_string(int(cal['uuid_id'][i])), int(cal['start'][i]), int(cal['end'][i]),
+             int(cal['owner'][i]), None if cal['cancelled_raw'][i] < 0 else int(cal['cancelled_raw'][i]))
+            for i in range(len(cal['id']))]
+    return SqlCalendar(rows)
+
+
+@pytest.mark.parametrize('seed', range(40))
+def test_every_entry_point_against_the_sql_text(lib_built, seed):
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle.sql_ref import EPOCH
+    cal, grid, rng = _world(seed)
+    sql = _sql(cal)
+    u = cal['n_uuids']
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=u)
+    name = lambda k: synth.uuid_string(int(k))
+    owner_of = {int(i): int(o) for i, o in zip(cal['id'], cal['owner'])}
+    canc_of = {int(i): int(c) for i, c in zip(cal['id'], cal['cancelled'])}
+
+    # candidates on the same tiny time grid (+-1 us), with and without a self id, some for unknown uuids
+    m = 150
+    qu = rng.integers(-1, u + 1, size=m).astype(np.int64)
+    qa = rng.choice(grid, size=m) + rng.integers(-1, 2, size=m)
+    qb = rng.choice(grid, size=m) + rng.integers(-1, 2, size=m)
+    qs, qe = np.minimum(qa, qb).astype(np.int64), np.maximum(qa, qb).astype(np.int64)
+    pool = np.concatenate([cal['id'], [10_000_000]]) if len(cal['id']) else np.array([10_000_000])
+    qf = np.where(rng.random(m) < 0.5, -1, rng.choice(pool, size=m)).astype(np.int64)
+
+    bits = snap.conflict_bitmap(qu, qs, qe, qf)
+    off, ids, canc = snap.conflict_sets(qu, qs, qe, qf, th.MODE_STRICT)
+    lists = csr_to_lists(off, ids)
+    off2, ids2, canc2 = snap.conflict_sets(qu, qs, qe, None, th.MODE_INCLUSIVE)
+    lists2 = csr_to_lists(off2, ids2)
+    incl_bits = snap.conflict_bitmap(qu, qs, qe, None, th.MODE_INCLUSIVE)
+    for i in range(m):
+        known = 0 <= qu[i] < u
+        rows = sql.would_interfere_rows(name(qu[i]), int(qs[i]), int(qe[i]), None if qf[i] < 0 else int(qf[i])) if known else []
+        assert lists[i] == [r[0] for r in rows], ('strict list', i)
+        assert bool(bits[i]) == any(not c for _, c in rows), ('verdict', i)
+        if known:
+            want = sorted(sql.filter_by_uuids_and_time_range([name(qu[i])], EPOCH + dt.timedelta(microseconds=int(qs[i])),
+                                                             EPOCH + dt.timedelta(microseconds=int(qe[i]))))
+        else:
+            want = []
+        assert lists2[i] == want, ('range list', i)
+        assert bool(incl_bits[i]) == bool(want)
+    assert [canc_of[int(x)] for x in ids] == [int(c) for c in canc]
+
+    uu = np.arange(-1, u + 1, dtype=np.int64)
+    for now in [int(grid[0]) - 5, int(grid[3]), int(grid[3]) + 1, int(grid[7]) - 1, int(grid[-1]), int(grid[-1]) + 7]:
+        res, own = snap.current_owner(now)
+        for k in range(u):
+            cur = sql.current_events(now, name(k))
+            assert (cur[0] if cur else -1) == res[k]
+            assert (owner_of[cur[0]] if cur else -1) == own[k]
+        for period in (0, 1, 1000, 2500, 100_000):
+            fid, fst, fow, cnt = snap.upcoming(now, period, uu)
+            offu, idu, _ = snap.conflict_sets(uu, np.full(len(uu), now), np.full(len(uu), now + period), None, th.MODE_UPCOMING)
+            ulists = csr_to_lists(offu, idu)
+            for j, k in enumerate(uu):
+                want = sql.upcoming_events_for_resource(name(k), now, period) if 0 <= k < u else []
+                assert ulists[j] == want, ('upcoming', now, period, k)
+                assert cnt[j] == len(want)
+                assert fid[j] == (want[0] if want else -1)
+            for test, fn in ((th.OWNER_ANY, lambda o, w: len(w) > 0), (th.OWNER_OTHER, lambda o, w: any(owner_of[x] != o for x in w)),
+                             (th.OWNER_SAME, lambda o, w: any(owner_of[x] == o for x in w))):
+                to = rng.integers(1, 5, size=len(uu)).astype(np.int64)
+                flags = snap.upcoming_owner_flags(now, period, uu, to, test)
+                for j, k in enumerate(uu):
+                    w = sql.upcoming_events_for_resource(name(k), now, period) if 0 <= k < u else []
+                    assert bool(flags[j]) == fn(int(to[j]), w)
+        for strict in (False, True):
+            pu = rng.integers(-1, u + 1, size=60).astype(np.int64)
+            po = rng.integers(-2, 5, size=60).astype(np.int64)
+            fl, rid = snap.violation_join(now, strict, pu, po)
+            for j in range(60):
+                cur = sql.current_events(now, name(pu[j])) if 0 <= pu[j] < u else []
+                if cur:
+                    want = (po[j] != owner_of[cur[0]], cur[0] if po[j] != owner_of[cur[0]] else -1)
+                else:
+                    want = (strict, -1)
+                assert (bool(fl[j]), int(rid[j])) == (bool(want[0]), int(want[1]))
+    snap.close()
+
+
+def test_long_lists_take_the_radix_path(lib_built):
+    """One uuid with 30 000 rows and a whole-calendar range: the id ordering of the list goes through K1."""
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    cal = synth.make_calendar(30_000, 2, seed=12)
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=2)
+    qu = np.array([0, 1, 0, 5], np.int64)
+    qs = np.array([cal['start'].min(), cal['start'].min(), int(np.median(cal['start'])), 0], np.int64)
+    qe = np.array([cal['end'].max(), int(np.median(cal['start'])), int(np.median(cal['start'])) + synth.DAY_US, 10], np.int64)
+    for mode, bmode in ((th.MODE_INCLUSIVE, brute.INCLUSIVE), (th.MODE_STRICT, brute.STRICT)):
+        off, ids, canc = snap.conflict_sets(qu, qs, qe, np.full(4, -1, np.int64) if mode == th.MODE_STRICT else None, mode)
+        got = csr_to_lists(off, ids)
+        want = brute.conflict_sets(cal, qu, qs, qe, np.full(4, -1, np.int64), bmode)
+        assert got == want
+        assert len(got[0]) > 10_000 and got[0] == sorted(got[0])
+        flag = {int(i): int(c) for i, c in zip(cal['id'], cal['cancelled'])}
+        assert [flag[int(i)] for i in ids] == [int(c) for c in canc]
+    snap.close()
