@@ -333,6 +333,29 @@ def run_ours(args):
         a.record(); graph.replay(); b.record()
         torch.cuda.synchronize()
         k_ms_warm = a.elapsed_time(b) / 20.0
+    # service steady state for context: the snapshot stays resident while 8 DIFFERENT query batches (8 x 32 MB > L2)
+    # stream through, no flush -- queries come from HBM every time, the index mostly from L2
+    k_ms_stream = None
+    if dist is None and N_QUERIES <= 2_000_000:
+        batches = [[torch.roll(t, shifts=1000 * (j + 1)) for t in qd] for j in range(8)]
+        outs_b = [torch.empty_like(words) for _ in range(8)]
+        g8 = torch.cuda.CUDAGraph()        # one graph = the 8 batches back to back: no CPU launch gaps inside
+        with torch.cuda.graph(g8):
+            cap = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            for j in range(8):
+                native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, batches[j][0].data_ptr(), batches[j][1].data_ptr(),
+                                                    batches[j][2].data_ptr(), batches[j][3].data_ptr(), 0,
+                                                    outs_b[j].data_ptr(), 1, cap))
+        flush.sum()
+        g8.replay()
+        reps = []
+        for _ in range(5):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); g8.replay(); b.record()
+            torch.cuda.synchronize()
+            reps.append(a.elapsed_time(b) / 8.0)
+        k_ms_stream = float(np.median(reps))
+        del batches, outs_b
     peak, peak_src = _peaks()
     alg_bytes = N_QUERIES * 32 + N_ROWS * 25 + 8 * (N_UUIDS + 1) + N_QUERIES // 8
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
@@ -390,6 +413,7 @@ def run_ours(args):
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,
                          'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes, 'kernel_ms': k_ms, 'kernel_ms_warm_l2': k_ms_warm,
+                         'kernel_ms_streaming_8_batches_no_flush': k_ms_stream,
                          'frac_of_nominal_8TBs': achieved / 8000.0},
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
                               'radix_passes': info['radix_passes'], 'device_bytes': info['device_bytes']}}
