@@ -408,7 +408,7 @@ def run_ours(args):
                     'ms_per_step': 1e3 * e2e_s / steps,
                     'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
-            'gpu_launches': steps * (2 if px is not None else 1),      # K2 (+ the unpack kernel of the fused exchange)
+            'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,
                          'peak_source': peak_src,

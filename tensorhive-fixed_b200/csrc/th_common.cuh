@@ -110,6 +110,13 @@ struct ThPeerOut {
     i64 word_off;                // rank * words_per_rank
     u64 *dst[TH_MAX_PEERS];      // slot array (this step's generation) of every rank, peer-mapped
     u32 *flags[TH_MAX_PEERS];    // th_peer_barrier only: barrier flag array of every rank
+    // receive half inside the same kernel (unpack != 0): this rank's own slots / compact output / expectations
+    int unpack;
+    i64 wpr;
+    const volatile u64 *my_slots;
+    u32 *my_out;
+    int *err;
+    i64 expect[TH_MAX_PEERS];    // bitmap words each rank contributes this step
 };
 struct ThPeerCounts { i64 words[TH_MAX_PEERS]; };   // bitmap words each rank contributes this step
 struct th_peer {

@@ -208,6 +208,27 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             for (int j = threadIdx.x; j < cnt; j += BM_THREADS) dst[j] = (u64)swords[j] | tag;
         }
     }
+    if (po.n > 0 && po.unpack) {
+        // Receive half, fused: a CTA that has sent its own words turns to a share of the incoming slots, waits for
+        // each to show this step's epoch and writes the compact word.  Early finishers start polling while the
+        // stragglers (here and on the other GPUs) still compute, and no second launch sits on the critical path.
+        const i64 total = (i64)po.n * po.wpr;
+        for (i64 idx = (i64)blockIdx.x * BM_THREADS + threadIdx.x; idx < total; idx += (i64)gridDim.x * BM_THREADS) {
+            const int r = (int)(idx / po.wpr);
+            const i64 j = idx - (i64)r * po.wpr;
+            u32 w = 0;
+            if (j < po.expect[r]) {
+                u64 v = po.my_slots[idx];
+                for (u64 spins = 0; (u32)(v >> 32) != po.epoch; ++spins) {
+                    if (spins > (1ull << 22)) { *po.err = 1; break; }
+                    __nanosleep(64);
+                    v = po.my_slots[idx];
+                }
+                w = (u32)v;
+            }
+            po.my_out[idx] = w;
+        }
+    }
 }
 
 // receivers: poll every expected slot until it carries this step's epoch, and write the compact words the caller
@@ -512,6 +533,7 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     TH_TRY(sc.out(out_bits_u32, 4 * words, mem, &d_bits));
     ThPeerOut none;
     none.n = 0;
+    none.unpack = 0;
     TH_TRY(k2_launch(h, m, d_u, d_s, d_e, d_f, mode, (u32 *)d_bits, none, st));
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_bits_u32, d_bits, 4 * words, mem, st));
@@ -670,9 +692,18 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
     for (int p = 0; p < world; ++p) {
         po.dst[p] = th_peer_slots(peer->peer_base[p], world, wpr, parity);
         po.flags[p] = nullptr;
+        po.expect[p] = peer->counts.words[p];
     }
+    // wait = 1: the receive half runs inside the K2 kernel (needs every rank's kernel to be running at the same time,
+    // i.e. one rank per GPU); wait = 0: only the send half is enqueued and th_peer_wait adds the unpack kernel later
+    // (ranks emulated on one GPU, where a kernel must never wait for one that is queued behind it).
+    po.unpack = (wait && m > 0) ? 1 : 0;
+    po.wpr = wpr;
+    po.my_slots = th_peer_slots(peer->base, world, wpr, parity);
+    po.my_out = th_peer_out(peer, parity);
+    po.err = (int *)th_peer_misc(peer->base, world, wpr);
     if (m > 0) TH_TRY(k2_launch(h, m, q_uuid, q_start, q_end, q_self_id, mode, nullptr, po, st));
-    if (wait) TH_TRY(k2_launch_unpack(peer, st));
+    if (wait && m == 0) TH_TRY(k2_launch_unpack(peer, st));
     if (out_gathered) *out_gathered = th_peer_out(peer, parity);
     return TH_OK;
 }
@@ -698,7 +729,7 @@ extern "C" int th_peer_barrier(th_peer *peer, void *stream) {
     TH_CUDA(cudaGetDevice(&prev));
     if (prev != peer->device) TH_CUDA(cudaSetDevice(peer->device));
     ThPeerOut po;
-    po.n = peer->world; po.rank = peer->rank; po.epoch = ++peer->bepoch; po.word_off = 0;
+    po.n = peer->world; po.rank = peer->rank; po.epoch = ++peer->bepoch; po.word_off = 0; po.unpack = 0;
     for (int p = 0; p < peer->world; ++p) {
         po.dst[p] = nullptr;
         po.flags[p] = th_peer_bflags(peer->peer_base[p], peer->world, peer->words_per_rank);
