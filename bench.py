@@ -290,6 +290,17 @@ def run_ours(args):
         snap.load(*d_cal, n_uuids=N_UUIDS)
         ld.append(1e3 * (time.perf_counter() - t0))
     info = snap.info()
+    # maintenance from a delta (1000 changed rows): survivors gathered on the device, no table re-upload
+    up = {k: cal[k][:1000].copy() for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')}
+    up['end'] = up['end'] + 1
+    dl = []
+    for _ in range(4):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        snap.apply_delta(snap, N_UUIDS, up['id'], up['uuid_id'], up['start'], up['end'], up['owner'], up['cancelled'],
+                         np.zeros(0, np.int64))
+        dl.append(1e3 * (time.perf_counter() - t0))
+    snap.load(*d_cal, n_uuids=N_UUIDS)      # back to the benchmark table
 
     for _ in range(warmup):
         flush.sum()
@@ -416,6 +427,7 @@ def run_ours(args):
                          'kernel_ms_streaming_8_batches_no_flush': k_ms_stream,
                          'frac_of_nominal_8TBs': achieved / 8000.0},
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
+                              'ms_apply_delta_1000_rows_host_arrays': float(np.median(dl[1:])),
                               'radix_passes': info['radix_passes'], 'device_bytes': info['device_bytes']}}
 
     # ---- BASELINE config 4: ProtectionService + job-queue sweep over the same calendar ---------------------------

@@ -72,6 +72,17 @@ int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *
                      const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
                      const uint8_t *cancelled_u8, int mem, void *stream);
 
+/* Snapshot maintenance.  The reference commits every change through CRUDModel.save /
+ * destroy (tensorhive/models/CRUDModel.py:21-50); instead of re-sending the whole table after each commit, send the
+ * delta: `dst` becomes `src` without the rows whose id is upserted or deleted, plus the upserted rows (insert, update
+ * and cancel are all upserts), re-indexed on the device.  Only the delta crosses PCIe.  dst may be src (in place; then
+ * no query may run on it meanwhile) or a second handle (readers keep using src until the caller swaps).  n_uuids may
+ * grow but not shrink. */
+int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src, int64_t n_uuids, int64_t n_upsert, const int64_t *id,
+                            const int64_t *uuid_id, const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
+                            const uint8_t *cancelled_u8, int64_t n_delete, const int64_t *delete_ids, int mem,
+                            void *stream);
+
 /* Size / bookkeeping of the loaded table. radix_passes = digit passes the last load ran. */
 int th_snapshot_info(const th_snapshot *h, int64_t *n, int64_t *n_uuids, int64_t *device_bytes,
                      int64_t *radix_passes);

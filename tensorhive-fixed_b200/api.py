@@ -121,6 +121,18 @@ class Snapshot:
         self.n, self.n_uuids = n, int(n_uuids)
         return self
 
+    def apply_delta(self, src: 'Snapshot', n_uuids: int, id, uuid_id, start, end, owner, cancelled, delete_ids) -> 'Snapshot':
+        """Make this snapshot = ``src`` minus upserted/deleted ids plus the upserted rows (``self`` may be ``src``).
+        Only the delta is uploaded; the survivors are gathered and re-indexed on the device."""
+        a = _Args(id, uuid_id, start, end, owner, cancelled, delete_ids)
+        n_up, n_del = int(len(id)), int(len(delete_ids))
+        native.check(self._lib.th_snapshot_apply_delta(self._h, src._h, int(n_uuids), n_up, a.inp(id), a.inp(uuid_id),
+                                                       a.inp(start), a.inp(end), a.inp(owner), a.inp(cancelled, np.uint8),
+                                                       n_del, a.inp(delete_ids), a.mem, a.stream()))
+        info = self.info()
+        self.n, self.n_uuids = info['n'], info['n_uuids']
+        return self
+
     def info(self) -> dict:
         v = [C.c_int64(0) for _ in range(4)]
         native.check(self._lib.th_snapshot_info(self._h, *[C.byref(x) for x in v]))

@@ -76,6 +76,7 @@ class Calendar:
         self._lock = threading.Lock()
         self.version = 0
         self._state = None
+        self._spares = []
         self.refresh(rows)
 
     # -- building -------------------------------------------------------------------------------------------
@@ -120,6 +121,44 @@ class Calendar:
         with self._lock:
             return self._state
 
+    def apply_delta(self, upserts: Iterable = (), deleted_ids: Iterable[int] = ()) -> None:
+        """Incremental maintenance after a commit (CRUDModel.save / destroy, tensorhive/models/CRUDModel.py:21-50):
+        ``upserts`` are new or changed rows (a cancel is a changed row), ``deleted_ids`` rows that were destroyed.
+        Only the delta is sent to the GPU; the new snapshot is built in a spare handle from the current one and then
+        swapped in, so concurrent readers are never blocked (three handles rotate: a reader would have to outlive two
+        further commits to see its handle reused)."""
+        upserts = list(upserts)
+        deleted = [int(i) for i in deleted_ids]
+        with self._lock:
+            snap, uuids, by_id = self._state
+        new_uuids = UuidDictionary()
+        new_uuids.code = dict(uuids.code)
+        new_uuids.names = list(uuids.names)
+        new_by_id = dict(by_id)
+        n = len(upserts)
+        cid = np.empty(n, np.int64); cuu = np.empty(n, np.int64); cst = np.empty(n, np.int64)
+        cen = np.empty(n, np.int64); cow = np.empty(n, np.int64); cca = np.empty(n, np.uint8)
+        for k, r in enumerate(upserts):
+            rid = int(self._get(r, 'id'))
+            cid[k] = rid
+            cuu[k] = new_uuids.add(self._get(r, 'resource_id'))
+            s, e = self._get(r, 'start'), self._get(r, 'end')
+            cst[k] = dt_to_us(s) if isinstance(s, _dt.datetime) else int(s)
+            cen[k] = dt_to_us(e) if isinstance(e, _dt.datetime) else int(e)
+            uid = self._get(r, 'user_id')
+            cow[k] = int(uid) if (uid is not None and (not self.users or uid in self.users)) else -1
+            raw = self._get(r, 'is_cancelled')
+            cca[k] = 1 if (raw is not None and raw) else 0
+            new_by_id[rid] = r
+        for i in deleted:
+            new_by_id.pop(i, None)
+        spare = self._spares.pop(0) if len(self._spares) >= 2 else Snapshot(self.device)
+        spare.apply_delta(snap, max(len(new_uuids), 1), cid, cuu, cst, cen, cow, cca, np.array(deleted, np.int64))
+        with self._lock:
+            self._spares.append(snap)
+            self._state = (spare, new_uuids, new_by_id)
+            self.version += 1
+
     # -- helpers ----------------------------------------------------------------------------------------------
     def now_us(self) -> int:
         return dt_to_us(self.clock())
@@ -156,3 +195,6 @@ class Calendar:
         st = self.state()
         if st:
             st[0].close()
+        for s in self._spares:
+            s.close()
+        self._spares = []

@@ -267,6 +267,10 @@ int th_copy_back(void *host_dst, const void *dev_src, size_t bytes, int mem, cud
 // staging buffers back to the driver, and the next TH_MEM_HOST call pays for mapping them again.
 cudaError_t th_malloc_async(void **p, size_t bytes, cudaStream_t st);
 
+// exclusive scan of int32 counts into int64 offsets[m + 1] (th_search.cu); totals[0] = sum, totals[1] = max count.
+// All pointers are device memory; `totals` must hold two i64.  Enqueued on `st`, no synchronisation.
+int th_exclusive_scan_i32(const int *d_cnt, i64 m, i64 *d_offsets, i64 *d_totals, ThScratch &sc, cudaStream_t st);
+
 // ---- K1 internal entry (th_sort.cu) ----------------------------------------------------------------------
 // Sorts n records by (k1, k0) ascending, stable, using only the low k0_bits / k1_bits of each word.
 // `a` holds the input; the sorted result is returned in *sorted (either a or b).  `passes` gets the

@@ -509,6 +509,19 @@ static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d
     return TH_OK;
 }
 
+int th_exclusive_scan_i32(const int *d_cnt, i64 m, i64 *d_offsets, i64 *d_totals, ThScratch &sc, cudaStream_t st) {
+    const i64 tiles = (m + XS_TILE - 1) / XS_TILE;
+    i64 *d_tile;
+    TH_TRY(sc.alloc((void **)&d_tile, 8 * (size_t)(tiles > 0 ? tiles : 1)));
+    TH_CUDA(cudaMemsetAsync(d_totals, 0, 16, st));
+    if (m == 0) { TH_CUDA(cudaMemsetAsync(d_offsets, 0, 8, st)); return TH_OK; }
+    xs_tile_sum_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_totals + 1);
+    xs_carry_kernel<<<1, XS_THREADS, 0, st>>>(d_tile, tiles, d_totals);
+    xs_write_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_totals, d_offsets);
+    TH_CUDA(cudaGetLastError());
+    return TH_OK;
+}
+
 extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t *q_uuid, const int64_t *q_start,
                                   const int64_t *q_end, const int64_t *q_self_id, int mode, uint32_t *out_bits_u32,
                                   int mem, void *stream) {
@@ -581,15 +594,9 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     k2_sets_count_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
                                                        (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
     TH_CUDA(cudaGetLastError());
-    const i64 tiles = (m + XS_TILE - 1) / XS_TILE;
-    i64 *d_tile, *d_total;
-    TH_TRY(sc.alloc((void **)&d_tile, 8 * (size_t)tiles));
+    i64 *d_total;
     TH_TRY(sc.alloc((void **)&d_total, 16));       // [0] = total rows, [1] = longest list
-    TH_CUDA(cudaMemsetAsync(d_total, 0, 16, st));
-    xs_tile_sum_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_total + 1);
-    xs_carry_kernel<<<1, XS_THREADS, 0, st>>>(d_tile, tiles, d_total);
-    xs_write_kernel<<<(unsigned)tiles, XS_THREADS, 0, st>>>(d_cnt, m, d_tile, d_total, (i64 *)d_off);
-    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_exclusive_scan_i32(d_cnt, m, (i64 *)d_off, d_total, sc, st));
     i64 tot2[2] = {0, 0};
     TH_CUDA(cudaMemcpyAsync(tot2, d_total, 16, cudaMemcpyDeviceToHost, st));
     TH_TRY(th_copy_back(out_offsets, d_off, 8 * (zm + 1), mem, st));

@@ -327,6 +327,59 @@ __global__ void __launch_bounds__(256) ex_export_kernel(i64 nt, i64 n_uuids, con
         for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u <= n_uuids; u += stride) o_seg[u] = seg[u] - u;
 }
 
+// ---- delta maintenance: survivors of the old table + upserted rows -> columns for a device-side rebuild -----------
+__global__ void __launch_bounds__(256) dl_killrec_kernel(const i64 *__restrict__ up_id, i64 n_up, const i64 *__restrict__ del_id,
+                                                        i64 n_del, ThRec *rec) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n_up + n_del; i += (i64)gridDim.x * blockDim.x) {
+        ThRec r;
+        r.k0 = (u64)(i < n_up ? up_id[i] : del_id[i - n_up]); r.k1 = 0; r.idx = (u32)i;
+        rec[i] = r;
+    }
+}
+// keep[pos] = 1 for every real row whose id is neither replaced nor deleted
+__global__ void __launch_bounds__(256) dl_keep_kernel(i64 nt, const u32 *__restrict__ uuid, const int *__restrict__ seg,
+                                                     const ThP3 *__restrict__ p3, const ThRec *__restrict__ kill, i64 n_kill,
+                                                     int *keep) {
+    for (i64 pos = (i64)blockIdx.x * blockDim.x + threadIdx.x; pos < nt; pos += (i64)gridDim.x * blockDim.x) {
+        int k = 0;
+        if ((i64)seg[uuid[pos]] != pos) {
+            const u64 id = (u64)th_idc_id(p3[pos].idc);
+            i64 lo = 0, hi = n_kill;
+            while (lo < hi) {
+                const i64 mid = (lo + hi) >> 1;
+                if (kill[mid].k0 < id) lo = mid + 1; else hi = mid;
+            }
+            k = !(lo < n_kill && kill[lo].k0 == id);
+        }
+        keep[pos] = k;
+    }
+}
+__global__ void __launch_bounds__(256) dl_gather_kernel(i64 nt, const int *__restrict__ keep, const i64 *__restrict__ off,
+                                                       const ThP1 *__restrict__ p1, const ThP3 *__restrict__ p3,
+                                                       const ThP4 *__restrict__ p4, const u32 *__restrict__ uuid, i64 *o_id,
+                                                       i64 *o_uuid, i64 *o_start, i64 *o_end, i64 *o_owner, u8 *o_canc) {
+    for (i64 pos = (i64)blockIdx.x * blockDim.x + threadIdx.x; pos < nt; pos += (i64)gridDim.x * blockDim.x) {
+        if (!keep[pos]) continue;
+        const i64 j = off[pos];
+        const ThP3 e = p3[pos];
+        o_id[j] = th_idc_id(e.idc);
+        o_uuid[j] = uuid[pos];
+        o_start[j] = p1[pos].start;
+        o_end[j] = e.end;
+        o_owner[j] = p4[pos].owner;
+        o_canc[j] = th_idc_cancelled(e.idc) ? 1 : 0;
+    }
+}
+__global__ void __launch_bounds__(256) dl_append_kernel(i64 n_up, i64 base, const i64 *__restrict__ id, const i64 *__restrict__ uuid,
+                                                       const i64 *__restrict__ start, const i64 *__restrict__ end,
+                                                       const i64 *__restrict__ owner, const u8 *__restrict__ canc, i64 *o_id,
+                                                       i64 *o_uuid, i64 *o_start, i64 *o_end, i64 *o_owner, u8 *o_canc) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += (i64)gridDim.x * blockDim.x) {
+        o_id[base + i] = id[i]; o_uuid[base + i] = uuid[i]; o_start[base + i] = start[i]; o_end[base + i] = end[i];
+        o_owner[base + i] = owner[i]; o_canc[base + i] = canc[i];
+    }
+}
+
 struct DeviceGuard {
     int prev;
     bool ok;
@@ -528,4 +581,92 @@ extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uu
     TH_TRY(th_copy_back(seg_offsets, d_seg, 8 * zu, mem, st));
     if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
     return TH_OK;
+}
+
+
+// Snapshot maintenance without re-sending the table (the reference commits every write
+// through CRUDModel.save / destroy, tensorhive/models/CRUDModel.py:21-50): `dst` becomes `src` minus the rows whose
+// id is upserted or deleted, plus the upserted rows.  Only the delta crosses PCIe; survivors are gathered from the
+// source snapshot on the device and the table is re-indexed there (same K1 + index build as a load).  dst may be src.
+extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src, int64_t n_uuids, int64_t n_upsert,
+                                       const int64_t *id, const int64_t *uuid_id, const int64_t *start_us,
+                                       const int64_t *end_us, const int64_t *owner, const uint8_t *cancelled_u8,
+                                       int64_t n_delete, const int64_t *delete_ids, int mem, void *stream) {
+    TH_REQUIRE(dst != nullptr && src != nullptr && src->loaded, "th_snapshot_apply_delta: source snapshot not loaded");
+    TH_REQUIRE(dst->device == src->device, "th_snapshot_apply_delta: snapshots live on different devices");
+    TH_REQUIRE(n_upsert >= 0 && n_delete >= 0, "th_snapshot_apply_delta: negative size");
+    TH_REQUIRE(n_uuids >= src->n_uuids, "th_snapshot_apply_delta: n_uuids=%lld is smaller than the source's %lld",
+               (long long)n_uuids, (long long)src->n_uuids);
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_snapshot_apply_delta: bad mem flag %d", mem);
+    TH_REQUIRE(n_upsert == 0 || (id && uuid_id && start_us && end_us && owner && cancelled_u8),
+               "th_snapshot_apply_delta: a column pointer is NULL");
+    TH_REQUIRE(n_delete == 0 || delete_ids, "th_snapshot_apply_delta: delete_ids is NULL");
+    DeviceGuard guard(src->device);
+    if (!guard.ok) { th_set_error("th_snapshot_apply_delta: cannot select device %d", src->device); return TH_ECUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    ThScratch sc(st);
+    const size_t zu = (size_t)n_upsert, zd = (size_t)n_delete;
+    const void *u_id, *u_uuid, *u_start, *u_end, *u_owner, *u_canc, *d_del;
+    TH_TRY(sc.in(id, 8 * zu, mem, &u_id));
+    TH_TRY(sc.in(uuid_id, 8 * zu, mem, &u_uuid));
+    TH_TRY(sc.in(start_us, 8 * zu, mem, &u_start));
+    TH_TRY(sc.in(end_us, 8 * zu, mem, &u_end));
+    TH_TRY(sc.in(owner, 8 * zu, mem, &u_owner));
+    TH_TRY(sc.in(cancelled_u8, zu, mem, &u_canc));
+    TH_TRY(sc.in(delete_ids, 8 * zd, mem, &d_del));
+    // ids that leave the old table, sorted for the per-row membership test
+    const i64 n_kill = n_upsert + n_delete;
+    ThRec *ka = nullptr, *kb = nullptr, *kill = nullptr;
+    TH_TRY(sc.alloc((void **)&ka, sizeof(ThRec) * (size_t)(n_kill > 0 ? n_kill : 1)));
+    TH_TRY(sc.alloc((void **)&kb, sizeof(ThRec) * (size_t)(n_kill > 0 ? n_kill : 1)));
+    kill = ka;
+    if (n_kill > 0) {
+        dl_killrec_kernel<<<th_grid_for(n_kill, 256, 8), 256, 0, st>>>((const i64 *)u_id, n_upsert, (const i64 *)d_del,
+                                                                       n_delete, ka);
+        TH_CUDA(cudaGetLastError());
+        int passes = 0;
+        TH_TRY(th_radix_sort(ka, kb, n_kill, 63, 0, &kill, &passes, st));
+    }
+    // survivors
+    const i64 nt = src->nt;
+    int *keep = nullptr;
+    i64 *off = nullptr, *totals = nullptr;
+    TH_TRY(sc.alloc((void **)&keep, 4 * (size_t)(nt > 0 ? nt : 1)));
+    TH_TRY(sc.alloc((void **)&off, 8 * (size_t)(nt + 1)));
+    TH_TRY(sc.alloc((void **)&totals, 16));
+    if (nt > 0) {
+        dl_keep_kernel<<<th_grid_for(nt, 256 * 4, 8), 256, 0, st>>>(nt, src->uuid, src->seg, src->p3, kill, n_kill, keep);
+        TH_CUDA(cudaGetLastError());
+    }
+    TH_TRY(th_exclusive_scan_i32(keep, nt, off, totals, sc, st));
+    i64 tot[2] = {0, 0};
+    TH_CUDA(cudaMemcpyAsync(tot, totals, 16, cudaMemcpyDeviceToHost, st));
+    TH_CUDA(cudaStreamSynchronize(st));
+    const i64 n_keep = tot[0];
+    const i64 n_new = n_keep + n_upsert;
+    TH_REQUIRE(n_new < (1ll << 30), "th_snapshot_apply_delta: %lld rows exceed the 2^30 limit", (long long)n_new);
+    const size_t zn = (size_t)(n_new > 0 ? n_new : 1);
+    i64 *c_id, *c_uuid, *c_start, *c_end, *c_owner;
+    u8 *c_canc;
+    TH_TRY(sc.alloc((void **)&c_id, 8 * zn));
+    TH_TRY(sc.alloc((void **)&c_uuid, 8 * zn));
+    TH_TRY(sc.alloc((void **)&c_start, 8 * zn));
+    TH_TRY(sc.alloc((void **)&c_end, 8 * zn));
+    TH_TRY(sc.alloc((void **)&c_owner, 8 * zn));
+    TH_TRY(sc.alloc((void **)&c_canc, zn));
+    if (nt > 0) {
+        dl_gather_kernel<<<th_grid_for(nt, 256 * 4, 8), 256, 0, st>>>(nt, keep, off, src->p1, src->p3, src->p4, src->uuid, c_id,
+                                                                      c_uuid, c_start, c_end, c_owner, c_canc);
+        TH_CUDA(cudaGetLastError());
+    }
+    if (n_upsert > 0) {
+        dl_append_kernel<<<th_grid_for(n_upsert, 256, 8), 256, 0, st>>>(n_upsert, n_keep, (const i64 *)u_id, (const i64 *)u_uuid,
+                                                                        (const i64 *)u_start, (const i64 *)u_end,
+                                                                        (const i64 *)u_owner, (const u8 *)u_canc, c_id, c_uuid,
+                                                                        c_start, c_end, c_owner, c_canc);
+        TH_CUDA(cudaGetLastError());
+    }
+    // the gathers above read `src`; if dst == src the rebuild below overwrites it only after them (stream order)
+    return th_snapshot_load(dst, n_new, n_uuids, (const int64_t *)c_id, (const int64_t *)c_uuid, (const int64_t *)c_start,
+                            (const int64_t *)c_end, (const int64_t *)c_owner, c_canc, TH_MEM_DEVICE, stream);
 }

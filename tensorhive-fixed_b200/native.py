@@ -26,6 +26,7 @@ SIGNATURES = {
     'th_snapshot_create': (_int, [_int, C.POINTER(_vp)]),
     'th_snapshot_destroy': (_int, [_vp]),
     'th_snapshot_load': (_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
+    'th_snapshot_apply_delta': (_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _int, _vp]),
     'th_snapshot_info': (_int, [_vp, _i64p, _i64p, _i64p, _i64p]),
     'th_snapshot_export': (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
     'th_conflict_bitmap': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, _vp]),

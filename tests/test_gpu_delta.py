@@ -1,0 +1,129 @@
+"""Snapshot maintenance from deltas (th_snapshot_apply_delta): after any sequence of inserts, updates, cancels and
+deletes the snapshot must be indistinguishable from one loaded from scratch with the resulting table."""
+import datetime as dt
+from datetime import timedelta
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+COLS = ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')
+
+
+def _fresh(th, table, u):
+    snap = th.Snapshot(0)
+    snap.load(*[table[k] for k in COLS], n_uuids=u)
+    return snap
+
+
+def _same(a, b):
+    ea, eb = a.export(), b.export()
+    return all(np.array_equal(ea[k], eb[k]) for k in ea)
+
+
+@pytest.mark.parametrize('in_place', [False, True])
+def test_random_delta_sequences_equal_a_fresh_load(lib_built, in_place):
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    rng = np.random.default_rng(7 if in_place else 8)
+    u = 40
+    cal = synth.make_calendar(20_000, u, seed=5)
+    table = {k: cal[k].copy() for k in COLS}
+    cur = _fresh(th, table, u)
+    spare = th.Snapshot(0)
+    next_id = int(table['id'].max()) + 1
+    for step in range(6):
+        n = len(table['id'])
+        # deletes, updates (moved / cancelled rows keep their id), inserts (some on brand-new uuids)
+        del_pos = rng.choice(n, size=int(rng.integers(0, 300)), replace=False)
+        rest = np.setdiff1d(np.arange(n), del_pos)
+        upd_pos = rng.choice(rest, size=int(rng.integers(0, 300)), replace=False)
+        n_ins = int(rng.integers(0, 400))
+        if step == 3:
+            u += 5
+        ins = synth.make_calendar(max(n_ins, 1), u, seed=100 + step)
+        ins = {k: ins[k][:n_ins] for k in COLS}
+        ins['id'] = np.arange(next_id, next_id + n_ins, dtype=np.int64)
+        next_id += n_ins
+        upd = {k: table[k][upd_pos].copy() for k in COLS}
+        upd['start'] = upd['start'] + rng.integers(-10**9, 10**9, size=len(upd_pos))
+        upd['end'] = np.maximum(upd['end'] + rng.integers(-10**9, 10**9, size=len(upd_pos)), upd['start'])
+        upd['cancelled'] = (rng.random(len(upd_pos)) < 0.3).astype(np.uint8)
+        ups = {k: np.concatenate([upd[k], ins[k]]) for k in COLS}
+        order = rng.permutation(len(ups['id']))
+        ups = {k: v[order] for k, v in ups.items()}
+        del_ids = table['id'][del_pos].copy()
+        if step == 2:
+            del_ids = np.concatenate([del_ids, [10**12]])          # deleting an id that does not exist is a no-op
+        # the truth
+        keep = np.ones(n, bool)
+        keep[del_pos] = False
+        keep[upd_pos] = False
+        table = {k: np.concatenate([table[k][keep], ups[k]]) for k in COLS}
+        # the delta
+        dst = cur if in_place else spare
+        dst.apply_delta(cur, u, *[ups[k] for k in COLS], del_ids)
+        if not in_place:
+            cur, spare = dst, cur
+        ref = _fresh(th, table, u)
+        assert cur.info()['n'] == len(table['id'])
+        assert _same(cur, ref), step
+        q = synth.make_queries(dict(table, n_uuids=u), 3000, seed=200 + step)
+        got = cur.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
+        assert np.array_equal(got, brute.conflict_bits(dict(table, n_uuids=u), q['uuid_id'], q['start'], q['end'], q['self_id']))
+        ref.close()
+    cur.close(); spare.close()
+
+
+def test_delta_with_device_pointers_and_empty_cases(lib_built):
+    import torch
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    dev = torch.device('cuda:0')
+    cal = synth.make_calendar(5000, 8, seed=9)
+    table = {k: cal[k].copy() for k in COLS}
+    snap = _fresh(th, table, 8)
+    z = np.zeros(0, np.int64)
+    snap.apply_delta(snap, 8, z, z, z, z, z, np.zeros(0, np.uint8), z)           # empty delta: nothing changes
+    assert _same(snap, _fresh(th, table, 8))
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    snap.apply_delta(snap, 8, t(z), t(z), t(z), t(z), t(z), t(np.zeros(0, np.uint8)), t(table['id']))   # delete everything
+    assert snap.info()['n'] == 0
+    assert not snap.conflict_bitmap(np.zeros(4, np.int64), np.zeros(4, np.int64), np.full(4, 2**62, np.int64),
+                                    np.full(4, -1, np.int64)).any()
+    snap.apply_delta(snap, 8, *[t(table[k]) for k in COLS], t(z))                # and insert it all back
+    assert _same(snap, _fresh(th, table, 8))
+    with pytest.raises(th.NativeError):
+        snap.apply_delta(snap, 4, z, z, z, z, z, np.zeros(0, np.uint8), z)       # uuid dictionary cannot shrink
+    snap.close()
+
+
+def test_calendar_apply_delta_through_the_dropin(lib_built):
+    from tensorhive_fixed_b200 import dropin
+    from tensorhive_fixed_b200.calendar import Calendar
+    gpu = 'GPU-d38d4de3-85ee-e837-3d87-e8e2faeb6a63'
+    gpu2 = 'GPU-d38d4de3-85ee-e837-3d87-e8e2faeb6a64'
+    now = dt.datetime(2026, 3, 1, 12, 0, 0)
+    mk = lambda i, g, s, e, c=None: dropin.Reservation(id=i, user_id=1, title='T', description='D', resource_id=g,
+                                                       start=now + timedelta(minutes=s), end=now + timedelta(minutes=e),
+                                                       is_cancelled=c)
+    cal = Calendar([mk(1, gpu, 0, 60)], clock=lambda: now)
+    dropin.bind(cal)
+    cand = mk(None, gpu, 30, 90)
+    assert cand.would_interfere() is True
+    v0 = cal.version
+    cal.apply_delta(upserts=[mk(1, gpu, 0, 60, True)])                 # cancel row 1
+    assert cal.version == v0 + 1 and cand.would_interfere() is False
+    cal.apply_delta(upserts=[mk(2, gpu, 45, 120), mk(3, gpu2, 0, 600)])   # insert two rows, one on a new GPU
+    assert cand.would_interfere() is True
+    assert [r.id for r in dropin.Reservation.current_events(gpu2)] == [3]
+    cal.apply_delta(upserts=[mk(2, gpu, 90, 150)])                     # move row 2: now it only touches the candidate
+    assert cand.would_interfere() is False
+    cal.apply_delta(deleted_ids=[3])
+    assert dropin.Reservation.current_events(gpu2) == []
+    for _ in range(4):                                                 # handle rotation
+        cal.apply_delta(upserts=[mk(1, gpu, 0, 60, None)])
+    assert cand.would_interfere() is True
+    cal.close()
