@@ -1,0 +1,125 @@
+"""Host-side logic of the drop-in layer on a CPU-only box: the same reference-surface tests as tests/test_gpu_dropin.py,
+with the device snapshot replaced by a stand-in that answers from the brute-force oracle.  This exercises everything
+above the C ABI -- uuid dictionary, datetime conversion, owner encoding, flattening and re-grouping of the process
+table, the greedy pass, error behaviour -- without a GPU; the kernels themselves are covered by the `-m gpu` tests."""
+import numpy as np
+import pytest
+
+import test_gpu_dropin as G
+from oracle import brute
+
+
+class FakeSnapshot:
+    """Same methods as tensorhive_fixed_b200.api.Snapshot, answered by oracle/brute.py (test double, CPU only)."""
+
+    def __init__(self, device=0):
+        self.cal = None
+        self.n = self.n_uuids = 0
+
+    def load(self, id, uuid_id, start, end, owner, cancelled, n_uuids):
+        self.cal = {'id': np.asarray(id, np.int64), 'uuid_id': np.asarray(uuid_id, np.int64),
+                    'start': np.asarray(start, np.int64), 'end': np.asarray(end, np.int64),
+                    'owner': np.asarray(owner, np.int64), 'cancelled': np.asarray(cancelled, np.uint8), 'n_uuids': n_uuids}
+        self.n, self.n_uuids = len(self.cal['id']), n_uuids
+        return self
+
+    def apply_delta(self, src, n_uuids, id, uuid_id, start, end, owner, cancelled, delete_ids):
+        old = src.cal
+        gone = np.isin(old['id'], np.concatenate([np.asarray(id, np.int64), np.asarray(delete_ids, np.int64)]))
+        cols = {}
+        for k, new in (('id', id), ('uuid_id', uuid_id), ('start', start), ('end', end), ('owner', owner), ('cancelled', cancelled)):
+            cols[k] = np.concatenate([old[k][~gone], np.asarray(new, old[k].dtype)])
+        return self.load(n_uuids=n_uuids, **cols)
+
+    def info(self):
+        return {'n': self.n, 'n_uuids': self.n_uuids, 'device_bytes': 0, 'radix_passes': 0}
+
+    def close(self):
+        pass
+
+    def conflict_bitmap(self, qu, qs, qe, qf=None, mode=0):
+        qf = np.full(len(qu), -1, np.int64) if qf is None else qf
+        return brute.conflict_bits(self.cal, qu, qs, qe, qf, mode)
+
+    def conflict_sets(self, qu, qs, qe, qf=None, mode=0, capacity=None):
+        qf = np.full(len(qu), -1, np.int64) if qf is None else qf
+        lists = brute.conflict_sets(self.cal, qu, qs, qe, qf, mode)
+        off = np.zeros(len(lists) + 1, np.int64)
+        off[1:] = np.cumsum([len(x) for x in lists])
+        ids = np.array([i for x in lists for i in x], np.int64)
+        flag = {int(i): int(c) for i, c in zip(self.cal['id'], self.cal['cancelled'])}
+        return off, ids, np.array([flag[int(i)] for i in ids], np.uint8)
+
+    def current_owner(self, now_us, device_out=False):
+        return brute.current_owner(self.cal, self.n_uuids, now_us)
+
+    def upcoming(self, now_us, period_us, uuids):
+        return brute.upcoming_summary(self.cal, uuids, now_us, period_us)
+
+    def upcoming_owner_flags(self, now_us, period_us, task_uuid, task_owner, test):
+        k = len(task_uuid)
+        lists = brute.conflict_sets(self.cal, task_uuid, np.full(k, now_us), np.full(k, now_us + period_us),
+                                    np.full(k, -1), brute.UPCOMING)
+        own = {int(i): int(o) for i, o in zip(self.cal['id'], self.cal['owner'])}
+        fn = {0: lambda o, w: len(w) > 0, 1: lambda o, w: any(own[x] != o for x in w),
+              2: lambda o, w: any(own[x] == o for x in w)}[test]
+        return np.array([fn(int(task_owner[j]), lists[j]) for j in range(k)], np.uint8)
+
+    def violation_join(self, now_us, strict, proc_uuid, proc_owner):
+        res, own = brute.current_owner(self.cal, self.n_uuids, now_us)
+        pu = np.asarray(proc_uuid, np.int64)
+        ok = (pu >= 0) & (pu < self.n_uuids)
+        r = np.where(ok, res[np.clip(pu, 0, max(self.n_uuids - 1, 0))], -1)
+        o = np.where(ok, own[np.clip(pu, 0, max(self.n_uuids - 1, 0))], -1)
+        flag = np.where(r >= 0, (o >= 0) & (np.asarray(proc_owner) != o), bool(strict))
+        return flag.astype(np.uint8), np.where((r >= 0) & flag, r, -1)
+
+
+def _fake_usage_reduce(off, ts, gpu, mem, wu, ws, we, device=0):
+    sg, sm, cnt = brute.usage_reduce(off, ts, gpu, mem, wu, ws, we)
+    ag = np.array([brute.floor_avg(a, c) for a, c in zip(sg, cnt)], np.int64)
+    am = np.array([brute.floor_avg(a, c) for a, c in zip(sm, cnt)], np.int64)
+    return sg, sm, cnt, ag, am
+
+
+@pytest.fixture()
+def dropin(monkeypatch):
+    import tensorhive_fixed_b200.calendar as calmod
+    from tensorhive_fixed_b200 import dropin as d
+    monkeypatch.setattr(calmod, 'Snapshot', FakeSnapshot)
+    monkeypatch.setattr(d.api, 'usage_reduce', _fake_usage_reduce)
+    return d
+
+
+# the reference-surface tests, now collected without the gpu marker and run against the stand-in
+test_known_answers = G.test_reference_known_answers_through_the_dropin
+test_invalid_time_range = G.test_invalid_reservation_time_range
+test_avg = G.test_avg_matches_reference_semantics
+test_protection_service = G.test_protection_service_violations_match_the_reference_loops
+test_job_scheduling = G.test_job_scheduling_checks_match_the_reference_loops
+test_bulk_revalidation = G.test_bulk_revalidation_batches_would_interfere
+test_usage_log = G.test_usage_log_averages
+
+
+def test_calendar_delta_bookkeeping(dropin):
+    import datetime as dt
+    from datetime import timedelta
+    from tensorhive_fixed_b200.calendar import Calendar
+    now = dt.datetime(2026, 3, 1, 12)
+    mk = lambda i, g, s, e, c=None: dropin.Reservation(id=i, user_id=1, title='T', description='D', resource_id=g,
+                                                       start=now + timedelta(minutes=s), end=now + timedelta(minutes=e),
+                                                       is_cancelled=c)
+    g1, g2 = 'GPU-' + 'a' * 36, 'GPU-' + 'b' * 36
+    cal = Calendar([mk(1, g1, 0, 60)], clock=lambda: now)
+    dropin.bind(cal)
+    cand = mk(None, g1, 30, 90)
+    assert cand.would_interfere() is True
+    cal.apply_delta(upserts=[mk(1, g1, 0, 60, True), mk(2, g2, 0, 600)])
+    assert cand.would_interfere() is False
+    assert [r.id for r in dropin.Reservation.current_events()] == [2]
+    assert cal.all_resource_ids() == [g1, g2] and cal.version == 2
+    cal.apply_delta(deleted_ids=[2])
+    assert dropin.Reservation.current_events() == []
+    with pytest.raises(RuntimeError):
+        dropin._calendar = None
+        dropin.Reservation.current_events()
