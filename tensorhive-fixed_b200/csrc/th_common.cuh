@@ -246,6 +246,17 @@ __device__ __forceinline__ i64 th_warp_sum(i64 v) {
     return v;
 }
 
+// makes `dev` current for the lifetime of the object and restores the caller's device afterwards
+struct DeviceGuard {
+    int prev;
+    bool ok;
+    explicit DeviceGuard(int dev) : prev(0), ok(true) {
+        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
+        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
 // ---- host-side scratch: stream-ordered device buffers used to stage TH_MEM_HOST calls -----------------
 struct ThScratch {
     cudaStream_t st;

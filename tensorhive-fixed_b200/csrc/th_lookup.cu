@@ -15,16 +15,6 @@
 
 namespace {
 
-struct DeviceGuard {
-    int prev;
-    bool ok;
-    explicit DeviceGuard(int dev) : prev(0), ok(true) {
-        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
-        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
-    }
-    ~DeviceGuard() { cudaSetDevice(prev); }
-};
-
 constexpr int LK_THREADS = 256;
 constexpr int LK_WARPS = LK_THREADS / 32;
 

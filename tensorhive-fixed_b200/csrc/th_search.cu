@@ -19,16 +19,6 @@
 
 namespace {
 
-struct DeviceGuard {
-    int prev;
-    bool ok;
-    explicit DeviceGuard(int dev) : prev(0), ok(true) {
-        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
-        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
-    }
-    ~DeviceGuard() { cudaSetDevice(prev); }
-};
-
 constexpr int BM_THREADS = 256;
 #ifndef BM_MIN_BLOCKS
 #define BM_MIN_BLOCKS 4

@@ -380,16 +380,6 @@ __global__ void __launch_bounds__(256) dl_append_kernel(i64 n_up, i64 base, cons
     }
 }
 
-struct DeviceGuard {
-    int prev;
-    bool ok;
-    explicit DeviceGuard(int dev) : prev(0), ok(true) {
-        if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
-        if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
-    }
-    ~DeviceGuard() { cudaSetDevice(prev); }
-};
-
 }  // namespace
 
 extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
