@@ -167,6 +167,21 @@ __device__ __forceinline__ longlong2 th_ld16_if(const void *p, bool pred, longlo
 
 __device__ __forceinline__ u32 th_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
+// same, at a compile-time byte offset from `base`: neighbouring probes share ONE 64-bit address computation
+template <int OFF>
+__device__ __forceinline__ longlong2 th_ld16_if_off(const void *base, bool pred, longlong2 dflt) {
+    longlong2 v = dflt;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.s32 p, %2, 0;\n"
+        "@p ld.global.nc.v2.s64 {%0, %1}, [%3+%4];\n"
+        "}\n"
+        : "+l"(v.x), "+l"(v.y)
+        : "r"((int)pred), "l"(base), "n"(OFF));
+    return v;
+}
+
 // ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass registers, grouped for multi-stage rings -----
 __device__ __forceinline__ void th_cp_async16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(th_smem_addr(smem_dst)), "l"(gmem_src) : "memory");

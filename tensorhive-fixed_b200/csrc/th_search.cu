@@ -66,11 +66,18 @@ __device__ __forceinline__ bool k2_resolve(const longlong2 c, const ThP1 *__rest
         const longlong2 far = make_longlong2(TH_I64_MAX, 0);          // {start, m1}: never before qe
         const longlong2 none = make_longlong2(-1, TH_I64_MIN);       // {a1, m2}
         longlong2 e[BM_PROBE], t[BM_PROBE + 1];
-#pragma unroll
-        for (int k = 0; k < BM_PROBE; ++k) e[k] = th_ld16_if(&p1[pos + k], cnt > k, far);
-        t[0] = th_ld16_if(&p2[pos - 1], ws && pos > 0, none);
-#pragma unroll
-        for (int k = 0; k < BM_PROBE; ++k) t[k + 1] = th_ld16_if(&p2[pos + k], ws && cnt > k, none);
+        static_assert(BM_PROBE == 4, "the probe offsets below are written out for four rows");
+        const ThP1 *r1 = p1 + pos;             // one address per array; the probes use immediate offsets from it
+        const ThP2 *r2 = p2 + pos;
+        e[0] = th_ld16_if_off<0>(r1, cnt > 0, far);
+        e[1] = th_ld16_if_off<16>(r1, cnt > 1, far);
+        e[2] = th_ld16_if_off<32>(r1, cnt > 2, far);
+        e[3] = th_ld16_if_off<48>(r1, cnt > 3, far);
+        t[0] = th_ld16_if_off<-16>(r2, ws && pos > 0, none);
+        t[1] = th_ld16_if_off<0>(r2, ws && cnt > 0, none);
+        t[2] = th_ld16_if_off<16>(r2, ws && cnt > 1, none);
+        t[3] = th_ld16_if_off<32>(r2, ws && cnt > 2, none);
+        t[4] = th_ld16_if_off<48>(r2, ws && cnt > 3, none);
         // rows are start-sorted, so the ones before qe are a prefix of the bucket
         int k = 0;
         i64 m1 = c.y;

@@ -41,3 +41,15 @@ def test_argument_errors_do_not_need_a_gpu(lib_built):
     rc = lib.th_snapshot_info(None, None, None, None, None)
     assert rc == -1
     assert b'NULL' in lib.th_last_error()
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/th_b200.h must compile as C99 (no C++ or torch types in the signatures) and link against the library."""
+    import subprocess
+    src = tmp_path / 'use.c'
+    src.write_text('#include "th_b200.h"\n#include <stdio.h>\n'
+                   'int main(void) { printf("%d %s\\n", th_version(), th_last_error()); return th_version() == TH_ABI_VERSION ? 0 : 1; }\n')
+    subprocess.run(['gcc', '-std=c99', '-Wall', '-Wextra', '-Werror', '-fsyntax-only', '-x', 'c',
+                    os.path.join(ROOT, 'include', 'th_b200.h')], check=True)
+    subprocess.run(['gcc', '-std=c99', '-Wall', '-Werror', '-I', os.path.join(ROOT, 'include'), '-c', str(src), '-o',
+                    str(tmp_path / 'use.o')], check=True)
