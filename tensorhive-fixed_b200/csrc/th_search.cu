@@ -174,6 +174,10 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // Also measured and dropped: pulling the index (cells, P1, P2 = 44 MB) into L2 with cp.async.bulk.prefetch.L2 at
     // kernel start -- 26.8 us vs 24.6 us cold: the prefetch competes with the query stream for HBM and the probes'
     // HBM latency was not what the warps were waiting for.
+    // Also measured and dropped: compacting the lanes that need level 3 into a per-warp shared-memory queue and
+    // running the row probes only on full batches of 32 (dense lanes, level 3 once per ~3 tiles): correct, but
+    // 43.9 us cold / 483 us at 16 M queries -- the queue traffic, the extra ballots and atomicOr of late bits cost
+    // far more issue slots than the idle lanes they save.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
