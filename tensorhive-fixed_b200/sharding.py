@@ -112,6 +112,86 @@ def torch_all_gather(words: np.ndarray, device: Optional[str] = None) -> np.ndar
     return out.cpu().numpy().view(np.uint32).reshape(world, -1)
 
 
+def torch_all_gather_i64(values: np.ndarray, device: Optional[str] = None) -> np.ndarray:
+    """All-gather equal-length int64 vectors over the default process group -> [world, len]."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    t = torch.from_numpy(np.ascontiguousarray(values, np.int64).copy())
+    if device is not None:
+        t = t.to(device)
+    out = torch.empty(world * t.numel(), dtype=torch.int64, device=t.device)
+    dist.all_gather_into_tensor(out, t)
+    return out.cpu().numpy().reshape(world, -1)
+
+
+def sharded_window_averages(win_uuid, win_start, win_end, bounds, rank: int,
+                            local_reduce: Callable[[np.ndarray, np.ndarray, np.ndarray], Tuple],
+                            all_gather_i64: Callable[[np.ndarray], np.ndarray]) -> Tuple[np.ndarray, np.ndarray]:
+    """Replicated window list (one per reservation) -> (avg_gpu, avg_mem) of every window on every rank.
+
+    The samples of a uuid live on the rank that owns the uuid, so rank r reduces only its windows:
+    ``local_reduce(uuid_local, start, end)`` runs K4 on this rank's sample shard and returns
+    ``(sum_gpu, sum_mem, count)``; the floor division of UsageLoggingService.avg (``sum // count``, -1 when the
+    window holds no sample) is done here and the W x 2 int64 averages are all-gathered (section 8e)."""
+    router = Router(win_uuid, bounds)
+    idx = router.local_indices(rank)
+    cap = int(router.counts.max()) if router.m else 0
+    mine = np.full((cap, 2), -1, np.int64)
+    if idx.size:
+        sg, sm, cnt = (np.asarray(a, np.int64) for a in local_reduce(
+            router.local_uuid(win_uuid, rank), np.asarray(win_start, np.int64)[idx], np.asarray(win_end, np.int64)[idx])[:3])
+        some = cnt > 0
+        safe = np.where(some, cnt, 1)
+        mine[:idx.size, 0] = np.where(some, sg // safe, -1)
+        mine[:idx.size, 1] = np.where(some, sm // safe, -1)
+    g = all_gather_i64(mine.reshape(-1)).reshape(router.world, cap, 2)
+    avg_gpu = np.full(router.m, -1, np.int64)
+    avg_mem = np.full(router.m, -1, np.int64)
+    for r in range(router.world):
+        c = int(router.counts[r])
+        if c:
+            avg_gpu[router.local_indices(r)] = g[r, :c, 0]
+            avg_mem[router.local_indices(r)] = g[r, :c, 1]
+    return avg_gpu, avg_mem
+
+
+def sharded_current_owner(bounds, rank: int, local_current: Callable[[], Tuple[np.ndarray, np.ndarray]],
+                          all_gather_i64: Callable[[np.ndarray], np.ndarray]) -> Tuple[np.ndarray, np.ndarray]:
+    """Per-uuid ``(cur_res_id, cur_owner)`` of the WHOLE calendar on every rank (the table the violation join
+    and the slot check read): ``local_current()`` runs K3 on this rank's shard, the per-rank tables are
+    all-gathered (padded to the widest shard) and laid back out in global uuid-code order."""
+    bounds = np.asarray(bounds, np.int64)
+    world = bounds.size - 1
+    widths = np.diff(bounds)
+    cap = int(widths.max()) if world else 0
+    mine = np.full((2, cap), -1, np.int64)
+    w = int(widths[rank])
+    if w:
+        res_id, owner = local_current()
+        mine[0, :w] = np.asarray(res_id, np.int64)[:w]
+        mine[1, :w] = np.asarray(owner, np.int64)[:w]
+    g = all_gather_i64(mine.reshape(-1)).reshape(world, 2, cap)
+    res_all = np.full(int(bounds[-1]), -1, np.int64)
+    own_all = np.full(int(bounds[-1]), -1, np.int64)
+    for r in range(world):
+        lo, hi = int(bounds[r]), int(bounds[r + 1])
+        res_all[lo:hi] = g[r, 0, :hi - lo]
+        own_all[lo:hi] = g[r, 1, :hi - lo]
+    return res_all, own_all
+
+
+def shard_samples(samples: dict, bounds: np.ndarray, rank: int) -> dict:
+    """The usage samples (CSR by uuid, ``synth.make_samples`` layout) this rank owns, offsets rebased to the shard."""
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    off = np.asarray(samples['offsets'], np.int64)
+    a, b = int(off[lo]), int(off[hi])
+    out = {k: samples[k][a:b] for k in ('ts', 'gpu', 'mem')}
+    out['offsets'] = (off[lo:hi + 1] - a) if hi > lo else np.zeros(2, np.int64)
+    out['n_uuids'] = max(hi - lo, 1)
+    return out
+
+
 def shard_rows(cal: dict, bounds: np.ndarray, rank: int) -> dict:
     """The rows of ``cal`` this rank owns, with uuid codes rebased to the shard."""
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])

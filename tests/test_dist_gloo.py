@@ -55,6 +55,50 @@ def test_sharded_bitmap_over_gloo_world2(tmp_path):
     assert r0[2] + r1[2] == 6000 and min(r0[2], r1[2]) > 1500   # rows split, roughly balanced despite the skew
 
 
+def _worker_gathers(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from oracle import brute
+    from tensorhive_fixed_b200 import synth, sharding
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    n_uuids = 23
+    cal = synth.make_calendar(4000, n_uuids, seed=15, skew=1.0)
+    bounds = sharding.partition_uuids(np.bincount(cal['uuid_id'], minlength=n_uuids), world)
+    mine = sharding.shard_rows(cal, bounds, rank)
+    now = int(np.median(cal['start']))
+    # per-uuid current reservation / owner table of the whole calendar
+    res, own = sharding.sharded_current_owner(
+        bounds, rank, lambda: brute.current_owner(mine, mine['n_uuids'], now), sharding.torch_all_gather_i64)
+    want_res, want_own = brute.current_owner(cal, n_uuids, now)
+    ok = np.array_equal(res, want_res) and np.array_equal(own, want_own)
+    # window averages: samples sharded by uuid, windows replicated (some on unknown uuids -> -1)
+    smp = synth.make_samples(n_uuids, 300, seed=16, ragged=True)
+    win = synth.make_windows(smp, 700, seed=17)
+    win['uuid_id'][::50] = 99
+    ms = sharding.shard_samples(smp, bounds, rank)
+    ag, am = sharding.sharded_window_averages(
+        win['uuid_id'], win['start'], win['end'], bounds, rank,
+        lambda u, s, e: brute.usage_reduce(ms['offsets'], ms['ts'], ms['gpu'], ms['mem'], u, s, e),
+        sharding.torch_all_gather_i64)
+    sg, sm, cnt = brute.usage_reduce(smp['offsets'], smp['ts'], smp['gpu'], smp['mem'], win['uuid_id'], win['start'], win['end'])
+    want_g = np.array([brute.floor_avg(a, c) for a, c in zip(sg, cnt)], np.int64)
+    want_m = np.array([brute.floor_avg(a, c) for a, c in zip(sm, cnt)], np.int64)
+    ok = ok and np.array_equal(ag, want_g) and np.array_equal(am, want_m)
+    np.save(os.path.join(out_dir, 'g%d.npy' % rank), np.array([ok, (want_res >= 0).sum(), (want_g >= 0).sum(), (want_g < 0).sum()]))
+    dist.destroy_process_group()
+
+
+def test_sharded_owner_table_and_window_averages_over_gloo_world2(tmp_path):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_worker_gathers, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        g = np.load(tmp_path / ('g%d.npy' % r))
+        assert g[0] == 1
+        assert g[1] > 0 and g[2] > 0 and g[3] > 0       # some current reservations, some averages, some empty windows
+
+
 def test_partition_is_contiguous_and_balanced():
     from tensorhive_fixed_b200 import sharding
     rng = np.random.default_rng(0)

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Multi-GPU parity check, one rank per GPU (launch with torchrun): the calendar is sharded by uuid, a replicated
 query batch is routed, every rank runs K2 on its shard, the bitmap words are all-gathered over NCCL and the decoded
-verdict vector must equal the brute-force oracle over the WHOLE calendar on every rank."""
+verdict vector must equal the brute-force oracle over the WHOLE calendar on every rank.  The per-uuid owner table (K3)
+and the window averages (K4) are gathered and checked the same way."""
 import os
 import sys
 
@@ -49,6 +50,23 @@ def main():
         px.check()
         fused = router.decode(g.cpu().numpy())
         ok = ok and bool(np.array_equal(fused, want))
+    # the other two gathers of section 8e: per-uuid (cur_res_id, cur_owner) from K3 and window averages from K4
+    now = int(np.median(cal['start']))
+    gather64 = lambda v: sharding.torch_all_gather_i64(v, dev)
+    res, own = sharding.sharded_current_owner(bounds, rank, lambda: snap.current_owner(now), gather64)
+    want_res, want_own = brute.current_owner(cal, u, now)
+    ok = ok and bool(np.array_equal(res, want_res)) and bool(np.array_equal(own, want_own))
+    smp = synth.make_samples(u, 400, seed=79, ragged=True)
+    win = synth.make_windows(smp, 3000, seed=80)
+    ms = sharding.shard_samples(smp, bounds, rank)
+    ag, am = sharding.sharded_window_averages(
+        win['uuid_id'], win['start'], win['end'], bounds, rank,
+        lambda wu, ws, we: th.usage_reduce(ms['offsets'], ms['ts'], ms['gpu'], ms['mem'], wu, ws, we, device=local),
+        gather64)
+    sg, sm, cnt = brute.usage_reduce(smp['offsets'], smp['ts'], smp['gpu'], smp['mem'], win['uuid_id'], win['start'],
+                                     win['end'])
+    ok = ok and bool(np.array_equal(ag, [brute.floor_avg(a, c) for a, c in zip(sg, cnt)]))
+    ok = ok and bool(np.array_equal(am, [brute.floor_avg(a, c) for a, c in zip(sm, cnt)]))
     dist.barrier()
     px.close()
     flag = torch.tensor([1 if ok else 0], device='cuda:%d' % local)
