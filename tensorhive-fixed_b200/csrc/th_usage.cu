@@ -6,55 +6,125 @@
 // it was logged while the reservation was in current_events(): start <= ts <= end, both inclusive
 // (tensorhive/models/Reservation.py:96-97), so touching windows share their boundary sample.
 //
-// Eight lanes per window, four windows per warp: the range search is the same instruction stream for every
+// Eight lanes per window, four windows per warp (four lanes, eight windows for the uint8 format): the range search is the same instruction stream for every
 // lane of a group, so sharing a warp between four windows cuts the issue slots per window by 4 (the first
 // version, one warp per window, was instruction-issue bound at 70 % SM throughput, 36 % DRAM).  Samples of a
 // uuid are ts-sorted, so the window is a contiguous index range [a, b): both ends are located by an
 // interpolation guess followed by ONE coalesced 16-wide probe per end (exact for a regular logging cadence,
-// which is what the service produces; both probes are independent and issued back to back), with a
+// which is what the service produces; the four probe loads of both ends are issued together), with a
 // group-uniform binary search only when a guess misses.  The range is then summed with 16-byte loads of
 // gpu_util / mem_util.  The ts column is only probed, never streamed.
+//
+// The kernel is bound by the dependent chain per window (window columns -> uuid entry -> probes -> samples) times
+// the resident warps, and by issue slots (about 230 warp instructions per window in the first version): the per-uuid
+// entry table removes two levels of the chain and the int64 division, int32 positions relative to the window halve
+// the bounds arithmetic.  Measured and dropped: prefetching the next windows' columns / entries one or two
+// iterations ahead through registers (4.5-5.1 ms against 3.6 ms: the prefetches share scoreboards with the loads the
+// warp is waiting for and cost 15-40 registers) or through a cp.async shared-memory ring (4.0 ms), four or eight pairs
+// per lane and iteration (3.65 / 4.5 ms), and 48 resident warps at 40 registers (3.8 ms).
 #include "th_common.cuh"
+
 
 namespace {
 
 constexpr int US_THREADS = 256;
-constexpr int US_GROUP = 8;                              // lanes per window
-constexpr int US_GROUPS_PER_BLOCK = US_THREADS / US_GROUP;
+// lanes per window are a template parameter G (8 for int64 columns, 4 for uint8): US_THREADS / G windows per block
+// and iteration
 
-template <bool GE>
-__device__ __forceinline__ bool us_pred(i64 x, i64 key) { return GE ? (x >= key) : (x > key); }
+// Per-uuid entry of the sample log: where the segment starts, how long it is, its first timestamp and the
+// interpolation slope (n - 1) / (ts[last] - ts[first]).  Built by a tiny kernel in front of K4 so that a window
+// reaches its probes after ONE dependent 32-byte read (L2 resident: 2 MB for 65 536 uuids) instead of
+// off[u] -> ts[lo], ts[hi - 1]; with int64 division gone from the hot loop as well.
+struct __align__(16) UsSeg { i64 lo; i64 n; i64 t_lo; double inv; };
 
-// first index in [lo, hi) whose ts satisfies pred (GE: ts >= key, else ts > key); hi if none.
-// t_lo = ts[lo], t_hi = ts[hi - 1] (ignored when lo >= hi).  Arguments and result are uniform within the
-// 8-lane group `gmask`; gl = lane index inside the group.
+__device__ __forceinline__ UsSeg us_make_seg(const i64 *__restrict__ off, const i64 *__restrict__ ts, i64 u) {
+    UsSeg e;
+    e.lo = off[u];
+    e.n = off[u + 1] - e.lo;
+    e.t_lo = 0;
+    e.inv = 0.0;
+    if (e.n > 0) {
+        e.t_lo = ts[e.lo];
+        const double span = (double)ts[e.lo + e.n - 1] - (double)e.t_lo;
+        if (e.n > 1 && span > 0.0) e.inv = (double)(e.n - 1) / span;
+    }
+    return e;
+}
+
+__global__ void __launch_bounds__(256) k4_segments_kernel(i64 n_uuids, const i64 *__restrict__ off,
+                                                          const i64 *__restrict__ ts, UsSeg *__restrict__ tab) {
+    const i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u < n_uuids) tab[u] = us_make_seg(off, ts, u);
+}
+
+// 8-byte read-only load that executes only when `pred` holds (see th_ld16_if)
+__device__ __forceinline__ i64 us_ld8_if(const i64 *p, bool pred, i64 dflt) {
+    i64 v = dflt;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.s32 p, %1, 0;\n"
+        "@p ld.global.nc.s64 %0, [%2];\n"
+        "}\n"
+        : "+l"(v)
+        : "r"((int)pred), "l"(p));
+    return v;
+}
+
+// start of the 16-wide probe window for `key` inside a segment of n >= 1 samples (relative index)
+__device__ __forceinline__ i64 us_window(i64 n, i64 key, i64 t_lo, double inv) {
+    double x = ((double)key - (double)t_lo) * inv;        // only a guess: rounding cannot change the result
+    x = fmin(fmax(x, 0.0), (double)(n - 1));
+    i64 w0 = (i64)x - 7;
+    if (w0 > n - 16) w0 = n - 16;
+    if (w0 < 0) w0 = 0;
+    return w0;
+}
+
+// From the number of probe-window samples that fail the predicate (a prefix, the segment being ts-sorted) to the first
+// index that satisfies it; a group-uniform binary search only when the whole window lies on one side of the answer.
 template <bool GE>
-__device__ __forceinline__ i64 us_search(const i64 *__restrict__ ts, i64 lo, i64 hi, i64 key, i64 t_lo, i64 t_hi,
-                                         int gl, u32 gmask) {
-    if (lo >= hi) return lo;
-    if (us_pred<GE>(t_lo, key)) return lo;
-    if (!us_pred<GE>(t_hi, key)) return hi;
-    // invariant: pred(ts[lo]) false, pred(ts[hi - 1]) true, hence t_lo < t_hi
-    const double frac = (double)(key - t_lo) / (double)(t_hi - t_lo);
-    i64 g = lo + (i64)(frac * (double)(hi - 1 - lo));
-    if (g < lo) g = lo;
-    if (g > hi - 1) g = hi - 1;
-    i64 w0 = g - 7;
-    if (w0 + 16 > hi) w0 = hi - 16;
-    if (w0 < lo) w0 = lo;
-    const i64 i0 = w0 + gl, i1 = w0 + 8 + gl;
-    const bool f0 = i0 < hi ? !us_pred<GE>(__ldg(&ts[i0]), key) : false;
-    const bool f1 = i1 < hi ? !us_pred<GE>(__ldg(&ts[i1]), key) : false;
-    const int nfalse = __popc(__ballot_sync(gmask, f0) & gmask) + __popc(__ballot_sync(gmask, f1) & gmask);
-    i64 l, r;   // answer = first true in [l, r], pred(ts[r]) known true
-    if (nfalse == 0) { l = lo + 1; r = w0; }
-    else if (nfalse == 16) { l = w0 + 16; r = hi - 1; }
-    else return w0 + nfalse;
+__device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64 key, i64 w0, int nfalse) {
+    const i64 cntw = n - w0 < 16 ? n - w0 : 16;
+    i64 l, r;   // the answer lies in [l, r]; the predicate holds at r (r == n counts as "holds")
+    if (nfalse == 0) {
+        if (w0 == 0) return 0;
+        l = 0; r = w0;
+    } else if (nfalse == (int)cntw) {
+        if (w0 + cntw == n) return n;
+        l = w0 + cntw; r = n;
+    } else {
+        return w0 + nfalse;
+    }
     while (l < r) {
         const i64 mid = l + ((r - l) >> 1);
-        if (us_pred<GE>(__ldg(&ts[mid]), key)) r = mid; else l = mid + 1;
+        const i64 x = __ldg(&seg[mid]);
+        if (GE ? (x >= key) : (x > key)) r = mid; else l = mid + 1;
     }
     return l;
+}
+
+// [a, b) = samples of the segment with ws <= ts <= we, as indices relative to the segment.  Both ends are probed
+// together: four independent loads per lane, then four ballots.  All arguments are uniform within the 8-lane group.
+template <int G>
+__device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSeg &e, i64 ws, i64 we, int gl, u32 gmask,
+                                         i64 &a, i64 &b) {
+    constexpr int R = 16 / G;                     // probe loads per lane and end
+    const i64 n = e.n;
+    const i64 wa = us_window(n, ws, e.t_lo, e.inv), wb = us_window(n, we, e.t_lo, e.inv);
+    i64 va[R], vb[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) va[r] = us_ld8_if(seg + wa + r * G + gl, wa + r * G + gl < n, TH_I64_MAX);
+#pragma unroll
+    for (int r = 0; r < R; ++r) vb[r] = us_ld8_if(seg + wb + r * G + gl, wb + r * G + gl < n, TH_I64_MAX);
+    int fa = 0, fb = 0;                           // beyond the segment counts as "holds"
+#pragma unroll
+    for (int r = 0; r < R; ++r) fa += __popc(__ballot_sync(gmask, wa + r * G + gl < n && va[r] < ws));
+#pragma unroll
+    for (int r = 0; r < R; ++r) fb += __popc(__ballot_sync(gmask, wb + r * G + gl < n && vb[r] <= we));
+    a = us_finish<true>(seg, n, ws, wa, fa);      // first ts >= ws
+    b = us_finish<false>(seg, n, we, wb, fb);     // first ts >  we
+    if (b < a) b = a;                             // end before start: empty window
 }
 
 __device__ __forceinline__ i64 us_floor_div(i64 a, i64 b) {   // b > 0; Python's //
@@ -63,90 +133,43 @@ __device__ __forceinline__ i64 us_floor_div(i64 a, i64 b) {   // b > 0; Python's
     return q;
 }
 
-template <bool VEC>
-__global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
-                                                              const i64 *__restrict__ ts, const i64 *__restrict__ gpu,
-                                                              const i64 *__restrict__ mem, i64 w,
-                                                              const i64 *__restrict__ win_uuid,
-                                                              const i64 *__restrict__ win_start,
-                                                              const i64 *__restrict__ win_end, i64 *__restrict__ o_sg,
-                                                              i64 *__restrict__ o_sm, i64 *__restrict__ o_cnt,
-                                                              i64 *__restrict__ o_ag, i64 *__restrict__ o_am) {
-    const int lane = threadIdx.x & 31;
-    const int gl = lane & (US_GROUP - 1);
-    const u32 gmask = 0xffu << (lane & ~(US_GROUP - 1));
-    const i64 gstride = (i64)gridDim.x * US_GROUPS_PER_BLOCK;
-    for (i64 q = (i64)blockIdx.x * US_GROUPS_PER_BLOCK + (threadIdx.x / US_GROUP); q < w; q += gstride) {
-        const i64 u = win_uuid[q];
-        i64 a = 0, b = 0;
-        if (u >= 0 && u < n_uuids) {
-            const i64 lo = off[u], hi = off[u + 1];
-            if (lo < hi) {
-                const i64 ws = win_start[q], we = win_end[q];
-                const i64 t_lo = __ldg(&ts[lo]), t_hi = __ldg(&ts[hi - 1]);
-                // the two ends are independent searches over the whole segment: their probes overlap
-                a = us_search<true>(ts, lo, hi, ws, t_lo, t_hi, gl, gmask);
-                b = us_search<false>(ts, lo, hi, we, t_lo, t_hi, gl, gmask);
-                if (b < a) b = a;   // end before start: empty window
-            }
-        }
-        i64 sg = 0, sm = 0;
-        if (VEC) {
-            // element pairs (2p, 2p + 1): 16-byte aligned because the column bases are
-            const i64 p1 = (b + 1) >> 1;
-            for (i64 p = (a >> 1) + gl; p < p1; p += 2 * US_GROUP) {
-                const i64 i0 = p << 1;
-                const i64 j0 = (p + US_GROUP) << 1;
-                const bool second = p + US_GROUP < p1;
-                i64 g0, g1 = 0, m0, m1 = 0, h0 = 0, h1 = 0, n0 = 0, n1 = 0;
-                // issue every load of the iteration before consuming any
-                if (i0 + 1 < s_total) {
-                    const longlong2 g2 = th_ld16(gpu + i0);
-                    const longlong2 m2 = th_ld16(mem + i0);
-                    g0 = g2.x; g1 = g2.y; m0 = m2.x; m1 = m2.y;
-                } else {
-                    g0 = __ldg(&gpu[i0]); m0 = __ldg(&mem[i0]);
-                }
-                if (second) {
-                    if (j0 + 1 < s_total) {
-                        const longlong2 g2 = th_ld16(gpu + j0);
-                        const longlong2 m2 = th_ld16(mem + j0);
-                        h0 = g2.x; h1 = g2.y; n0 = m2.x; n1 = m2.y;
-                    } else {
-                        h0 = __ldg(&gpu[j0]); n0 = __ldg(&mem[j0]);
-                    }
-                }
-                if (i0 >= a && i0 < b) { sg += g0; sm += m0; }
-                if (i0 + 1 >= a && i0 + 1 < b) { sg += g1; sm += m1; }
-                if (second) {
-                    if (j0 < b) { sg += h0; sm += n0; }          // j0 > a always
-                    if (j0 + 1 < b) { sg += h1; sm += n1; }
-                }
-            }
-        } else {
-            for (i64 i = a + gl; i < b; i += US_GROUP) { sg += __ldg(&gpu[i]); sm += __ldg(&mem[i]); }
-        }
-#pragma unroll
-        for (int o = US_GROUP / 2; o > 0; o >>= 1) {
-            sg += __shfl_xor_sync(gmask, sg, o);
-            sm += __shfl_xor_sync(gmask, sm, o);
-        }
-        if (gl == 0) {
-            const i64 c = b - a;
-            if (o_sg) o_sg[q] = sg;
-            if (o_sm) o_sm[q] = sm;
-            if (o_cnt) o_cnt[q] = c;
-            if (o_ag) o_ag[q] = c > 0 ? us_floor_div(sg, c) : -1;
-            if (o_am) o_am[q] = c > 0 ? us_floor_div(sm, c) : -1;
-        }
+// ---- range sums --------------------------------------------------------------------------------------------------
+// int64 columns, 16-byte aligned: element pairs, two pairs per lane and iteration, every load issued before any is
+// consumed.  Positions are int32 offsets from the (even) first pair, so the bounds checks are single compares.
+template <int G>
+__device__ __forceinline__ void us_sum_i64(const i64 *__restrict__ gpu, const i64 *__restrict__ mem, i64 s_total, i64 a,
+                                           i64 b, int gl, i64 &sg, i64 &sm) {
+    const i64 base = a & ~1ll;
+    const i64 span = b - base;
+    if (span <= 0) return;
+    if (span >= (1ll << 30)) {                       // a window of a billion samples: plain strided loop
+        for (i64 i = a + gl; i < b; i += G) { sg += __ldg(&gpu[i]); sm += __ldg(&mem[i]); }
+        return;
     }
+    const int ra = (int)(a - base), rb = (int)span;
+    const i64 room = s_total - 1 - base;             // pair j may be loaded as 16 bytes iff 2 j < room
+    const int rl = room < (i64)rb ? (int)room : rb;
+    const longlong2 *gp = reinterpret_cast<const longlong2 *>(gpu + base);
+    const longlong2 *mp = reinterpret_cast<const longlong2 *>(mem + base);
+    const longlong2 zero2 = make_longlong2(0, 0);
+    for (int j = gl; 2 * j < rb; j += 2 * G) {
+        const int k = j + G;
+        longlong2 g0 = th_ld16_if(gp + j, 2 * j < rl, zero2);
+        longlong2 m0 = th_ld16_if(mp + j, 2 * j < rl, zero2);
+        longlong2 g1 = th_ld16_if(gp + k, 2 * k < rl, zero2);
+        longlong2 m1 = th_ld16_if(mp + k, 2 * k < rl, zero2);
+        if (2 * j < ra) { g0.x = 0; m0.x = 0; }              // first pair of a window that starts on an odd index
+        if (2 * j + 1 >= rb) { g0.y = 0; m0.y = 0; }         // last pair of a window that ends on an odd index
+        if (2 * k + 1 >= rb) { g1.y = 0; m1.y = 0; }
+        sg += (g0.x + g0.y) + (g1.x + g1.y);
+        sm += (m0.x + m0.y) + (m1.x + m1.y);
+    }
+    // the last element of an odd-length column has no 16-byte partner
+    if (rl < rb && (room & 1) == 0 && gl == 0 && s_total - 1 >= a) { sg += __ldg(&gpu[s_total - 1]); sm += __ldg(&mem[s_total - 1]); }
 }
 
-
-// ---- narrow sample format: utilisation as uint8 -------------------------------------
-// gpu_util / mem_util are percentages (0..100), so one byte each is lossless; the range sum then reads 2 bytes per
-// sample instead of 16.  Same range search as above (ts stays int64: it is probed, never streamed); the sum loads
-// 16 samples per lane and load (128-bit), masks the bytes outside [a, b) and adds four bytes per __dp4a.
+// uint8 columns (utilisation is a percentage, one byte is lossless), 16-byte aligned:
+// 16 samples per lane and load, bytes outside [a, b) masked, four bytes added per __dp4a.
 __device__ __forceinline__ u32 us_mask4(int lo, int hi, int base) {   // 0xff for bytes base..base+3 that lie in [lo, hi)
     u32 m = 0;
 #pragma unroll
@@ -154,62 +177,86 @@ __device__ __forceinline__ u32 us_mask4(int lo, int hi, int base) {   // 0xff fo
         if (base + t >= lo && base + t < hi) m |= 0xffu << (8 * t);
     return m;
 }
-__device__ __forceinline__ int us_sum16(const uint4 v, int lo, int hi) {
+__device__ __forceinline__ int us_sum16(const uint4 v) {
     u32 acc = 0;   // unsigned bytes x 1: at most 16 * 255
-    acc = __dp4a(v.x & us_mask4(lo, hi, 0), 0x01010101u, acc);
-    acc = __dp4a(v.y & us_mask4(lo, hi, 4), 0x01010101u, acc);
-    acc = __dp4a(v.z & us_mask4(lo, hi, 8), 0x01010101u, acc);
-    acc = __dp4a(v.w & us_mask4(lo, hi, 12), 0x01010101u, acc);
+    acc = __dp4a(v.x, 0x01010101u, acc);
+    acc = __dp4a(v.y, 0x01010101u, acc);
+    acc = __dp4a(v.z, 0x01010101u, acc);
+    acc = __dp4a(v.w, 0x01010101u, acc);
     return (int)acc;
 }
+__device__ __forceinline__ uint4 us_mask16(uint4 v, int lo, int hi) {
+    v.x &= us_mask4(lo, hi, 0); v.y &= us_mask4(lo, hi, 4); v.z &= us_mask4(lo, hi, 8); v.w &= us_mask4(lo, hi, 12);
+    return v;
+}
+template <int G>
+__device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *__restrict__ mem, i64 s_total, i64 a,
+                                          i64 b, int gl, i64 &sg, i64 &sm) {
+    const i64 c1 = (b + 15) >> 4;                       // 16-sample chunks
+    for (i64 c = (a >> 4) + gl; c < c1; c += G) {
+        const i64 i0 = c << 4;
+        const int lo = (int)(a > i0 ? a - i0 : 0);
+        const int hi = (int)(b < i0 + 16 ? b - i0 : 16);
+        if (i0 + 16 <= s_total) {
+            uint4 g4 = __ldg(reinterpret_cast<const uint4 *>(gpu + i0));
+            uint4 m4 = __ldg(reinterpret_cast<const uint4 *>(mem + i0));
+            if (lo > 0 || hi < 16) { g4 = us_mask16(g4, lo, hi); m4 = us_mask16(m4, lo, hi); }   // edge chunks only
+            sg += us_sum16(g4);
+            sm += us_sum16(m4);
+        } else {
+            for (int t = lo; t < hi; ++t) { sg += gpu[i0 + t]; sm += mem[i0 + t]; }
+        }
+    }
+}
 
-template <bool VEC>
-__global__ void __launch_bounds__(US_THREADS) k4_usage_u8_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
-                                                                 const i64 *__restrict__ ts, const u8 *__restrict__ gpu,
-                                                                 const u8 *__restrict__ mem, i64 w,
-                                                                 const i64 *__restrict__ win_uuid,
-                                                                 const i64 *__restrict__ win_start,
-                                                                 const i64 *__restrict__ win_end, i64 *__restrict__ o_sg,
-                                                                 i64 *__restrict__ o_sm, i64 *__restrict__ o_cnt,
-                                                                 i64 *__restrict__ o_ag, i64 *__restrict__ o_am) {
+// ELEM = bytes per utilisation sample (8: int64 columns, 1: uint8 columns); VEC = the columns are 16-byte aligned;
+// TAB = `tab` holds the per-uuid entries (otherwise each window derives its entry from off / ts itself -- used when
+// there are far more uuids than windows).
+template <int ELEM, bool VEC, bool TAB, int G>
+__global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
+                                                              const UsSeg *__restrict__ tab, const i64 *__restrict__ ts,
+                                                              const void *__restrict__ gpu_v, const void *__restrict__ mem_v,
+                                                              i64 w, const i64 *__restrict__ win_uuid,
+                                                              const i64 *__restrict__ win_start,
+                                                              const i64 *__restrict__ win_end, i64 *__restrict__ o_sg,
+                                                              i64 *__restrict__ o_sm, i64 *__restrict__ o_cnt,
+                                                              i64 *__restrict__ o_ag, i64 *__restrict__ o_am) {
     const int lane = threadIdx.x & 31;
-    const int gl = lane & (US_GROUP - 1);
-    const u32 gmask = 0xffu << (lane & ~(US_GROUP - 1));
-    const i64 gstride = (i64)gridDim.x * US_GROUPS_PER_BLOCK;
-    for (i64 q = (i64)blockIdx.x * US_GROUPS_PER_BLOCK + (threadIdx.x / US_GROUP); q < w; q += gstride) {
+    constexpr int GROUPS_PER_BLOCK = US_THREADS / G;
+    const int gl = lane & (G - 1);
+    const u32 gmask = ((1u << G) - 1u) << (lane & ~(G - 1));
+    const i64 gstride = (i64)gridDim.x * GROUPS_PER_BLOCK;
+    for (i64 q = (i64)blockIdx.x * GROUPS_PER_BLOCK + (threadIdx.x / G); q < w; q += gstride) {
         const i64 u = win_uuid[q];
+        const i64 ws = win_start[q], we = win_end[q];
         i64 a = 0, b = 0;
         if (u >= 0 && u < n_uuids) {
-            const i64 lo = off[u], hi = off[u + 1];
-            if (lo < hi) {
-                const i64 ws = win_start[q], we = win_end[q];
-                const i64 t_lo = __ldg(&ts[lo]), t_hi = __ldg(&ts[hi - 1]);
-                a = us_search<true>(ts, lo, hi, ws, t_lo, t_hi, gl, gmask);
-                b = us_search<false>(ts, lo, hi, we, t_lo, t_hi, gl, gmask);
-                if (b < a) b = a;
+            UsSeg e;
+            if (TAB) {
+                const longlong2 x = th_ld16(&tab[u]);
+                const longlong2 y = th_ld16(reinterpret_cast<const char *>(&tab[u]) + 16);
+                e.lo = x.x; e.n = x.y; e.t_lo = y.x; e.inv = __longlong_as_double(y.y);
+            } else {
+                e = us_make_seg(off, ts, u);
+            }
+            if (e.n > 0) {
+                us_range<G>(ts + e.lo, e, ws, we, gl, gmask, a, b);
+                a += e.lo;
+                b += e.lo;
             }
         }
         i64 sg = 0, sm = 0;
-        if (VEC) {
-            const i64 c1 = (b + 15) >> 4;                       // 16-sample chunks, 16-byte aligned
-            for (i64 c = (a >> 4) + gl; c < c1; c += US_GROUP) {
-                const i64 i0 = c << 4;
-                const int lo = (int)(a > i0 ? a - i0 : 0);
-                const int hi = (int)(b < i0 + 16 ? b - i0 : 16);
-                if (i0 + 16 <= s_total) {
-                    const uint4 g4 = __ldg(reinterpret_cast<const uint4 *>(gpu + i0));
-                    const uint4 m4 = __ldg(reinterpret_cast<const uint4 *>(mem + i0));
-                    sg += us_sum16(g4, lo, hi);
-                    sm += us_sum16(m4, lo, hi);
-                } else {
-                    for (int t = lo; t < hi; ++t) { sg += gpu[i0 + t]; sm += mem[i0 + t]; }
-                }
-            }
+        if (ELEM == 8) {
+            const i64 *gpu = static_cast<const i64 *>(gpu_v), *mem = static_cast<const i64 *>(mem_v);
+            if (VEC) us_sum_i64<G>(gpu, mem, s_total, a, b, gl, sg, sm);
+            else for (i64 i = a + gl; i < b; i += G) { sg += __ldg(&gpu[i]); sm += __ldg(&mem[i]); }
         } else {
-            for (i64 i = a + gl; i < b; i += US_GROUP) { sg += gpu[i]; sm += mem[i]; }
+            const u8 *gpu = static_cast<const u8 *>(gpu_v), *mem = static_cast<const u8 *>(mem_v);
+            if (VEC) us_sum_u8<G>(gpu, mem, s_total, a, b, gl, sg, sm);
+            else for (i64 i = a + gl; i < b; i += G) { sg += gpu[i]; sm += mem[i]; }
         }
 #pragma unroll
-        for (int o = US_GROUP / 2; o > 0; o >>= 1) {
+        for (int o = G / 2; o > 0; o >>= 1) {
             sg += __shfl_xor_sync(gmask, sg, o);
             sm += __shfl_xor_sync(gmask, sm, o);
         }
@@ -222,6 +269,16 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_u8_kernel(i64 s_total, i6
             if (o_am) o_am[q] = c > 0 ? us_floor_div(sm, c) : -1;
         }
     }
+}
+
+template <int ELEM, bool VEC, int G>
+void us_launch(bool tab_mode, int grid, cudaStream_t st, i64 s, i64 n_uuids, const i64 *off, const UsSeg *tab, const i64 *ts,
+               const void *g, const void *m, i64 w, const i64 *wu, const i64 *ws, const i64 *we, i64 *sg, i64 *sm, i64 *c,
+               i64 *ag, i64 *am) {
+    if (tab_mode)
+        k4_usage_kernel<ELEM, VEC, true, G><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
+    else
+        k4_usage_kernel<ELEM, VEC, false, G><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
 }
 
 }  // namespace
@@ -261,31 +318,25 @@ static int usage_reduce_impl(int elem, int device, int64_t s, int64_t n_uuids, c
             US_TRY(sc.out(out_avg_gpu, 8 * zw, mem, &d_ag));
             US_TRY(sc.out(out_avg_mem, 8 * zw, mem, &d_am));
             const bool vec = (((uintptr_t)d_g | (uintptr_t)d_m) & 15) == 0;
-            const int grid = th_grid_for(w, US_GROUPS_PER_BLOCK, 64);
-            if (elem == 1 && vec)
-                k4_usage_u8_kernel<true><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
-                                                                      (const u8 *)d_g, (const u8 *)d_m, w,
-                                                                      (const i64 *)d_wu, (const i64 *)d_ws,
-                                                                      (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
-                                                                      (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
-            else if (elem == 1)
-                k4_usage_u8_kernel<false><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
-                                                                       (const u8 *)d_g, (const u8 *)d_m, w,
-                                                                       (const i64 *)d_wu, (const i64 *)d_ws,
-                                                                       (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
-                                                                       (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
-            else if (vec)
-                k4_usage_kernel<true><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
-                                                                   (const i64 *)d_g, (const i64 *)d_m, w,
-                                                                   (const i64 *)d_wu, (const i64 *)d_ws,
-                                                                   (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
-                                                                   (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
-            else
-                k4_usage_kernel<false><<<grid, US_THREADS, 0, st>>>(s, n_uuids, (const i64 *)d_off, (const i64 *)d_ts,
-                                                                    (const i64 *)d_g, (const i64 *)d_m, w,
-                                                                    (const i64 *)d_wu, (const i64 *)d_ws,
-                                                                    (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm,
-                                                                    (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
+            // lanes per window, measured on config 3: 8 / 4 / 2 lanes = 2.98 / 3.34 / 4.9 ms for int64 columns (a
+            // 100-sample window is 50 16-byte pairs) and 2.00 / 1.82 / 2.9 ms for uint8 columns (7 16-byte chunks)
+            const int lanes = elem == 1 ? 4 : 8;
+            const int grid = th_grid_for(w, US_THREADS / lanes, 64);
+            // per-uuid entries: worth a pass over the uuids unless there are far more of them than windows
+            const bool tab_mode = n_uuids > 0 && n_uuids <= 4 * w + 1024;
+            void *d_tab = nullptr;
+            if (tab_mode) {
+                US_TRY(sc.alloc(&d_tab, sizeof(UsSeg) * zu));
+                k4_segments_kernel<<<(unsigned)((n_uuids + 255) / 256), 256, 0, st>>>(n_uuids, (const i64 *)d_off,
+                                                                                     (const i64 *)d_ts, (UsSeg *)d_tab);
+            }
+#define US_ARGS tab_mode, grid, st, s, n_uuids, (const i64 *)d_off, (const UsSeg *)d_tab, (const i64 *)d_ts, d_g, d_m, w, \
+                (const i64 *)d_wu, (const i64 *)d_ws, (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm, (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am
+            if (elem == 1 && vec) us_launch<1, true, 4>(US_ARGS);
+            else if (elem == 1) us_launch<1, false, 4>(US_ARGS);
+            else if (vec) us_launch<8, true, 8>(US_ARGS);
+            else us_launch<8, false, 8>(US_ARGS);
+#undef US_ARGS
             cudaError_t e = cudaGetLastError();
             if (e != cudaSuccess) { th_set_error("th_usage_reduce: launch -> %s", cudaGetErrorString(e)); rc = TH_ECUDA; break; }
             US_TRY(th_copy_back(out_sum_gpu, d_sg, 8 * zw, mem, st));

@@ -320,6 +320,63 @@ def test_usage_reduce_touching_windows_share_the_boundary_sample(th):
     assert list(ag) == [20, 65, -1] and list(am) == [1, 1, -1]
 
 
+@pytest.mark.parametrize('n_uuids,n_windows', [(9, 4000), (6000, 200)])     # with and without the per-uuid entry table
+@pytest.mark.parametrize('narrow', [False, True])
+def test_usage_reduce_irregular_logs(th, brute, n_uuids, n_windows, narrow):
+    """Logs the interpolation guess cannot hit: exponential and bursty spacing, repeated timestamps, segments of
+    0 / 1 / 2 / 15 / 16 / 17 samples, an odd total length, windows far outside the log and at the int64 extremes."""
+    rng = np.random.default_rng(100 + n_uuids)
+    sizes = [0, 1, 2, 15, 16, 17, 333, 4096, 2501][:n_uuids] if n_uuids <= 9 else list(rng.integers(0, 40, size=n_uuids))
+    ts_parts = []
+    for k, n in enumerate(sizes):
+        kind = k % 4
+        if kind == 0:
+            t = np.cumsum(rng.integers(0, 3, size=n))                      # many repeated timestamps
+        elif kind == 1:
+            t = np.floor(np.exp(np.linspace(0, 30, n))).astype(np.int64) if n else np.zeros(0, np.int64)   # exponential
+        elif kind == 2:
+            t = np.cumsum(np.where(rng.random(n) < 0.02, 10**9, 1))        # bursts separated by huge gaps
+        else:
+            t = np.cumsum(rng.integers(1, 2_000_000, size=n))
+        ts_parts.append(np.sort(t.astype(np.int64)) + 1_700_000_000_000_000)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    ts = np.concatenate(ts_parts) if ts_parts else np.zeros(0, np.int64)
+    s = int(off[-1])
+    assert n_uuids > 9 or s % 2 == 1
+    gpu = rng.integers(0, 101, size=s, dtype=np.int64)
+    mem = rng.integers(0, 101, size=s, dtype=np.int64)
+    wu = rng.integers(-1, n_uuids + 1, size=n_windows, dtype=np.int64)     # includes unknown uuids on both sides
+    ws = np.empty(n_windows, np.int64)
+    we = np.empty(n_windows, np.int64)
+    for j in range(n_windows):
+        u = int(wu[j])
+        a, b = (int(off[u]), int(off[u + 1])) if 0 <= u < n_uuids else (0, 0)
+        c = rng.random()
+        if b > a and c < 0.6:                                   # ends exactly on samples
+            i, k = sorted(rng.integers(a, b, size=2))
+            ws[j], we[j] = ts[i], ts[k]
+        elif b > a and c < 0.8:                                 # just beside samples
+            i, k = sorted(rng.integers(a, b, size=2))
+            ws[j], we[j] = ts[i] + rng.integers(-1, 2), ts[k] + rng.integers(-1, 2)
+        elif c < 0.85:
+            ws[j], we[j] = np.iinfo(np.int64).min, np.iinfo(np.int64).max
+        elif c < 0.9:
+            ws[j], we[j] = np.iinfo(np.int64).max - 5, np.iinfo(np.int64).max
+        elif c < 0.95:
+            ws[j], we[j] = np.iinfo(np.int64).min, np.iinfo(np.int64).min + 5
+        else:
+            ws[j], we[j] = 1_700_000_000_000_500, 1_700_000_000_000_100       # end before start
+    if narrow:
+        outs = th.usage_reduce_u8(off, ts, gpu.astype(np.uint8), mem.astype(np.uint8), wu, ws, we)
+    else:
+        outs = th.usage_reduce(off, ts, gpu, mem, wu, ws, we)
+    esg, esm, ecnt = brute.usage_reduce(off, ts, gpu, mem, wu, ws, we)
+    assert np.array_equal(outs[2], ecnt)
+    assert np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm)
+    assert np.array_equal(outs[3], np.array([brute.floor_avg(a, c) for a, c in zip(esg, ecnt)]))
+    assert (ecnt == 0).any() and (ecnt > 16).any()
+
+
 def test_usage_reduce_unaligned_columns_and_negative_values(th, brute):
     rng = np.random.default_rng(8)
     n = 5001

@@ -1,9 +1,12 @@
 #!/usr/bin/env python
-"""Per-instruction stall-sample shares of one kernel in an .ncu-rep:  python tools/ncu_sass.py rep regex [min_pct]"""
+"""Per-instruction stall-sample shares of one kernel in an .ncu-rep:
+python tools/ncu_sass.py rep regex [min_pct [skip]]   (regex on the base name; skip = matching launches to pass over)"""
 import csv, subprocess, sys
 rep, rx = sys.argv[1], sys.argv[2]
 minp = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
-raw = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name', 'regex:' + rx], capture_output=True, text=True).stdout
+skip = sys.argv[4] if len(sys.argv) > 4 else '0'
+raw = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-name', 'regex:' + rx, '--launch-skip', skip,
+                      '--launch-count', '1'], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hidx = [i for i, r in enumerate(rows) if r and r[0] == 'Address']
 h = rows[hidx[0]]

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Short, fixed launch sequence for ncu: snapshot load (K1 + index build) on BASELINE config 2, three
-flushed K2 launches, then three K4 launches on a 1/5-scale config 3.  Run plain first, then under ncu
+flushed K2 launches, then three K4 launches on config 3 (TH_PROF_SCALE, default 1.0 = 1 B samples) and three of the
+uint8 format.  Run plain first, then under ncu
 (see /opt/skills/guides/B200_PROFILING.md); a number printed under ncu is never a bench value."""
 import ctypes as C
 import os
@@ -14,7 +15,7 @@ sys.path.insert(0, ROOT)
 import tensorhive_fixed_b200 as th                      # noqa: E402
 from tensorhive_fixed_b200 import native, synth         # noqa: E402
 
-SCALE = float(os.environ.get('TH_PROF_SCALE', '0.2'))
+SCALE = float(os.environ.get('TH_PROF_SCALE', '1.0'))
 dev = torch.device('cuda:0')
 lib = native.load()
 cal = synth.make_calendar(1_000_000, 4096, seed=20260102)
@@ -47,3 +48,10 @@ for _ in range(3):
                                      wu.data_ptr(), ws.data_ptr(), we.data_ptr(), *[o.data_ptr() for o in outs], 1, sp))
 torch.cuda.synchronize()
 print('k4 samples inside windows:', int(outs[2].sum().item()))
+g8, m8 = gpu.to(torch.uint8), mem.to(torch.uint8)
+del gpu, mem
+for _ in range(3):
+    native.check(lib.th_usage_reduce_u8(0, S, U, off.data_ptr(), ts.data_ptr(), g8.data_ptr(), m8.data_ptr(), W,
+                                        wu.data_ptr(), ws.data_ptr(), we.data_ptr(), *[o.data_ptr() for o in outs], 1, sp))
+torch.cuda.synchronize()
+print('k4 u8 samples inside windows:', int(outs[2].sum().item()))
