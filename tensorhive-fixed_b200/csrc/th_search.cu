@@ -178,6 +178,11 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // running the row probes only on full batches of 32 (dense lanes, level 3 once per ~3 tiles): correct, but
     // 43.9 us cold / 483 us at 16 M queries -- the queue traffic, the extra ballots and atomicOr of late bits cost
     // far more issue slots than the idle lanes they save.
+    // Also measured and dropped: level 2 of tile k + 1 under level 3 of tile k WITHOUT registers or scoreboards -- each
+    // lane copies its cell into shared memory with a 16-byte cp.async gather, one commit group behind the query stage:
+    // 24.5 us cold (same), 15.5 vs 14.5 us warm, 209 vs 213 us at 16 M queries, and 421 vs 375 us on 12.5 M rows x
+    // 12.5 M queries, where every probe misses L2.  More probes in flight do not help: at that size the kernel moves
+    // ~3.5 TB/s of scattered 32-byte sectors, which is what HBM delivers for this access pattern.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
