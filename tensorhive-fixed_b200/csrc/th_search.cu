@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // lane copies its cell into shared memory with a 16-byte cp.async gather, one commit group behind the query stage:
     // 24.5 us cold (same), 15.5 vs 14.5 us warm, 209 vs 213 us at 16 M queries, and 421 vs 375 us on 12.5 M rows x
     // 12.5 M queries, where every probe misses L2.  More probes in flight do not help: at that size the kernel moves
-    // ~3.5 TB/s of scattered 32-byte sectors, which is what HBM delivers for this access pattern.
+    // ~3 TB/s of scattered 32-byte sectors (about 2.7 per query), about what HBM delivers for this access pattern.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
