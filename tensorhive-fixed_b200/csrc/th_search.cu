@@ -183,6 +183,10 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // 24.5 us cold (same), 15.5 vs 14.5 us warm, 209 vs 213 us at 16 M queries, and 421 vs 375 us on 12.5 M rows x
     // 12.5 M queries, where every probe misses L2.  More probes in flight do not help: at that size the kernel moves
     // ~3 TB/s of scattered 32-byte sectors (about 2.7 per query), about what HBM delivers for this access pattern.
+    // Also measured and dropped: a 64-byte record per grid cell (header + first three rows, one HBM atom per query)
+    // read by a one-level fast path that defers self-updates with an unfiltered conflict and long buckets (~7 % of
+    // the lanes) to a per-CTA queue resolved densely after the CTA's tiles: 32.5 us cold / 24 us warm, and 503 vs 387 us
+    // on 12.5 M x 12.5 M -- the extra loads per lane and the thin, latency-bound tail cost more than the level saved.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
