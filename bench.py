@@ -432,7 +432,7 @@ def run_ours(args):
 
     # ---- BASELINE config 4: ProtectionService + job-queue sweep over the same calendar ---------------------------
     if not args.skip_sweep:
-        line['service_sweep'] = bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak)
+        line['service_sweep'] = bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd)
 
     # ---- K4 on BASELINE config 3, generated on the device -------------------------------------------------------
     if not args.skip_usage:
@@ -457,7 +457,7 @@ def th_snapshot_wrapper(snap):
     return snap
 
 
-def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
+def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd=None):
     """BASELINE configs[3]: 1M live GPU processes joined against the current reservation owners (K3 + K5,
     ProtectionService.py:84-102) and 100k queued jobs' tasks tested against upcoming reservations (K5,
     JobSchedulingService.py:117-132), device-resident inputs, cold L2, median of 10."""
@@ -503,6 +503,26 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
     off, ids, canc = snapshot.conflict_sets(np.arange(U, dtype=np.int64), r_s, r_e, None, 1)
     ms_range = 1e3 * (time.perf_counter() - t0)
     torch.cuda.synchronize()
+    # conflict SETS of the whole candidate batch (R1's list form: ids ascending, cancelled rows included with their flag),
+    # device-resident; the call counts, scans, synchronises once for the capacity check, fills and ranks by id
+    sets = None
+    if qd is not None:
+        import ctypes as C
+        M = int(qd[0].numel())
+        cap = 8 * M
+        s_off = torch.empty(M + 1, dtype=torch.int64, device=dev)
+        s_ids = torch.empty(cap, dtype=torch.int64, device=dev)
+        s_canc = torch.empty(cap, dtype=torch.uint8, device=dev)
+        needed = C.c_int64(0)
+
+        def sets_step():
+            native.check(lib.th_conflict_sets(snap._h, M, qd[0].data_ptr(), qd[1].data_ptr(), qd[2].data_ptr(),
+                                              qd[3].data_ptr(), 0, s_off.data_ptr(), s_ids.data_ptr(), s_canc.data_ptr(),
+                                              cap, C.byref(needed), 1, sp))
+        ms_sets = med(sets_step)
+        sets = {'ms': ms_sets, 'queries_per_s': M / (ms_sets * 1e-3), 'rows_returned': int(needed.value),
+                'note': 'th_conflict_sets(TH_MODE_STRICT) on the config-2 batch, device arrays; four kernels and one '
+                        'host synchronisation (capacity check) inside the call'}
     join_bytes = P * 16 + P * 9 + U * 16          # the K5 join proper
     return {'workload': 'BASELINE configs[3]: 1M GPU processes + 100k queued jobs (%d tasks) vs the config-2 calendar' % T,
             'violation_join': {'ms': ms_join, 'processes_per_s': P / (ms_join * 1e-3), 'violations': int(flags.sum().item()),
@@ -511,6 +531,7 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak):
                                'note': 'two launches: K3 current-owner table over %d uuids, then the K5 join' % U},
             'job_tasks': {'ms': ms_task, 'tasks_per_s': T / (ms_task * 1e-3), 'interfering': int(tflags.sum().item())},
             'gpu_slots': {'ms': ms_up, 'uuids_per_s': U / (ms_up * 1e-3)},
+            'conflict_sets': sets,
             'calendar_range': {'ms_host_call': ms_range, 'ranges': U, 'rows_returned': int(len(ids)),
                                'note': 'th_conflict_sets(TH_MODE_INCLUSIVE), host arrays, wall clock incl. copies'}}
 

@@ -108,7 +108,7 @@ __device__ __forceinline__ UpAcc lk_upcoming(const ThGrid &g, i64 u, const ThP1 
     return a;
 }
 
-constexpr int LK_GROUP = 8;
+constexpr int LK_GROUP = 4;   // lanes per uuid / task: 250 k job tasks in 22.5 us with 4 lanes, 27.5 us with 8 (chains of dependent probes)
 constexpr int LK_GROUPS_PER_BLOCK = LK_THREADS / LK_GROUP;
 
 __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(ThGrid g, const int *__restrict__ seg, const ThP1 *__restrict__ p1,

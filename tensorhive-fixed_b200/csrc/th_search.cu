@@ -286,6 +286,12 @@ __device__ __forceinline__ bool cs_more(int mode, const RowView &v, int c1, i64 
     return e.x >= qs || e.y > qs;
 }
 
+// G lanes per query (32: one warp per query, for few long lists; 4: eight queries per warp, for large batches of
+// short lists -- the walk is a chain of dependent probes, so what matters is how many queries are in flight).
+template <int G>
+__device__ __forceinline__ u32 cs_gmask(int lane) { return G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << (lane & ~(G - 1))); }
+
+template <int G>
 __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i64 n_uuids, i64 m,
                                                                   const i64 *__restrict__ q_uuid,
                                                                   const i64 *__restrict__ q_start,
@@ -293,9 +299,10 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
                                                                   const i64 *__restrict__ q_self, int mode,
                                                                   int *__restrict__ out_cnt, int *__restrict__ out_beg,
                                                                   int *__restrict__ out_end) {
-    const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * CS_WARPS;
-    for (i64 q = (i64)blockIdx.x * CS_WARPS + (threadIdx.x >> 5); q < m; q += wstride) {
+    const int lane = threadIdx.x & 31, gl = lane & (G - 1);
+    const u32 gmask = cs_gmask<G>(lane);
+    const i64 gstride = (i64)gridDim.x * (CS_THREADS / G);
+    for (i64 q = (i64)blockIdx.x * (CS_THREADS / G) + (threadIdx.x / G); q < m; q += gstride) {
         const i64 u = q_uuid[q];
         int cnt = 0, beg = 0, pend = 0;
         if (u >= 0 && u < n_uuids) {
@@ -307,40 +314,42 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
             int c1 = pend;
             beg = pend;
             while (c1 > lo && cs_more(mode, v, c1, qs)) {
-                const int c0 = c1 - 32 > lo ? c1 - 32 : lo;
-                const int j = c0 + lane;
+                const int c0 = c1 - G > lo ? c1 - G : lo;
+                const int j = c0 + gl;
                 bool mt = false;
                 if (j < c1) {
                     const longlong2 e = th_ld16(&v.p3[j]);   // {end, idc}
                     const i64 s = (mode == TH_MODE_UPCOMING) ? __ldg(&v.p1[j].start) : 0;
                     mt = cs_match(mode, s, e.x, e.y, qs, self);
                 }
-                cnt += __popc(__ballot_sync(0xffffffffu, mt));
+                cnt += __popc(__ballot_sync(gmask, mt) & gmask);
                 beg = c0;
                 c1 = c0;
             }
         }
-        if (lane == 0) { out_cnt[q] = cnt; out_beg[q] = beg; out_end[q] = pend; }
+        if (gl == 0) { out_cnt[q] = cnt; out_beg[q] = beg; out_end[q] = pend; }
     }
 }
 
+template <int G>
 __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64 m, const i64 *__restrict__ q_start,
                                                                  const i64 *__restrict__ q_self, int mode,
                                                                  const int *__restrict__ beg_arr,
                                                                  const int *__restrict__ end_arr,
                                                                  const i64 *__restrict__ offsets,
                                                                  i64 *__restrict__ out_ids, u8 *__restrict__ out_canc) {
-    const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * CS_WARPS;
-    for (i64 q = (i64)blockIdx.x * CS_WARPS + (threadIdx.x >> 5); q < m; q += wstride) {
+    const int lane = threadIdx.x & 31, gl = lane & (G - 1);
+    const u32 gmask = cs_gmask<G>(lane);
+    const i64 gstride = (i64)gridDim.x * (CS_THREADS / G);
+    for (i64 q = (i64)blockIdx.x * (CS_THREADS / G) + (threadIdx.x / G); q < m; q += gstride) {
         const i64 o0 = offsets[q];
         if (offsets[q + 1] == o0) continue;
         const int beg = beg_arr[q], pend = end_arr[q];
         const i64 qs = q_start[q];
         const i64 self = q_self ? q_self[q] : -1;
         i64 o = o0;
-        for (int c0 = beg; c0 < pend; c0 += 32) {
-            const int j = c0 + lane;
+        for (int c0 = beg; c0 < pend; c0 += G) {
+            const int j = c0 + gl;
             bool mt = false;
             longlong2 e = make_longlong2(0, 0);
             if (j < pend) {
@@ -348,7 +357,7 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64
                 const i64 s = (mode == TH_MODE_UPCOMING) ? __ldg(&v.p1[j].start) : 0;
                 mt = cs_match(mode, s, e.x, e.y, qs, self);
             }
-            const u32 bal = __ballot_sync(0xffffffffu, mt);
+            const u32 bal = __ballot_sync(gmask, mt) & gmask;
             if (mt) {
                 const i64 pos = o + __popc(bal & ((1u << lane) - 1));
                 out_ids[pos] = th_idc_id(e.y);
@@ -361,16 +370,17 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64
 
 // rows come out of the fill pass in (start, id) order; SQLite returns them in rowid = ascending-id order.
 // Ids are unique, so the rank of an id inside its list is the number of smaller ids.
+template <int G>
 __global__ void __launch_bounds__(CS_THREADS) k2_sets_order_kernel(i64 m, const i64 *__restrict__ offsets,
                                                                   const i64 *__restrict__ tmp_ids,
                                                                   const u8 *__restrict__ tmp_canc,
                                                                   i64 *__restrict__ out_ids, u8 *__restrict__ out_canc) {
-    const int lane = threadIdx.x & 31;
-    const i64 wstride = (i64)gridDim.x * CS_WARPS;
-    for (i64 q = (i64)blockIdx.x * CS_WARPS + (threadIdx.x >> 5); q < m; q += wstride) {
+    const int gl = threadIdx.x & (G - 1);
+    const i64 gstride = (i64)gridDim.x * (CS_THREADS / G);
+    for (i64 q = (i64)blockIdx.x * (CS_THREADS / G) + (threadIdx.x / G); q < m; q += gstride) {
         const i64 o0 = offsets[q], o1 = offsets[q + 1];
         const i64 c = o1 - o0;
-        for (i64 k = lane; k < c; k += 32) {
+        for (i64 k = gl; k < c; k += G) {
             const i64 mine = tmp_ids[o0 + k];
             i64 rank = 0;
             for (i64 t = 0; t < c; ++t) rank += tmp_ids[o0 + t] < mine ? 1 : 0;
@@ -600,9 +610,17 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_TRY(sc.alloc((void **)&d_end, 4 * zm));
     RowView v;
     v.seg = h->seg; v.p1 = h->p1; v.p3 = h->p3; v.p4 = h->p4; v.g = th_grid_of(h);
-    const int wgrid = th_grid_for(m, CS_WARPS, 16);
-    k2_sets_count_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
-                                                       (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
+    // large batches (would_interfere for a whole candidate list): 4 lanes per query, eight queries per warp (1 M
+    // config-2 candidates, 1.25 M rows returned: 0.54 / 0.37 / 0.26 / 0.185 ms with 32 / 16 / 8 / 4 lanes -- the walk is
+    // a chain of dependent probes, so queries in flight are what counts); a few calendar ranges: one warp per query
+    const bool narrow = m >= 32768;
+    const int wgrid = th_grid_for(m, narrow ? CS_THREADS / 4 : CS_WARPS, 16);
+    if (narrow)
+        k2_sets_count_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
+                                                              (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
+    else
+        k2_sets_count_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
+                                                               (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
     TH_CUDA(cudaGetLastError());
     i64 *d_total;
     TH_TRY(sc.alloc((void **)&d_total, 16));       // [0] = total rows, [1] = longest list
@@ -622,18 +640,30 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_TRY(sc.out(out_ids, 8 * (size_t)total, mem, &d_ids));
     TH_TRY(sc.out(out_cancelled_u8, (size_t)total, mem, &d_canc));
     if (mode == TH_MODE_UPCOMING) {
-        k2_sets_fill_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                          (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
+        if (narrow)
+            k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                 (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
+        else
+            k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                  (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
     } else {
         i64 *t_ids; u8 *t_canc;
         TH_TRY(sc.alloc((void **)&t_ids, 8 * (size_t)total));
         TH_TRY(sc.alloc((void **)&t_canc, (size_t)total));
-        k2_sets_fill_kernel<<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                          (const i64 *)d_off, t_ids, t_canc);
+        if (narrow)
+            k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                 (const i64 *)d_off, t_ids, t_canc);
+        else
+            k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                  (const i64 *)d_off, t_ids, t_canc);
         if (longest <= 64 || total >= (1ll << 30) || m >= (1ll << 32)) {
             // short lists: rank by counting inside the warp (c^2 / 32 compares per list)
-            k2_sets_order_kernel<<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
-                                                               (u8 *)d_canc);
+            if (narrow)
+                k2_sets_order_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
+                                                                      (u8 *)d_canc);
+            else
+                k2_sets_order_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
+                                                                       (u8 *)d_canc);
         } else {
             // calendar views return thousands of rows per uuid: sort all of them by (query, id) with K1 instead
             ThRec *ra, *rb, *sorted;

@@ -191,10 +191,11 @@ def test_bad_arguments_are_reported_not_thrown_across_the_abi(th, synth):
 
 
 # ---- K2 row lists ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('m', [5000, 40_000])       # one warp per query / 8 lanes per query (batches >= 32768)
 @pytest.mark.parametrize('mode_name', ['STRICT', 'INCLUSIVE', 'UPCOMING'])
-def test_conflict_sets_match_brute_force(th, synth, brute, mode_name):
+def test_conflict_sets_match_brute_force(th, synth, brute, mode_name, m):
     cal = synth.make_calendar(30_000, 40, seed=77, skew=0.8)
-    q = synth.make_queries(cal, 5000, seed=78)
+    q = synth.make_queries(cal, m, seed=78)
     mode = getattr(th, 'MODE_' + mode_name)
     bmode = getattr(brute, mode_name)
     qs, qe = q['start'].copy(), q['end'].copy()
