@@ -67,10 +67,11 @@ __global__ void __launch_bounds__(256) ld_stats_kernel(const i64 *__restrict__ i
 }
 
 // records keyed by id (only when the caller's rows are not already in ascending-id order)
-__global__ void __launch_bounds__(256) ld_idrec_kernel(const i64 *__restrict__ id, i64 n, i64 min_id, ThRec *rec) {
+__global__ void __launch_bounds__(256) ld_idrec_kernel(const i64 *__restrict__ id, i64 n, i64 min_id, ThRec *rec,
+                                                       i64 base = 0) {   // rows [base, base + n) of the columns
     for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
         ThRec r;
-        r.k0 = (u64)(id[i] - min_id); r.k1 = 0; r.idx = (u32)i;
+        r.k0 = (u64)(id[base + i] - min_id); r.k1 = 0; r.idx = (u32)(base + i);
         rec[i] = r;
     }
 }
@@ -84,6 +85,29 @@ __global__ void __launch_bounds__(256) ld_keyrec_kernel(const i64 *__restrict__ 
         ThRec r;
         r.k0 = (u64)(start[i] - min_start); r.k1 = (u32)uuid[i]; r.idx = i;
         rec[j] = r;
+    }
+}
+
+// Merge of two runs that are each in (uuid, start, id) order -- the survivors of a snapshot and a sorted delta
+// (SURVEY.md section 8f item 1).  Ids are unique, so the order is total and every record's place in the output is its
+// own index plus the number of records of the OTHER run that precede it: one binary search per record, no passes.
+__device__ __forceinline__ bool mg_less(const ThRec &a, const ThRec &b, const i64 *__restrict__ id) {
+    if (a.k1 != b.k1) return a.k1 < b.k1;
+    if (a.k0 != b.k0) return a.k0 < b.k0;
+    return id[a.idx] < id[b.idx];
+}
+__global__ void __launch_bounds__(256) mg_merge_kernel(const ThRec *__restrict__ a, i64 na, const ThRec *__restrict__ b,
+                                                       i64 nb, const i64 *__restrict__ id, ThRec *__restrict__ out) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < na + nb; i += (i64)gridDim.x * blockDim.x) {
+        const bool from_a = i < na;
+        const ThRec x = from_a ? a[i] : b[i - na];
+        const ThRec *other = from_a ? b : a;
+        i64 lo = 0, hi = from_a ? nb : na;
+        while (lo < hi) {                       // how many records of the other run come before x
+            const i64 mid = lo + ((hi - lo) >> 1);
+            if (mg_less(other[mid], x, id)) lo = mid + 1; else hi = mid;
+        }
+        out[(from_a ? i : i - na) + lo] = x;
     }
 }
 
@@ -382,9 +406,11 @@ __global__ void __launch_bounds__(256) dl_append_kernel(i64 n_up, i64 base, cons
 
 }  // namespace
 
-extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
-                                const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
-                                const uint8_t *cancelled_u8, int mem, void *stream) {
+// `presorted` >= 0: rows [0, presorted) are already in (uuid, start, id) order (th_snapshot_apply_delta hands over
+// the survivors of the source snapshot that way); only the rows behind them are sorted, then the two runs are merged.
+static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
+                        const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
+                        const uint8_t *cancelled_u8, int mem, void *stream, int64_t presorted) {
     TH_REQUIRE(h != nullptr, "th_snapshot_load: handle is NULL");
     TH_REQUIRE(n >= 0 && n < (1ll << 30), "th_snapshot_load: n=%lld outside [0, 2^30)", (long long)n);
     TH_REQUIRE(n_uuids >= 0 && n_uuids < (1ll << 30), "th_snapshot_load: n_uuids=%lld outside [0, 2^30)",
@@ -462,6 +488,34 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
         const ThRec *order = nullptr;
         ThRec *sorted = nullptr;
         ThRec *key_a = ra, *key_b = rb;
+        if (presorted >= 0) {
+            const i64 nb = n - presorted;
+            ld_keyrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, nullptr, presorted,
+                                                   stats.min_start, ra);                 // run A: as it stands
+            TH_CUDA(cudaGetLastError());
+            sorted = ra;
+            if (nb > 0) {
+                // run B: the delta rows, by id first so that the stable key sort leaves ties in id order
+                ThRec *ba = nullptr, *bb = nullptr, *bc = nullptr, *b_id = nullptr, *b_key = nullptr;
+                TH_TRY(sc.alloc((void **)&ba, sizeof(ThRec) * (size_t)nb));
+                TH_TRY(sc.alloc((void **)&bb, sizeof(ThRec) * (size_t)nb));
+                TH_TRY(sc.alloc((void **)&bc, sizeof(ThRec) * (size_t)nb));
+                const int bgrid = th_grid_for(nb, 256 * 4, 8);
+                ld_idrec_kernel<<<bgrid, 256, 0, st>>>((const i64 *)d_id, nb, stats.min_id, ba, presorted);
+                TH_CUDA(cudaGetLastError());
+                TH_TRY(th_radix_sort(ba, bb, nb, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &b_id, &passes, st));
+                passes_total += passes;
+                ThRec *other = (b_id == ba) ? bb : ba;
+                ld_keyrec_kernel<<<bgrid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, b_id, nb, stats.min_start, bc);
+                TH_CUDA(cudaGetLastError());
+                TH_TRY(th_radix_sort(bc, other, nb, th_bits_for((u64)(stats.max_start - stats.min_start)),
+                                     th_bits_for((u64)stats.max_uuid), &b_key, &passes, st));
+                passes_total += passes;
+                mg_merge_kernel<<<grid, 256, 0, st>>>(ra, presorted, b_key, nb, (const i64 *)d_id, rb);
+                TH_CUDA(cudaGetLastError());
+                sorted = rb;
+            }
+        } else {
         if (stats.id_inversions > 0) {
             // rows are not in ascending-id order: establish it first so that the stable (uuid, start)
             // sort leaves equal keys in id order (SQLite's scan order for ties).
@@ -482,6 +536,7 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
         TH_TRY(th_radix_sort(key_a, key_b, n, th_bits_for((u64)(stats.max_start - stats.min_start)),
                              th_bits_for((u64)stats.max_uuid), &sorted, &passes, st));
         passes_total += passes;
+        }
         // 3. payload gather + sentinel positions
         ld_finalize_kernel<<<grid, 256, 0, st>>>(sorted, n, n_uuids, stats.min_start, (const i64 *)d_id,
                                                  (const i64 *)d_end, (const i64 *)d_owner, (const u8 *)d_canc, h->p1,
@@ -538,6 +593,12 @@ extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, cons
     return TH_OK;
 }
 
+extern "C" int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
+                                const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
+                                const uint8_t *cancelled_u8, int mem, void *stream) {
+    return th_load_impl(h, n, n_uuids, id, uuid_id, start_us, end_us, owner, cancelled_u8, mem, stream, -1);
+}
+
 extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uuid_id, int64_t *start_us,
                                   int64_t *end_us, int64_t *owner, uint8_t *cancelled_u8, int64_t *seg_offsets,
                                   int mem, void *stream) {
@@ -577,7 +638,8 @@ extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uu
 // Snapshot maintenance without re-sending the table (the reference commits every write
 // through CRUDModel.save / destroy, tensorhive/models/CRUDModel.py:21-50): `dst` becomes `src` minus the rows whose
 // id is upserted or deleted, plus the upserted rows.  Only the delta crosses PCIe; survivors are gathered from the
-// source snapshot on the device and the table is re-indexed there (same K1 + index build as a load).  dst may be src.
+// source snapshot on the device in their sorted order, the upserted rows are sorted (K1 on the delta only) and merged in
+// with one binary search per record, and the index is rebuilt.  dst may be src.
 extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src, int64_t n_uuids, int64_t n_upsert,
                                        const int64_t *id, const int64_t *uuid_id, const int64_t *start_us,
                                        const int64_t *end_us, const int64_t *owner, const uint8_t *cancelled_u8,
@@ -657,6 +719,7 @@ extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src,
         TH_CUDA(cudaGetLastError());
     }
     // the gathers above read `src`; if dst == src the rebuild below overwrites it only after them (stream order)
-    return th_snapshot_load(dst, n_new, n_uuids, (const int64_t *)c_id, (const int64_t *)c_uuid, (const int64_t *)c_start,
-                            (const int64_t *)c_end, (const int64_t *)c_owner, c_canc, TH_MEM_DEVICE, stream);
+    // survivors come out of the source in (uuid, start, id) order: only the upserted rows are sorted, then merged in
+    return th_load_impl(dst, n_new, n_uuids, (const int64_t *)c_id, (const int64_t *)c_uuid, (const int64_t *)c_start,
+                        (const int64_t *)c_end, (const int64_t *)c_owner, c_canc, TH_MEM_DEVICE, stream, n_keep);
 }

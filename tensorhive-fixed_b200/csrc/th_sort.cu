@@ -247,6 +247,43 @@ void rs_add_passes(RsPlan &plan, int word, int nbits) {
 
 }  // namespace
 
+// Small inputs (a delta of a few hundred rows, a kill list): one CTA, bitonic network in shared memory on
+// (k1, k0, input position) -- the position makes it stable like the LSD passes -- instead of histogram + scan + one
+// launch per digit and a host synchronisation for the look-back watchdog.
+constexpr int RS_SMALL = 2048;
+__global__ void __launch_bounds__(1024) rs_small_sort_kernel(const ThRec *__restrict__ in, ThRec *__restrict__ out, u32 n,
+                                                             u64 mask0, u32 mask1) {
+    __shared__ ThRec s[RS_SMALL];
+    __shared__ u32 pos[RS_SMALL];
+    u32 P = 2;
+    while (P < n) P <<= 1;
+    for (u32 i = threadIdx.x; i < P; i += blockDim.x) {
+        if (i < n) { s[i] = in[i]; pos[i] = i; }
+        else { ThRec pad; pad.k0 = ~0ull; pad.k1 = ~0u; pad.idx = 0; s[i] = pad; pos[i] = ~0u; }
+    }
+    __syncthreads();
+    for (u32 k = 2; k <= P; k <<= 1) {
+        for (u32 j = k >> 1; j > 0; j >>= 1) {
+            for (u32 i = threadIdx.x; i < P; i += blockDim.x) {
+                const u32 l = i ^ j;
+                if (l > i) {
+                    const ThRec x = s[i], y = s[l];
+                    const u32 px = pos[i], py = pos[l];
+                    const u32 x1 = x.k1 & mask1, y1 = y.k1 & mask1;
+                    const u64 x0 = x.k0 & mask0, y0 = y.k0 & mask0;
+                    bool x_after_y;                          // pads (pos = ~0) sort behind every record
+                    if (px == ~0u || py == ~0u) x_after_y = px == ~0u && py != ~0u;
+                    else x_after_y = x1 != y1 ? x1 > y1 : (x0 != y0 ? x0 > y0 : px > py);
+                    const bool ascending = (i & k) == 0;
+                    if (x_after_y == ascending) { s[i] = y; s[l] = x; pos[i] = py; pos[l] = px; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    for (u32 i = threadIdx.x; i < n; i += blockDim.x) out[i] = s[i];
+}
+
 int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **sorted, int *passes,
                   cudaStream_t st) {
     *sorted = a;
@@ -263,6 +300,15 @@ int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **s
     rs_add_passes(plan, 0, k0_bits);
     rs_add_passes(plan, 1, k1_bits);
     if (plan.npass == 0) return TH_OK;
+    if (n <= RS_SMALL) {
+        const u64 mask0 = k0_bits >= 64 ? ~0ull : ((1ull << k0_bits) - 1ull);
+        const u32 mask1 = k1_bits >= 32 ? ~0u : ((1u << k1_bits) - 1u);
+        rs_small_sort_kernel<<<1, 1024, 0, st>>>(a, b, (u32)n, mask0, mask1);
+        TH_CUDA(cudaGetLastError());
+        *sorted = b;
+        if (passes) *passes = 1;
+        return TH_OK;
+    }
 
     static bool attr_set[64] = {false};
     int dev = 0;

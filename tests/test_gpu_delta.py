@@ -77,6 +77,37 @@ def test_random_delta_sequences_equal_a_fresh_load(lib_built, in_place):
     cur.close(); spare.close()
 
 
+def test_large_delta_with_equal_keys_merges_in_id_order(lib_built):
+    """A delta above the single-CTA sort limit whose rows share (uuid, start) with surviving rows and with each other:
+    the merge must interleave them by id, exactly as a sort from scratch would."""
+    import tensorhive_fixed_b200 as th
+    rng = np.random.default_rng(11)
+    u, n = 6, 30_000
+    starts = rng.integers(0, 50, size=n) * 1_000_000                # 50 distinct starts: ties everywhere
+    table = {'id': rng.permutation(np.arange(1, 3 * n, 3))[:n].astype(np.int64),      # ids with gaps, shuffled
+             'uuid_id': rng.integers(0, u, size=n).astype(np.int64), 'start': starts.astype(np.int64),
+             'end': (starts + rng.integers(0, 10**7, size=n)).astype(np.int64),
+             'owner': rng.integers(1, 9, size=n).astype(np.int64), 'cancelled': (rng.random(n) < 0.2).astype(np.uint8)}
+    snap = _fresh(th, table, u)
+    k = 5000
+    new_ids = rng.permutation(np.setdiff1d(np.arange(1, 3 * n), table['id']))[:k].astype(np.int64)   # ids BETWEEN old ones
+    ns = rng.integers(0, 50, size=k) * 1_000_000
+    ups = {'id': new_ids, 'uuid_id': rng.integers(0, u, size=k).astype(np.int64), 'start': ns.astype(np.int64),
+           'end': (ns + rng.integers(0, 10**7, size=k)).astype(np.int64), 'owner': rng.integers(1, 9, size=k).astype(np.int64),
+           'cancelled': (rng.random(k) < 0.2).astype(np.uint8)}
+    gone = rng.choice(n, size=3000, replace=False)
+    snap.apply_delta(snap, u, *[ups[c] for c in COLS], table['id'][gone])
+    keep = np.ones(n, bool)
+    keep[gone] = False
+    truth = {c: np.concatenate([table[c][keep], ups[c]]) for c in COLS}
+    ref = _fresh(th, truth, u)
+    assert _same(snap, ref)
+    ex = snap.export()
+    order = np.lexsort((truth['id'], truth['start'], truth['uuid_id']))
+    assert np.array_equal(ex['id'], truth['id'][order])
+    snap.close(); ref.close()
+
+
 def test_delta_with_device_pointers_and_empty_cases(lib_built):
     import torch
     import tensorhive_fixed_b200 as th
