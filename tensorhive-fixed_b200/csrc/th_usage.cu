@@ -10,9 +10,9 @@
 // lane of a group, so sharing a warp between four windows cuts the issue slots per window by 4 (the first
 // version, one warp per window, was instruction-issue bound at 70 % SM throughput, 36 % DRAM).  Samples of a
 // uuid are ts-sorted, so the window is a contiguous index range [a, b): both ends are located by an
-// interpolation guess followed by ONE coalesced 16-wide probe per end (exact for a regular logging cadence,
+// interpolation guess followed by ONE coalesced 8-wide probe per end (exact for a regular logging cadence,
 // which is what the service produces; the four probe loads of both ends are issued together), with a
-// group-uniform binary search only when a guess misses.  The range is then summed with 16-byte loads of
+// group-uniform galloping search from the window outwards only when a guess misses.  The range is then summed with 16-byte loads of
 // gpu_util / mem_util.  The ts column is only probed, never streamed.
 //
 // The kernel is bound by the dependent chain per window (window columns -> uuid entry -> probes -> samples) times
@@ -71,28 +71,45 @@ __device__ __forceinline__ i64 us_ld8_if(const i64 *p, bool pred, i64 dflt) {
     return v;
 }
 
-// start of the 16-wide probe window for `key` inside a segment of n >= 1 samples (relative index)
+// start of the W-wide probe window for `key` inside a segment of n >= 1 samples (relative index)
+template <int W>
 __device__ __forceinline__ i64 us_window(i64 n, i64 key, i64 t_lo, double inv) {
     double x = ((double)key - (double)t_lo) * inv;        // only a guess: rounding cannot change the result
     x = fmin(fmax(x, 0.0), (double)(n - 1));
-    i64 w0 = (i64)x - 7;
-    if (w0 > n - 16) w0 = n - 16;
+    i64 w0 = (i64)x - (W / 2 - 1);
+    if (w0 > n - W) w0 = n - W;
     if (w0 < 0) w0 = 0;
     return w0;
 }
 
 // From the number of probe-window samples that fail the predicate (a prefix, the segment being ts-sorted) to the first
-// index that satisfies it; a group-uniform binary search only when the whole window lies on one side of the answer.
-template <bool GE>
+// index that satisfies it; a group-uniform search only when the whole window lies on one side of the answer.
+template <bool GE, int W>
 __device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64 key, i64 w0, int nfalse) {
-    const i64 cntw = n - w0 < 16 ? n - w0 : 16;
+    const i64 cntw = n - w0 < W ? n - w0 : W;
+    // The guess missed.  Irregular logs (gaps, restarts) put the answer tens of samples away, rarely thousands: gallop
+    // from the window in doubling steps until the predicate flips, then bisect that bracket -- about 2 log2(distance)
+    // dependent loads instead of log2(n).
+    auto holds = [&](i64 p) { const i64 x = __ldg(&seg[p]); return GE ? (x >= key) : (x > key); };
     i64 l, r;   // the answer lies in [l, r]; the predicate holds at r (r == n counts as "holds")
     if (nfalse == 0) {
         if (w0 == 0) return 0;
-        l = 0; r = w0;
+        r = w0;
+        for (i64 step = W;; step <<= 1) {
+            const i64 p = r - step;
+            if (p <= 0) { l = 0; break; }
+            if (!holds(p)) { l = p + 1; break; }
+            r = p;
+        }
     } else if (nfalse == (int)cntw) {
         if (w0 + cntw == n) return n;
-        l = w0 + cntw; r = n;
+        l = w0 + cntw;
+        for (i64 step = W;; step <<= 1) {
+            const i64 p = l + step - 1;
+            if (p >= n) { r = n; break; }
+            if (holds(p)) { r = p; break; }
+            l = p + 1;
+        }
     } else {
         return w0 + nfalse;
     }
@@ -106,12 +123,12 @@ __device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64
 
 // [a, b) = samples of the segment with ws <= ts <= we, as indices relative to the segment.  Both ends are probed
 // together: four independent loads per lane, then four ballots.  All arguments are uniform within the 8-lane group.
-template <int G>
+template <int G, int W>
 __device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSeg &e, i64 ws, i64 we, int gl, u32 gmask,
                                          i64 &a, i64 &b) {
-    constexpr int R = 16 / G;                     // probe loads per lane and end
+    constexpr int R = W / G;                      // probe loads per lane and end
     const i64 n = e.n;
-    const i64 wa = us_window(n, ws, e.t_lo, e.inv), wb = us_window(n, we, e.t_lo, e.inv);
+    const i64 wa = us_window<W>(n, ws, e.t_lo, e.inv), wb = us_window<W>(n, we, e.t_lo, e.inv);
     i64 va[R], vb[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) va[r] = us_ld8_if(seg + wa + r * G + gl, wa + r * G + gl < n, TH_I64_MAX);
@@ -122,8 +139,8 @@ __device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSe
     for (int r = 0; r < R; ++r) fa += __popc(__ballot_sync(gmask, wa + r * G + gl < n && va[r] < ws));
 #pragma unroll
     for (int r = 0; r < R; ++r) fb += __popc(__ballot_sync(gmask, wb + r * G + gl < n && vb[r] <= we));
-    a = us_finish<true>(seg, n, ws, wa, fa);      // first ts >= ws
-    b = us_finish<false>(seg, n, we, wb, fb);     // first ts >  we
+    a = us_finish<true, W>(seg, n, ws, wa, fa);   // first ts >= ws
+    b = us_finish<false, W>(seg, n, we, wb, fb);  // first ts >  we
     if (b < a) b = a;                             // end before start: empty window
 }
 
@@ -212,7 +229,7 @@ __device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *
 // ELEM = bytes per utilisation sample (8: int64 columns, 1: uint8 columns); VEC = the columns are 16-byte aligned;
 // TAB = `tab` holds the per-uuid entries (otherwise each window derives its entry from off / ts itself -- used when
 // there are far more uuids than windows).
-template <int ELEM, bool VEC, bool TAB, int G>
+template <int ELEM, bool VEC, bool TAB, int G, int W>
 __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
                                                               const UsSeg *__restrict__ tab, const i64 *__restrict__ ts,
                                                               const void *__restrict__ gpu_v, const void *__restrict__ mem_v,
@@ -240,7 +257,7 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
                 e = us_make_seg(off, ts, u);
             }
             if (e.n > 0) {
-                us_range<G>(ts + e.lo, e, ws, we, gl, gmask, a, b);
+                us_range<G, W>(ts + e.lo, e, ws, we, gl, gmask, a, b);
                 a += e.lo;
                 b += e.lo;
             }
@@ -271,14 +288,14 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
     }
 }
 
-template <int ELEM, bool VEC, int G>
+template <int ELEM, bool VEC, int G, int W>
 void us_launch(bool tab_mode, int grid, cudaStream_t st, i64 s, i64 n_uuids, const i64 *off, const UsSeg *tab, const i64 *ts,
                const void *g, const void *m, i64 w, const i64 *wu, const i64 *ws, const i64 *we, i64 *sg, i64 *sm, i64 *c,
                i64 *ag, i64 *am) {
     if (tab_mode)
-        k4_usage_kernel<ELEM, VEC, true, G><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
+        k4_usage_kernel<ELEM, VEC, true, G, W><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
     else
-        k4_usage_kernel<ELEM, VEC, false, G><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
+        k4_usage_kernel<ELEM, VEC, false, G, W><<<grid, US_THREADS, 0, st>>>(s, n_uuids, off, tab, ts, g, m, w, wu, ws, we, sg, sm, c, ag, am);
 }
 
 }  // namespace
@@ -332,10 +349,13 @@ static int usage_reduce_impl(int elem, int device, int64_t s, int64_t n_uuids, c
             }
 #define US_ARGS tab_mode, grid, st, s, n_uuids, (const i64 *)d_off, (const UsSeg *)d_tab, (const i64 *)d_ts, d_g, d_m, w, \
                 (const i64 *)d_wu, (const i64 *)d_ws, (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm, (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am
-            if (elem == 1 && vec) us_launch<1, true, 4>(US_ARGS);
-            else if (elem == 1) us_launch<1, false, 4>(US_ARGS);
-            else if (vec) us_launch<8, true, 8>(US_ARGS);
-            else us_launch<8, false, 8>(US_ARGS);
+            // probe width 8 (16 / 8 / 4 measured on config 3: 2.96 / 2.80 / -- ms for int64 columns, 1.69 / 1.35 / 1.23 ms
+            // for uint8; on an irregular log -- a fifth of the samples missing, 0.9 s jitter -- 3.39 / 3.41 / -- and
+            // 2.15 / 1.91 / 1.90 ms: 8 keeps a margin of +-3 samples around the guess at no cost on either kind of log)
+            if (elem == 1 && vec) us_launch<1, true, 4, 8>(US_ARGS);
+            else if (elem == 1) us_launch<1, false, 4, 8>(US_ARGS);
+            else if (vec) us_launch<8, true, 8, 8>(US_ARGS);
+            else us_launch<8, false, 8, 8>(US_ARGS);
 #undef US_ARGS
             cudaError_t e = cudaGetLastError();
             if (e != cudaSuccess) { th_set_error("th_usage_reduce: launch -> %s", cudaGetErrorString(e)); rc = TH_ECUDA; break; }

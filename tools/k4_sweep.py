@@ -29,6 +29,13 @@ native.check(lib.th_synth_windows(0, U, SPU, synth.T0_US, 20260105, W, wu.data_p
 torch.cuda.synchronize()
 
 
+if os.environ.get('TH_SWEEP_GAPPY'):      # an irregular log: a fifth of the samples missing at random, 0.9 s of jitter
+    keep = torch.rand(S, device=dev) >= 0.2
+    ts = (ts + torch.randint(0, 900_000, (S,), device=dev, dtype=torch.int64))[keep].contiguous()
+    gpu, mem = gpu[keep].contiguous(), mem[keep].contiguous()
+    off = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), keep.view(U, SPU).sum(1).cumsum(0)]).contiguous()
+    S = int(ts.numel())
+    del keep
 g8, m8 = gpu.to(torch.uint8), mem.to(torch.uint8)
 
 
