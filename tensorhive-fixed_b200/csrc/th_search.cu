@@ -187,6 +187,9 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // read by a one-level fast path that defers self-updates with an unfiltered conflict and long buckets (~7 % of
     // the lanes) to a per-CTA queue resolved densely after the CTA's tiles: 32.5 us cold / 24 us warm, and 503 vs 387 us
     // on 12.5 M x 12.5 M -- the extra loads per lane and the thin, latency-bound tail cost more than the level saved.
+    // Also measured and dropped: probes without default values (every use guarded by the probe's own predicate, saving
+    // ~36 moves per tile) and per-lane precomputed staging addresses: ptxas then needs 64 registers plus 56 bytes of
+    // spill (predicate pressure), 28.6 us cold / 19.8 us warm / 279 us at 16 M queries.
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
