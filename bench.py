@@ -56,6 +56,27 @@ def _traffic(kernel: str):
     return None
 
 
+def _bind_to_gpu_numa_node(torch, index: int):
+    """Pin this process to the CPUs next to its GPU (what NCCL launchers do): pinned host buffers are then allocated on
+    the GPU's NUMA node and the PCIe copies of the e2e path do not cross the socket interconnect.  Best effort."""
+    try:
+        p = torch.cuda.get_device_properties(index)
+        bdf = '%04x:%02x:%02x.0' % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open('/sys/bus/pci/devices/%s/local_cpulist' % bdf) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(','):
+            a, _, b = part.partition('-')
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return {'pci': bdf, 'cpus': spec}
+    except Exception as e:                                    # no sysfs entry, no permission, old torch: leave it
+        return {'unbound': str(e)[:80]}
+    return {'unbound': 'empty cpu list'}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     FIELDS = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
@@ -221,6 +242,7 @@ def run_ours(args):
         raise SystemExit('bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    affinity = _bind_to_gpu_numa_node(torch, local)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -416,7 +438,7 @@ def run_ours(args):
             'clocks': clocks.summary(),
             'e2e': {'value': e2e_value, 'unit': 'queries/s', 'h2d_bytes_per_step': 32 * N_QUERIES,
                     'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32) * (world if px is not None else 1),
-                    'ms_per_step': 1e3 * e2e_s / steps,
+                    'ms_per_step': 1e3 * e2e_s / steps, 'host_affinity': affinity,
                     'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
             'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
