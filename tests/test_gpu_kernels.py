@@ -500,6 +500,34 @@ def test_fused_exchange_two_ranks_emulated_on_one_gpu(th, synth, brute):
         s.close()
 
 
+def test_fused_exchange_with_more_tiles_per_cta_than_the_word_buffer(th, synth):
+    """40 M queries in one step: every CTA owns more bitmap words than it buffers in shared memory, so the words leave
+    as one slot store per tile.  Checked against the plain kernel on the same (device-resident) batch."""
+    import torch
+    from tensorhive_fixed_b200 import sharding
+    dev = torch.device('cuda:0')
+    cal = synth.make_calendar(200_000, 128, seed=61)
+    snap = th.Snapshot(0)
+    snap.load(*[cal[k] for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')], n_uuids=128)
+    q = synth.make_queries(cal, 1_000_000, seed=62)
+    reps = 40
+    qd = [torch.from_numpy(np.ascontiguousarray(q[k])).to(dev).repeat(reps) for k in ('uuid_id', 'start', 'end', 'self_id')]
+    m = int(qd[0].numel())
+    px = sharding.PeerExchange(0, 1, 0, max_queries_per_rank=m, connect=False)
+    px.connect_local([px.local_base()])
+    for step in range(2):
+        got = px.conflict_words(snap, *qd, wait=False)
+        px.wait()
+        torch.cuda.synchronize()
+        px.check()
+        want = snap.conflict_words(*qd)
+        assert torch.equal(got.reshape(-1)[:want.numel()].cpu(), want.cpu()), step
+    one = th.api.unpack_bits(want[:(1_000_000 + 31) // 32], 1_000_000)
+    assert one.any() and not one.all()
+    px.close()
+    snap.close()
+
+
 def test_reloading_one_handle_reuses_or_regrows_its_buffers(th, synth, brute):
     snap = th.Snapshot(0)
     for n, u, seed in [(50_000, 64, 1), (3_000, 8, 2), (0, 4, 3), (80_000, 300, 4), (80_000, 300, 5)]:
