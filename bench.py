@@ -413,6 +413,17 @@ def run_ours(args):
         out_all.copy_(g.reshape(-1), non_blocking=True)   # everybody's verdicts back on the host
         torch.cuda.synchronize()
 
+    # for context: the same 32 MB as bare pinned-host -> device copies on this box (what the e2e step cannot beat)
+    bare = [torch.empty_like(t) for t in qd]
+    copy_ms = []
+    for _ in range(5):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for d, h in zip(bare, pin):
+            d.copy_(h, non_blocking=True)
+        torch.cuda.synchronize()
+        copy_ms.append(1e3 * (time.perf_counter() - t0))
+    del bare
     for _ in range(3):
         e2e_step()
     barrier()
@@ -439,6 +450,7 @@ def run_ours(args):
             'e2e': {'value': e2e_value, 'unit': 'queries/s', 'h2d_bytes_per_step': 32 * N_QUERIES,
                     'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32) * (world if px is not None else 1),
                     'ms_per_step': 1e3 * e2e_s / steps, 'host_affinity': affinity,
+                    'bare_h2d_copy_ms': min(copy_ms), 'bare_h2d_GBs': 32 * N_QUERIES / (min(copy_ms) * 1e-3) / 1e9,
                     'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
             'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
