@@ -451,7 +451,8 @@ def run_ours(args):
                     'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32) * (world if px is not None else 1),
                     'ms_per_step': 1e3 * e2e_s / steps, 'host_affinity': affinity,
                     'bare_h2d_copy_ms': min(copy_ms), 'bare_h2d_GBs': 32 * N_QUERIES / (min(copy_ms) * 1e-3) / 1e9,
-                    'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers' if px is None else
+                    'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers: the kernel reads the 32 MB of query columns in place over '
+                            'PCIe and writes the bitmap into the pinned output, no staging copies' if px is None else
                             'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
             'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',

@@ -13,6 +13,9 @@
  *   - `mem` says where EVERY array pointer of that call lives: TH_MEM_HOST (the library stages them
  *     through stream-ordered device scratch and returns only when the outputs are readable) or
  *     TH_MEM_DEVICE (pointers on the snapshot's device; the call only enqueues work on `stream`).
+ *     th_conflict_bitmap reads page-locked (cudaHostAlloc / cudaHostRegister) TH_MEM_HOST columns in place:
+ *     the kernel streams them over PCIe itself, no staging copy (TH_NO_ZERO_COPY=1 in the environment
+ *     forces the staged path).
  *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
  *   - a loaded snapshot is immutable; any number of threads may query it concurrently.  Loading is
  *     not concurrent with queries on the same handle (swap handles instead -- see DESIGN.md).

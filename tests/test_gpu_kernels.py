@@ -426,6 +426,39 @@ def test_device_pointer_path_equals_host_path(th, synth):
 
 
 # ---- BASELINE config 2 at full size ---------------------------------------------------------------------------------------------
+def test_pinned_host_columns_are_read_in_place(th, synth, brute, monkeypatch):
+    """TH_MEM_HOST with page-locked arrays: the kernel streams the columns (and writes the bitmap) over PCIe itself.
+    Same bits as pageable arrays (staged copies), as the staged path forced by TH_NO_ZERO_COPY, and as the oracle;
+    a mix of pinned and pageable columns falls back to staging."""
+    import torch
+    cal = synth.make_calendar(50_000, 100, seed=71)
+    q = synth.make_queries(cal, 70_001, seed=72)          # ragged last tile
+    snap = _load(th, cal)
+    cols = [q[k] for k in ('uuid_id', 'start', 'end', 'self_id')]
+    want = brute.conflict_bits(cal, *cols)
+    pinned = [torch.from_numpy(c.copy()).pin_memory() for c in cols]
+    pin_np = [p.numpy() for p in pinned]
+    lib = th.native.load()
+    words = (len(want) + 31) // 32
+
+    def run(arrs, out):
+        m = len(arrs[0])
+        th.native.check(lib.th_conflict_bitmap(snap._h, m, arrs[0].ctypes.data, arrs[1].ctypes.data,
+                                               arrs[2].ctypes.data, arrs[3].ctypes.data, 0, out.ctypes.data, 0, None))
+        return th.api.unpack_bits(out, m)
+
+    out_pin = torch.zeros(words, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+    assert np.array_equal(run(pin_np, out_pin), want)                                  # all pinned, pinned output
+    assert np.array_equal(run(pin_np, np.zeros(words, np.uint32)), want)               # pinned in, pageable out
+    assert np.array_equal(run(cols, np.zeros(words, np.uint32)), want)                 # pageable: staged
+    assert np.array_equal(run([pin_np[0], cols[1], pin_np[2], cols[3]], np.zeros(words, np.uint32)), want)   # mixed
+    off1 = [p[1:] for p in pin_np]                                                     # 8-byte aligned only
+    assert np.array_equal(run(off1, out_pin), want[1:])
+    monkeypatch.setenv('TH_NO_ZERO_COPY', '1')
+    assert np.array_equal(run(pin_np, out_pin), want)
+    snap.close()
+
+
 def test_config2_full_size_bit_exact(th, synth, brute):
     """1M reservations x 4096 uuids, 1M candidates: the whole bitmap against the brute-force oracle."""
     cal = synth.make_calendar(1_000_000, 4096, seed=20260102)
