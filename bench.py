@@ -534,12 +534,29 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd=
     r_s = np.full(U, now, np.int64)
     r_e = r_s + 30 * synth.DAY_US
     snapshot = th_snapshot_wrapper(snap)
-    t0 = time.perf_counter()
-    off, ids, canc = snapshot.conflict_sets(np.arange(U, dtype=np.int64), r_s, r_e, None, 1)
-    ms_range = 1e3 * (time.perf_counter() - t0)
+    r_u = np.arange(U, dtype=np.int64)
+    snapshot.conflict_sets(r_u, r_s, r_e, None, 1)          # first host-path call grows the library's staging pool
+    reps = []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        off, ids, canc = snapshot.conflict_sets(r_u, r_s, r_e, None, 1)
+        reps.append(1e3 * (time.perf_counter() - t0))
+    ms_range = float(np.median(reps))
     torch.cuda.synchronize()
     # conflict SETS of the whole candidate batch (R1's list form: ids ascending, cancelled rows included with their flag),
     # device-resident; the call counts, scans, synchronises once for the capacity check, fills and ranks by id
+    # one candidate at a time, the way Reservation.would_interfere() is called from a controller: host arrays of length
+    # 1, wall clock per call (staging, launch, copy back, synchronisation)
+    one = [np.ascontiguousarray(cal[k][:1]) for k in ('uuid_id', 'start', 'end')] + [np.full(1, -1, np.int64)]
+    one_out = np.zeros(1, np.uint32)
+    for _ in range(20):
+        native.check(lib.th_conflict_bitmap(snap._h, 1, one[0].ctypes.data, one[1].ctypes.data, one[2].ctypes.data,
+                                            one[3].ctypes.data, 0, one_out.ctypes.data, 0, sp))
+    t0 = time.perf_counter()
+    for _ in range(200):
+        native.check(lib.th_conflict_bitmap(snap._h, 1, one[0].ctypes.data, one[1].ctypes.data, one[2].ctypes.data,
+                                            one[3].ctypes.data, 0, one_out.ctypes.data, 0, sp))
+    us_single = 1e6 * (time.perf_counter() - t0) / 200
     sets = None
     if qd is not None:
         import ctypes as C
@@ -567,6 +584,7 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd=
             'job_tasks': {'ms': ms_task, 'tasks_per_s': T / (ms_task * 1e-3), 'interfering': int(tflags.sum().item())},
             'gpu_slots': {'ms': ms_up, 'uuids_per_s': U / (ms_up * 1e-3)},
             'conflict_sets': sets,
+            'single_would_interfere_call': {'us_per_call': us_single, 'note': 'th_conflict_bitmap(m = 1, TH_MEM_HOST), wall clock'},
             'calendar_range': {'ms_host_call': ms_range, 'ranges': U, 'rows_returned': int(len(ids)),
                                'note': 'th_conflict_sets(TH_MODE_INCLUSIVE), host arrays, wall clock incl. copies'}}
 
