@@ -28,7 +28,8 @@ words = torch.empty((1_000_000 + 31) // 32, dtype=torch.int32, device=dev)
 flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
 sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 for _ in range(3):
-    flush.fill_(1)
+    if not os.environ.get('TH_PROF_NOFLUSH'):     # warm-L2 captures: pair with ncu --cache-control none
+        flush.fill_(1)
     native.check(lib.th_conflict_bitmap(snap._h, 1_000_000, qd[0].data_ptr(), qd[1].data_ptr(), qd[2].data_ptr(),
                                         qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
 torch.cuda.synchronize()
