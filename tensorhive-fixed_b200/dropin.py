@@ -82,6 +82,32 @@ class Reservation:
         self.mem_util_avg = None
 
     # -- plain attributes mirroring the hybrid properties ------------------------------------------------
+    # Reservation.py:61-79 + utils/DateUtils.py:9,47-60: a str is parsed with the API's input format (ValueError on a
+    # malformed one, as in the reference), a datetime is kept, anything else becomes None (and fails check_assertions)
+    @staticmethod
+    def _try_parse(value):
+        if isinstance(value, str):
+            return _dt.datetime.strptime(value, '%Y-%m-%dT%H:%M:%S.%fZ')
+        if isinstance(value, _dt.datetime):
+            return value
+        return None
+
+    @property
+    def start(self):
+        return self._start
+
+    @start.setter
+    def start(self, value):
+        self._start = self._try_parse(value)
+
+    @property
+    def end(self):
+        return self._end
+
+    @end.setter
+    def end(self, value):
+        self._end = self._try_parse(value)
+
     @property
     def is_cancelled(self):
         return self._is_cancelled is not None and self._is_cancelled

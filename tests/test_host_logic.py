@@ -123,3 +123,29 @@ def test_calendar_delta_bookkeeping(dropin):
     with pytest.raises(RuntimeError):
         dropin._calendar = None
         dropin.Reservation.current_events()
+
+
+def test_reservation_times_are_parsed_like_the_reference(dropin):
+    """Reservation.py:61-79 with utils/DateUtils.py:47-60: the REST layer hands over strings in the API's input format."""
+    import datetime as dt
+    from tensorhive_fixed_b200.calendar import Calendar
+    now = dt.datetime(2026, 3, 1, 12)
+    gpu = 'GPU-' + 'c' * 36
+    cal = Calendar([dropin.Reservation(id=1, user_id=1, title='T', description='D', resource_id=gpu,
+                                       start='2026-03-01T12:00:00.000Z', end='2026-03-01T13:00:00.000Z')], clock=lambda: now)
+    dropin.bind(cal)
+    r = dropin.Reservation(user_id=1, title='T', description='D', resource_id=gpu, start='2026-03-01T12:30:00.000Z',
+                           end='2026-03-01T13:30:00.500Z')
+    assert r.start == dt.datetime(2026, 3, 1, 12, 30) and r.end == dt.datetime(2026, 3, 1, 13, 30, 0, 500000)
+    assert r.duration == dt.timedelta(hours=1, microseconds=500000)
+    assert r.would_interfere() is True
+    with pytest.raises(AssertionError, match='would interfere'):
+        r.check_assertions()
+    r.start, r.end = '2026-03-01T13:00:00.000Z', '2026-03-01T14:00:00.000Z'       # touching: no conflict
+    r.check_assertions()
+    with pytest.raises(ValueError):
+        r.start = '2026-03-01 13:00:00'                      # not the API format: DateUtils.parse_string re-raises
+    r.end = 1_700_000_000                                    # neither str nor datetime -> None
+    assert r.end is None
+    with pytest.raises(AssertionError, match='end time is invalid'):
+        r.check_assertions()
