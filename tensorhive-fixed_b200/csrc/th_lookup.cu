@@ -49,6 +49,9 @@ __global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(ThGrid g, const 
                                                                 const ThP3 *__restrict__ p3, const ThP4 *__restrict__ p4,
                                                                 i64 n_uuids, i64 now, i64 *__restrict__ out_res,
                                                                 i64 *__restrict__ out_owner) {
+    // let a dependent launch (the K5 join, launched with programmatic stream serialisation) start loading its process
+    // rows while this grid builds the table; it waits for this grid's completion before it reads the table
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int lane = threadIdx.x & 31;
     const i64 wstride = (i64)gridDim.x * LK_WARPS;
     for (i64 u = (i64)blockIdx.x * LK_WARPS + (threadIdx.x >> 5); u < n_uuids; u += wstride) {
@@ -169,21 +172,36 @@ __global__ void __launch_bounds__(256) k5_violation_kernel(const i64 *__restrict
                                                            const i64 *__restrict__ proc_uuid,
                                                            const i64 *__restrict__ proc_owner, u8 *__restrict__ out_flag,
                                                            i64 *__restrict__ out_res) {
-    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < p; i += (i64)gridDim.x * blockDim.x) {
-        const i64 u = proc_uuid[i];
+    // The process rows do not depend on the table: the first four per thread are read BEFORE waiting for the grid that
+    // builds it (no-op unless this kernel was launched with programmatic stream serialisation behind that grid).
+    const i64 stride = (i64)gridDim.x * blockDim.x;
+    const i64 i0 = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    i64 pu[4], po[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const i64 i = i0 + k * stride;
+        pu[k] = -1; po[k] = -1;
+        if (i < p) { pu[k] = th_ld_stream(&proc_uuid[i]); po[k] = th_ld_stream(&proc_owner[i]); }
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    auto judge = [&](i64 i, i64 u, i64 powner) {
         i64 res = -1, owner = -1;
         if (u >= 0 && u < n_uuids) { res = cur_res[u]; owner = cur_owner[u]; }
         u8 flag = 0;
         i64 rid = -1;
         if (res >= 0) {
             // a reservation is current: `reservation.user is None` (owner < 0) silences the GPU (:94-95)
-            if (owner >= 0 && proc_owner[i] != owner) { flag = 1; rid = res; }
+            if (owner >= 0 && powner != owner) { flag = 1; rid = res; }
         } else if (strict) {
             flag = 1;   // unreserved GPU in strict mode: every process is an intruder, reservation=None (:100-102)
         }
         out_flag[i] = flag;
         out_res[i] = rid;
-    }
+    };
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (i0 + k * stride < p) judge(i0 + k * stride, pu[k], po[k]);
+    for (i64 i = i0 + 4 * stride; i < p; i += stride) judge(i, proc_uuid[i], proc_owner[i]);
 }
 
 }  // namespace
@@ -299,9 +317,20 @@ extern "C" int th_violation_join(const th_snapshot *h, int64_t now_us, int stric
     TH_TRY(sc.in(proc_owner, 8 * zp, mem, &d_o));
     TH_TRY(sc.out(out_flag_u8, zp, mem, &d_f));
     TH_TRY(sc.out(out_res_id, 8 * zp, mem, &d_r));
-    k5_violation_kernel<<<th_grid_for(p, 256 * 4, 16), 256, 0, st>>>(cur_res, cur_owner, h->n_uuids, strict ? 1 : 0, p,
-                                                                     (const i64 *)d_u, (const i64 *)d_o, (u8 *)d_f,
-                                                                     (i64 *)d_r);
+    {
+        // programmatic dependent launch: the join may start (and read its process rows) while K3 is still running
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)th_grid_for(p, 256 * 4, 16));
+        cfg.blockDim = dim3(256);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        TH_CUDA(cudaLaunchKernelEx(&cfg, k5_violation_kernel, (const i64 *)cur_res, (const i64 *)cur_owner, (i64)h->n_uuids,
+                                   strict ? 1 : 0, (i64)p, (const i64 *)d_u, (const i64 *)d_o, (u8 *)d_f, (i64 *)d_r));
+    }
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_flag_u8, d_f, zp, mem, st));
     TH_TRY(th_copy_back(out_res_id, d_r, 8 * zp, mem, st));
