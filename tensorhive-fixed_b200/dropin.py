@@ -251,6 +251,70 @@ class UsageLog:
         return out
 
 
+class UsageRing:
+    """Append-only columnar sample store, one growing segment per GPU uuid: what the usage
+    logger writes instead of re-reading and re-writing one JSON file per reservation on every tick
+    (UsageLoggingService.py:85-116).  A sample is kept under the rule of ``Log.updated_log`` (:92-99): only when BOTH
+    gpu_util and mem_util are not None.  Timestamps must not decrease per uuid (the service appends ``utcnow()``).
+    Utilisation is stored as uint8 (percentages), timestamps as int64 microseconds; ``averages`` hands the columns to
+    K4's narrow path and returns what ``handle_expired_logs`` (:196-229) stores per reservation."""
+
+    def __init__(self, device: int = 0, initial_capacity: int = 1024):
+        self.device = int(device)
+        self._cap0 = max(int(initial_capacity), 1)
+        self._codes: Dict[str, int] = {}
+        self._ts: List[np.ndarray] = []
+        self._gpu: List[np.ndarray] = []
+        self._mem: List[np.ndarray] = []
+        self._len: List[int] = []
+
+    def __len__(self):
+        return int(sum(self._len))
+
+    def append(self, resource_id: str, ts, gpu_util, mem_util) -> bool:
+        """One monitoring tick of one GPU; returns False (and stores nothing) when either metric is unsupported."""
+        if gpu_util is None or mem_util is None:
+            return False
+        k = self._codes.get(resource_id)
+        if k is None:
+            k = self._codes[resource_id] = len(self._ts)
+            self._ts.append(np.empty(self._cap0, np.int64))
+            self._gpu.append(np.empty(self._cap0, np.uint8))
+            self._mem.append(np.empty(self._cap0, np.uint8))
+            self._len.append(0)
+        n = self._len[k]
+        t = dt_to_us(ts) if isinstance(ts, _dt.datetime) else int(ts)
+        assert n == 0 or t >= self._ts[k][n - 1], 'samples of one GPU must be appended in time order'
+        assert 0 <= int(gpu_util) <= 255 and 0 <= int(mem_util) <= 255, 'utilisation is a percentage'
+        if n == len(self._ts[k]):
+            for col in (self._ts, self._gpu, self._mem):
+                grown = np.empty(2 * n, col[k].dtype)
+                grown[:n] = col[k]
+                col[k] = grown
+        self._ts[k][n], self._gpu[k][n], self._mem[k][n] = t, int(gpu_util), int(mem_util)
+        self._len[k] = n + 1
+        return True
+
+    def columns(self):
+        """(uuid_codes, offsets[U + 1], ts, gpu_u8, mem_u8): the CSR layout K4 reads."""
+        off = np.zeros(len(self._len) + 1, np.int64)
+        off[1:] = np.cumsum(self._len)
+        cat = lambda cols, dt: (np.concatenate([c[:n] for c, n in zip(cols, self._len)]) if cols else np.zeros(0, dt))
+        return dict(self._codes), off, cat(self._ts, np.int64), cat(self._gpu, np.uint8), cat(self._mem, np.uint8)
+
+    def averages(self, reservations: List[Reservation]):
+        if not reservations:
+            return []
+        codes, off, ts, gpu, mem = self.columns()
+        if len(off) == 1:
+            return [(float(-1), float(-1))] * len(reservations)
+        wu = np.array([codes.get(r.resource_id, -1) for r in reservations], np.int64)
+        ws = np.array([dt_to_us(r.start) for r in reservations], np.int64)
+        we = np.array([dt_to_us(r.end) for r in reservations], np.int64)
+        _sg, _sm, cnt, ag, am = api.usage_reduce_u8(off, ts, gpu, mem, wu, ws, we, device=self.device)
+        return [(float(-1), float(-1)) if cnt[j] == 0 else (int(ag[j]), int(am[j])) for j in range(len(reservations))]
+
+
 # =========================================================================================================
 # core/managers/InfrastructureManager.py:22-63
 # =========================================================================================================

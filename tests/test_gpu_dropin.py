@@ -252,3 +252,46 @@ def test_usage_log_averages(dropin):
         assert ag == want_g and am == want_m and type(ag) is type(want_g)
     assert got[-1] == (-1.0, -1.0)
     cal.close()
+
+
+def test_usage_ring_follows_the_logger_rules(dropin):
+    """UsageRing against a literal replay of the reference logger: per reservation a list that grows by one entry per
+    tick while the reservation is current and both metrics are reported (Log.updated_log :92-99, log_current_usage
+    :159-171), averaged with avg() (:25-30) when it expires."""
+    from oracle import services_ref as ref
+    cal, _ = _calendar(dropin, [])
+    rng = np.random.default_rng(12)
+    gpus = ['GPU-%036d' % k for k in range(3)]
+    t0 = dt.datetime(2026, 4, 1, 8, 0, 0)
+    res = []
+    for k in range(12):
+        s = t0 + timedelta(minutes=int(rng.integers(0, 600)))
+        res.append(dropin.Reservation(id=k + 1, user_id=1, title='T', description='D', resource_id=gpus[k % 3], start=s,
+                                      end=s + timedelta(minutes=int(rng.integers(30, 240)))))
+    res.append(dropin.Reservation(id=50, user_id=1, title='T', description='D', resource_id='GPU-' + 'f' * 36,
+                                  start=t0, end=t0 + timedelta(hours=1)))              # a GPU that never reports
+    ring = dropin.UsageRing(initial_capacity=4)                                        # forces the buffers to grow
+    lists = {r.id: ([], []) for r in res}
+    for tick in range(0, 900 * 60, 47):                                                # one sample every 47 s
+        now = t0 + timedelta(seconds=tick, microseconds=int(rng.integers(0, 1000)))
+        for g in gpus:
+            gu = None if rng.random() < 0.05 else int(rng.integers(0, 101))            # unsupported metric now and then
+            mu = None if rng.random() < 0.05 else int(rng.integers(0, 101))
+            kept = ring.append(g, now, gu, mu)
+            assert kept == (gu is not None and mu is not None)
+            if kept:
+                for r in res:                                                          # the reference's per-reservation log
+                    if r.resource_id == g and r.start <= now <= r.end:
+                        lists[r.id][0].append(gu)
+                        lists[r.id][1].append(mu)
+    got = ring.averages(res)
+    for r, (ag, am) in zip(res, got):
+        want = (ref.avg(lists[r.id][0]), ref.avg(lists[r.id][1]))
+        assert (ag, am) == want and type(ag) is type(want[0]), r.id
+    assert got[-1] == (-1.0, -1.0) and any(a >= 0 for a, _ in got)
+    assert len(ring) == sum(len(c) for c in ring.columns()[2:3])
+    assert dropin.UsageRing().averages(res[:2]) == [(-1.0, -1.0)] * 2
+    with pytest.raises(AssertionError):
+        ring.append(gpus[0], t0, 1, 1)                                                 # time must not run backwards
+    cal.close()
+

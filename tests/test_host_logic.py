@@ -88,6 +88,7 @@ def dropin(monkeypatch):
     from tensorhive_fixed_b200 import dropin as d
     monkeypatch.setattr(calmod, 'Snapshot', FakeSnapshot)
     monkeypatch.setattr(d.api, 'usage_reduce', _fake_usage_reduce)
+    monkeypatch.setattr(d.api, 'usage_reduce_u8', _fake_usage_reduce)
     return d
 
 
@@ -99,6 +100,7 @@ test_protection_service = G.test_protection_service_violations_match_the_referen
 test_job_scheduling = G.test_job_scheduling_checks_match_the_reference_loops
 test_bulk_revalidation = G.test_bulk_revalidation_batches_would_interfere
 test_usage_log = G.test_usage_log_averages
+test_usage_ring = G.test_usage_ring_follows_the_logger_rules
 
 
 def test_calendar_delta_bookkeeping(dropin):
