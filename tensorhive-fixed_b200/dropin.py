@@ -80,6 +80,7 @@ class Reservation:
         self._is_cancelled = is_cancelled
         self.gpu_util_avg = None
         self.mem_util_avg = None
+        self.created_at = None
 
     # -- plain attributes mirroring the hybrid properties ------------------------------------------------
     # Reservation.py:61-79 + utils/DateUtils.py:9,47-60: a str is parsed with the API's input format (ValueError on a
@@ -123,6 +124,21 @@ class Reservation:
     @property
     def user(self):
         return _cal().users.get(self.user_id)
+
+    # -- Reservation.py:17-18,165-168 + CRUDModel.py:72-94: camelCased public attributes, datetimes as strings ------
+    __public__ = ['id', 'title', 'description', 'resource_id', 'user_id', 'gpu_util_avg', 'mem_util_avg', 'start', 'end',
+                  'created_at', 'is_cancelled']
+
+    def as_dict(self, include_private=False):
+        def camel(name):
+            head, *rest = name.split('_')
+            return head + ''.join(w.capitalize() for w in rest)
+        ret = {}
+        for c in self.__public__:
+            v = getattr(self, c, None)
+            ret[camel(c)] = (v.strftime('%Y-%m-%dT%H:%M:%S') + '+00:00') if type(v) is _dt.datetime else v
+        ret['userName'] = self.user.username
+        return ret
 
     def __repr__(self):
         return '<Reservation id=%s resource=%s %s..%s cancelled=%s>' % (self.id, self.resource_id, self.start,
@@ -192,6 +208,26 @@ class Reservation:
         k = len(uu)
         _off, ids, _canc = cal.sets(uu, [dt_to_us(start)] * k, [dt_to_us(end)] * k, MODE_INCLUSIVE)
         return cal.rows_for(np.sort(np.asarray(ids)))
+
+
+# =========================================================================================================
+# controllers/reservation.py:31-55 -- the calendar view; FullCalendar.vue polls it per view
+# =========================================================================================================
+def get_selected(resources_ids=None, start=None, end=None):
+    """Same contract as the reference controller: all three arguments or 400; API-format strings; the rows of
+    ``filter_by_uuids_and_time_range`` as dicts; ValueError / AssertionError -> 400, anything else -> 500."""
+    if not (resources_ids and start and end):
+        return {'msg': 'Bad Request'}, 400
+    try:
+        start_as_datetime = _dt.datetime.strptime(start, '%Y-%m-%dT%H:%M:%S.%fZ')
+        ends_as_datetime = _dt.datetime.strptime(end, '%Y-%m-%dT%H:%M:%S.%fZ')
+        matches = [m.as_dict() for m in
+                   Reservation.filter_by_uuids_and_time_range(resources_ids, start_as_datetime, ends_as_datetime)]
+    except (ValueError, AssertionError) as reason:
+        return {'msg': '{}. {}'.format('Bad Request', reason)}, 400
+    except Exception as e:                                         # noqa: BLE001 -- the reference answers 500 here
+        return {'msg': 'Internal server error' + str(e)}, 500
+    return matches, 200
 
 
 # =========================================================================================================

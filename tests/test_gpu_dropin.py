@@ -295,3 +295,32 @@ def test_usage_ring_follows_the_logger_rules(dropin):
         ring.append(gpus[0], t0, 1, 1)                                                 # time must not run backwards
     cal.close()
 
+
+def test_calendar_view_controller(dropin):
+    """controllers/reservation.py:31-55 over the snapshot: argument rules, status codes, id order, serialisation."""
+    from oracle.sql_ref import SqlCalendar
+    g1, g2 = GPU, GPU[:-1] + '4'
+    rows = [(5, g1, NOW_US - 3_600_000_000, NOW_US + 3_600_000_000, 1, None),
+            (2, g1, NOW_US + 3_600_000_000, NOW_US + 7_200_000_000, 2, True),        # cancelled rows are returned too
+            (9, g2, NOW_US + 1_800_000_000, NOW_US + 9_000_000_000, 1, False),
+            (3, g1, NOW_US + 86_400_000_000, NOW_US + 90_000_000_000, 2, None)]      # outside the view
+    cal, _ = _calendar(dropin, rows, users={1: User(1, 'alice'), 2: User(2, 'bob')})
+    fmt = lambda us: (EPOCH + timedelta(microseconds=us)).strftime('%Y-%m-%dT%H:%M:%S.%fZ')
+    lo, hi = NOW_US, NOW_US + 3_600_000_000                                          # ends inclusive: row 2 touches hi
+    body, status = dropin.get_selected([g1, g2, g1], fmt(lo), fmt(hi))
+    assert status == 200
+    sql = SqlCalendar([(r[0], r[1], r[2], r[3], r[4], None if r[5] is None else int(r[5])) for r in rows])
+    want = sql.filter_by_uuids_and_time_range([g1, g2], EPOCH + timedelta(microseconds=lo), EPOCH + timedelta(microseconds=hi))
+    assert [d['id'] for d in body] == want == [2, 5, 9]
+    first = body[0]
+    assert set(first) == {'id', 'title', 'description', 'resourceId', 'userId', 'gpuUtilAvg', 'memUtilAvg', 'start', 'end',
+                          'createdAt', 'isCancelled', 'userName'}
+    assert first['userName'] == 'bob' and first['isCancelled'] is True and first['resourceId'] == g1
+    assert first['start'] == (EPOCH + timedelta(microseconds=rows[1][2])).strftime('%Y-%m-%dT%H:%M:%S') + '+00:00'
+    assert dropin.get_selected([g1], fmt(lo), None) == ({'msg': 'Bad Request'}, 400)     # all three or nothing
+    assert dropin.get_selected([], fmt(lo), fmt(hi))[1] == 400
+    body, status = dropin.get_selected([g1], '2026-01-01 00:00', fmt(hi))             # not the API's date format
+    assert status == 400 and body['msg'].startswith('Bad Request. ')
+    assert dropin.get_selected(['GPU-unknown'], fmt(lo), fmt(hi)) == ([], 200)
+    cal.close()
+

@@ -101,6 +101,7 @@ test_job_scheduling = G.test_job_scheduling_checks_match_the_reference_loops
 test_bulk_revalidation = G.test_bulk_revalidation_batches_would_interfere
 test_usage_log = G.test_usage_log_averages
 test_usage_ring = G.test_usage_ring_follows_the_logger_rules
+test_calendar_view = G.test_calendar_view_controller
 
 
 def test_calendar_delta_bookkeeping(dropin):
