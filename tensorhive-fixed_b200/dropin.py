@@ -236,11 +236,22 @@ def get_selected(resources_ids=None, start=None, end=None):
 def reservations_that_may_be_restored(reservations: List[Reservation], is_allowed) -> List[Reservation]:
     """For a user whose permissions widened: the cancelled, still-running reservations that
     ``is_reservation_allowed`` accepts and that would not interfere.  ``is_allowed(reservation)`` is the
-    host-side restriction walk (out of scope); all would_interfere checks go out as ONE batch."""
+    host-side restriction walk (out of scope); all would_interfere checks against the calendar go out as ONE batch.
+
+    The reference restores and saves one reservation at a time, so a reservation restored earlier in the loop is a
+    live row for the ones after it: two of the user's cancelled reservations that overlap each other on one GPU are
+    not both restored.  That part is a sequential pass over the (few) candidates on the host."""
     now = _cal().clock()
     cand = [r for r in reservations if r.end > now and r.is_cancelled and is_allowed(r)]
     flags = Reservation.would_interfere_many(cand)
-    return [r for r, f in zip(cand, flags) if not f]
+    restored: List[Reservation] = []
+    for r, f in zip(cand, flags):
+        if f:
+            continue
+        if any(o.resource_id == r.resource_id and r.start < o.end and r.end > o.start and o.id != r.id for o in restored):
+            continue                       # Reservation.py:120-130 against a row this very loop has just revived
+        restored.append(r)
+    return restored
 
 
 # =========================================================================================================

@@ -222,9 +222,12 @@ def test_bulk_revalidation_batches_would_interfere(dropin):
     mine = [mk(10, 30, 90, True),      # overlaps the live row -> stays cancelled
             mk(11, 60, 120, True),     # touches it -> may be restored
             mk(12, 200, 260, False),   # not cancelled -> not a candidate
-            mk(13, -500, -400, True)]  # already over -> skipped
-    back = dropin.reservations_that_may_be_restored(mine, is_allowed=lambda r: True)
-    assert [r.id for r in back] == [11]
+            mk(13, -500, -400, True),  # already over -> skipped
+            mk(14, 100, 160, True),    # overlaps 11, which the loop has restored by then -> stays cancelled
+            mk(15, 120, 180, True),    # touches 11, overlaps 14 (still cancelled) -> restored
+            mk(16, 300, 400, True)]    # free, but the restriction walk says no
+    back = dropin.reservations_that_may_be_restored(mine, is_allowed=lambda r: r.id != 16)
+    assert [r.id for r in back] == [11, 15]
     cal.close()
 
 
