@@ -650,7 +650,7 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     RowView v;
     v.seg = h->seg; v.p1 = h->p1; v.p3 = h->p3; v.p4 = h->p4; v.g = th_grid_of(h);
     // large batches (would_interfere for a whole candidate list): 4 lanes per query, eight queries per warp (1 M
-    // config-2 candidates, 1.25 M rows returned: 0.54 / 0.37 / 0.26 / 0.185 ms with 32 / 16 / 8 / 4 lanes -- the walk is
+    // config-2 candidates, 1.25 M rows returned: 0.54 / 0.37 / 0.26 / 0.185 / 0.163 ms with 32 / 16 / 8 / 4 / 2 lanes; 4 keeps long ranges affordable -- the walk is
     // a chain of dependent probes, so queries in flight are what counts); a few calendar ranges: one warp per query
     const bool narrow = m >= 32768;
     const int wgrid = th_grid_for(m, narrow ? CS_THREADS / 4 : CS_WARPS, 16);
