@@ -97,13 +97,38 @@ __device__ __forceinline__ bool k2_resolve(const longlong2 c, const ThP1 *__rest
         // the last row with start < qe is at worst the uuid's sentinel (m1 = INT64_MIN)
         return (ws && tt.x == self) ? (tt.y > qs) : (m1 > qs);
     } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
-        int lo = pos, hi = pos + cnt;
-        while (lo < hi) {
-            const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-            if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
+        // mall (running maximum of `end` over ALL rows, P4) is at least m1 (non-cancelled rows only), so the cell's
+        // m1_before settles "yes" early; otherwise the same speculative probes as above, on {start} and {mall}.
+        if (c.y >= qs) return true;
+        const longlong2 far = make_longlong2(TH_I64_MAX, 0);
+        const longlong2 low = make_longlong2(-1, TH_I64_MIN);          // {owner, mall}
+        const ThP1 *r1 = p1 + pos;
+        const ThP4 *r4 = p4 + pos;
+        longlong2 e[BM_PROBE], w[BM_PROBE + 1];
+        e[0] = th_ld16_if_off<0>(r1, cnt > 0, far);
+        e[1] = th_ld16_if_off<16>(r1, cnt > 1, far);
+        e[2] = th_ld16_if_off<32>(r1, cnt > 2, far);
+        e[3] = th_ld16_if_off<48>(r1, cnt > 3, far);
+        w[0] = th_ld16_if_off<-16>(r4, pos > 0, low);
+        w[1] = th_ld16_if_off<0>(r4, cnt > 0, low);
+        w[2] = th_ld16_if_off<16>(r4, cnt > 1, low);
+        w[3] = th_ld16_if_off<32>(r4, cnt > 2, low);
+        w[4] = th_ld16_if_off<48>(r4, cnt > 3, low);
+        int k = 0;
+        i64 mall = w[0].y;
+#pragma unroll
+        for (int j = 0; j < BM_PROBE; ++j)
+            if (e[j].x <= qe) { k = j + 1; mall = w[j + 1].y; }
+        if (k == BM_PROBE && cnt > BM_PROBE) {        // long bucket: finish with a binary search
+            int lo = pos + BM_PROBE, hi = pos + cnt;
+            while (lo < hi) {
+                const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+                if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
+            }
+            // lo >= 1: bucket 0 starts with the sentinel, later buckets are preceded by it
+            mall = __ldg(&p4[lo - 1].mall);
         }
-        // lo >= 1: bucket 0 starts with the sentinel, later buckets are preceded by it
-        return __ldg(&p4[lo - 1].mall) >= qs;
+        return mall >= qs;
     }
 }
 
