@@ -237,7 +237,20 @@ __device__ __forceinline__ int th_grid_prefix_end(const ThGrid &g, const ThP1 *_
     }
     const longlong2 c = th_ld16(&g.cells[u * g.nb + b]);
     int lo = (int)(c.x & 0xffffffffll);
-    int hi = lo + (int)(c.x >> 32);
+    const int cnt = (int)(c.x >> 32);
+    int hi = lo + cnt;
+    {
+        // the bucket's first four rows in one round trip (a bucket holds ~1 row on average): rows are start-sorted, so
+        // the ones on the left of `key` are a prefix; only longer buckets go on to bisect the rest
+        const longlong2 far = make_longlong2(TH_I64_MAX, 0);
+        const ThP1 *r = p1 + lo;
+        const longlong2 e0 = th_ld16_if_off<0>(r, cnt > 0, far), e1 = th_ld16_if_off<16>(r, cnt > 1, far);
+        const longlong2 e2 = th_ld16_if_off<32>(r, cnt > 2, far), e3 = th_ld16_if_off<48>(r, cnt > 3, far);
+        auto left = [&](const longlong2 &e, int j) { return cnt > j && (STRICT ? e.x < key : e.x <= key); };
+        const int k = (int)left(e0, 0) + (int)left(e1, 1) + (int)left(e2, 2) + (int)left(e3, 3);
+        if (k < 4 || cnt <= 4) return lo + k;
+        lo += 4;
+    }
     while (lo < hi) {
         const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
         const i64 s = __ldg(&p1[mid].start);
