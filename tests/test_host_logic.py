@@ -152,3 +152,46 @@ def test_reservation_times_are_parsed_like_the_reference(dropin):
     assert r.end is None
     with pytest.raises(AssertionError, match='end time is invalid'):
         r.check_assertions()
+
+
+def test_bulk_load_from_columns_equals_the_row_wise_load(dropin):
+    """Calendar.refresh_from_columns (what `SELECT id, resource_id, _start, _end, user_id, is_cancelled` yields, with
+    SQLite's text datetimes and NULLs) against the row-wise constructor; rows come back lazily, by id."""
+    import datetime as dt
+    from datetime import timedelta
+    from tensorhive_fixed_b200.calendar import Calendar
+    now = dt.datetime(2026, 3, 1, 12)
+    g1, g2 = 'GPU-' + 'a' * 36, 'GPU-' + 'b' * 36
+    rows = [(7, g2, now - timedelta(minutes=10), now + timedelta(minutes=50), 1, None),
+            (3, g1, now + timedelta(minutes=60), now + timedelta(minutes=120), 2, 1),
+            (5, g1, now - timedelta(hours=1), now + timedelta(hours=1, microseconds=250), None, 0),
+            (9, g1, now + timedelta(minutes=20), now + timedelta(minutes=80), 2, None)]
+    users = {1: object(), 2: object()}
+    mk = lambda r: dropin.Reservation(id=r[0], resource_id=r[1], start=r[2], end=r[3], user_id=r[4], is_cancelled=r[5],
+                                      title='T', description='D')
+    a = Calendar([mk(r) for r in rows], users=users, clock=lambda: now)
+    b = Calendar([], users=users, clock=lambda: now)
+    text = lambda d: d.strftime('%Y-%m-%d %H:%M:%S.%f')                 # the way SQLAlchemy stores DateTime in SQLite
+    b.refresh_from_columns([r[0] for r in rows], [r[1] for r in rows], [text(r[2]) for r in rows], [text(r[3]) for r in rows],
+                           [r[4] for r in rows], [r[5] for r in rows],
+                           row_factory=lambda **kw: dropin.Reservation(title='T', description='D', **kw))
+    sa, sb = a.state()[0].cal, b.state()[0].cal
+    name_a, name_b = a.state()[1].names, b.state()[1].names
+    key = lambda c, names: sorted(zip(c['id'], [names[k] for k in c['uuid_id']], c['start'], c['end'], c['owner'], c['cancelled']))
+    assert key(sa, name_a) == key(sb, name_b)
+    for cal in (a, b):
+        dropin.bind(cal)
+        assert [r.id for r in dropin.Reservation.current_events()] == [5, 7]
+        assert [r.id for r in dropin.Reservation.upcoming_events_for_resource(g1, timedelta(minutes=30))] == [5, 9]
+        got = dropin.Reservation.filter_by_uuids_and_time_range([g1], now, now + timedelta(hours=1))
+        assert [(r.id, r.is_cancelled, r.user_id, r.start, r.end) for r in got] == \
+            [(3, True, 2, rows[1][2], rows[1][3]), (5, False, None, rows[2][2], rows[2][3]), (9, False, 2, rows[3][2], rows[3][3])]
+    # deltas on top of a bulk load: overlay of upserts / deletes over the lazy rows
+    b.apply_delta(upserts=[mk((9, g1, now + timedelta(minutes=200), now + timedelta(minutes=260), 2, None)),
+                           mk((11, g2, now, now + timedelta(minutes=30), 1, None))], deleted_ids=[5])
+    dropin.bind(b)
+    assert [r.id for r in dropin.Reservation.current_events()] == [7, 11]
+    assert [r.id for r in dropin.Reservation.filter_by_uuids_and_time_range([g1], now, now + timedelta(hours=9))] == [3, 9]
+    with pytest.raises(KeyError):
+        b.rows_for([5])
+    assert b.rows_for([3])[0].resource_id == g1
