@@ -327,3 +327,30 @@ def test_calendar_view_controller(dropin):
     assert dropin.get_selected(['GPU-unknown'], fmt(lo), fmt(hi)) == ([], 200)
     cal.close()
 
+
+
+def test_bulk_column_load_on_the_device(dropin):
+    """Calendar.refresh_from_columns builds the same snapshot as the row-wise path (device export compared)."""
+    from tensorhive_fixed_b200 import synth
+    from tensorhive_fixed_b200.calendar import Calendar
+    cal = synth.make_calendar(3000, 9, seed=31)
+    n = len(cal['id'])
+    names = [synth.uuid_string(int(k)) for k in cal['uuid_id']]
+    raw = [None if c < 0 else int(c) for c in cal['cancelled_raw']]
+    rows = [dropin.Reservation(id=int(cal['id'][i]), resource_id=names[i], start=EPOCH + timedelta(microseconds=int(cal['start'][i])),
+                               end=EPOCH + timedelta(microseconds=int(cal['end'][i])), user_id=int(cal['owner'][i]),
+                               is_cancelled=raw[i], title='T', description='D') for i in range(n)]
+    a = Calendar(rows)
+    b = Calendar([])
+    b.refresh_from_columns(cal['id'], names, cal['start'].astype('datetime64[us]'), cal['end'], cal['owner'], raw)
+    ea, eb = a.state()[0].export(), b.state()[0].export()
+    ua, ub = a.state()[1].names, b.state()[1].names
+    assert [ua[k] for k in ea['uuid_id']] != [] and len(ea['id']) == n
+    key = lambda e, names_: sorted(zip(e['id'].tolist(), [names_[k] for k in e['uuid_id']], e['start'].tolist(),
+                                       e['end'].tolist(), e['owner'].tolist(), e['cancelled'].tolist()))
+    assert key(ea, ua) == key(eb, ub)
+    dropin.bind(b)
+    probe = rows[17]
+    got = dropin.Reservation.filter_by_uuids_and_time_range([probe.resource_id], probe.start, probe.end)
+    assert probe.id in [r.id for r in got] and all(r.resource_id == probe.resource_id for r in got)
+    a.close(); b.close()
