@@ -7,6 +7,10 @@ A "step" = one pass of the hot path over one batch: K2 (`th_conflict_bitmap`) ov
 reservations against the resident 1 M-reservation / 4096-uuid snapshot of BASELINE config 2
 (`configs[1]`), and -- when N > 1 -- the all-gather of the bitmap words, which is the path's one exchange.
 With N ranks every rank owns its own 4096-uuid shard and 1 M routed queries (weak scaling).
+Every line also carries "cfg5_share": one rank's share of BASELINE configs[4] -- ONE global calendar of N x 12.5 M
+reservations over N x 8192 uuids (100 M / 65 536 at N = 8), partitioned by `sharding.partition_uuids`, each rank holding
+only its uuid range, 12.5 M routed candidates per GPU through the fused exchange -- with an all-ranks parity check of a
+replicated, `Router`-routed batch against the brute-force oracle, and the two other gathers of SURVEY 8(e) timed.
 The same run also measures K4 (`th_usage_reduce`) on BASELINE config 3 (1 B samples -> 10 M windows,
 generated on the device) and reports it under "usage_reduce".
 
@@ -36,6 +40,8 @@ if ROOT not in sys.path:
 
 N_ROWS, N_UUIDS, N_QUERIES = 1_000_000, 4096, 1_000_000          # BASELINE config 2
 S_UUIDS, S_PER_UUID, S_WINDOWS = 65_536, 15_259, 10_000_000       # BASELINE config 3 (65536 * 15259 ~ 1.0e9)
+C5_ROWS, C5_UUIDS = 12_500_000, 8192                               # one rank's share of BASELINE config 5
+C5_SAMPLES_PER_UUID, C5_WINDOWS = 2000, 1_000_000                  # usage log behind the K4 gather of the same block
 SEED = 20260101
 
 
@@ -287,7 +293,7 @@ def run_ours(args):
             native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, qd[0].data_ptr(), qd[1].data_ptr(),
                                                 qd[2].data_ptr(), qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
             return words
-        return px.conflict_words(snap, qd[0], qd[1], qd[2], qd[3])      # [world, words] on every rank
+        return px.conflict_words(snap, qd[0], qd[1], qd[2], qd[3], check=False)      # [world, words] on every rank
 
     def timed(step_fn, n):
         """n steps, each bracketed by its own CUDA events; L2 flushed before every step, outside the events."""
@@ -398,7 +404,6 @@ def run_ours(args):
     pin_np = [p.numpy() for p in pin]
     out_pin = torch.empty((N_QUERIES + 31) // 32, dtype=torch.int32).pin_memory()
 
-    stage = [torch.empty_like(t) for t in qd] if px is not None else None
     out_all = torch.empty(world * ((N_QUERIES + 31) // 32), dtype=torch.int32).pin_memory() if px is not None else None
 
     def e2e_step():
@@ -407,10 +412,10 @@ def run_ours(args):
                                                 pin_np[2].ctypes.data, pin_np[3].ctypes.data, 0, out_pin.data_ptr(), 0,
                                                 sp))
             return
-        for d, h in zip(stage, pin):                      # pinned host -> device
-            d.copy_(h, non_blocking=True)
-        g = px.conflict_words(snap, stage[0], stage[1], stage[2], stage[3])
-        out_all.copy_(g.reshape(-1), non_blocking=True)   # everybody's verdicts back on the host
+        # the fused kernel reads the pinned columns in place over PCIe (no staging copies); everybody's verdicts
+        # come back to the host
+        g = px.conflict_words(snap, pin[0], pin[1], pin[2], pin[3], check=False)
+        out_all.copy_(g.reshape(-1), non_blocking=True)
         torch.cuda.synchronize()
 
     # for context: the same 32 MB as bare pinned-host -> device copies on this box (what the e2e step cannot beat)
@@ -436,12 +441,28 @@ def run_ours(args):
     e2e_value = world * N_QUERIES * steps / e2e_s
     # check the last e2e result against the device-resident run (same queries)
     k2_only(); torch.cuda.synchronize()
+    exchange_check = None
     if px is None:
         assert np.array_equal(out_pin.numpy(), words.cpu().numpy()), 'host-path and device-path bitmaps differ'
     else:
+        # EVERY rank's words as delivered by the fused exchange (device-resident step and e2e step) against the same
+        # words moved by NCCL: all_gather of each rank's plain-kernel bitmap
         px.check()
-        mine = out_all.numpy().reshape(world, -1)[rank]
-        assert np.array_equal(mine, words.cpu().numpy()), 'fused-exchange words differ from the plain kernel'
+        nccl_all = torch.empty(world * words.numel(), dtype=torch.int32, device=dev)
+        dist.all_gather_into_tensor(nccl_all, words)
+        fused = k2_step()
+        torch.cuda.synchronize()
+        px.check()
+        want_all = nccl_all.view(world, -1).cpu().numpy()
+        bad = int((fused.cpu().numpy()[:, :words.numel()] != want_all).sum())
+        bad += int((out_all.numpy().reshape(world, -1) != want_all).sum())
+        t_bad = torch.tensor([bad], dtype=torch.int64, device=dev)
+        dist.all_reduce(t_bad)
+        exchange_check = {'words_compared_per_rank': 2 * int(want_all.size), 'ranks': world,
+                          'mismatching_words_all_ranks': int(t_bad.item()),
+                          'what': 'fused-exchange words of ALL ranks (device step and e2e step) vs an NCCL all_gather of the '
+                                  'plain-kernel words, on every rank'}
+        assert int(t_bad.item()) == 0, 'fused-exchange words differ from the NCCL all-gather of the plain kernel'
 
     line = {'metric': 'conflict_queries_per_s', 'value': value, 'unit': 'queries/s', 'n_gpus': world, 'steps': steps,
             'warmup': warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -453,7 +474,8 @@ def run_ours(args):
                     'bare_h2d_copy_ms': min(copy_ms), 'bare_h2d_GBs': 32 * N_QUERIES / (min(copy_ms) * 1e-3) / 1e9,
                     'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers: the kernel reads the 32 MB of query columns in place over '
                             'PCIe and writes the bitmap into the pinned output, no staging copies' if px is None else
-                            'pinned H2D + th_conflict_bitmap_exchange (fused K2 + peer all-gather) + D2H of all words')},
+                            'th_conflict_bitmap_exchange on pinned buffers (fused K2 + peer all-gather; the kernel reads the query '
+                            'columns in place over PCIe) + D2H of all ranks\' words')},
             'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,
@@ -465,6 +487,15 @@ def run_ours(args):
                               'ms_apply_delta_1000_rows_host_arrays': float(np.median(dl[1:])),
                               'radix_passes': info['radix_passes'], 'device_bytes': info['device_bytes']}}
 
+    if exchange_check is not None:
+        line['exchange_check'] = exchange_check
+    # ---- BASELINE config 5: this rank's share of ONE global calendar, cross-rank parity, the other two gathers ------
+    if not args.skip_cfg5:
+        c5 = bench_cfg5(torch, lib, native, dist, dev, local, rank, world, sp, stream, flush, steps, warmup, peak, peak_src,
+                        barrier, max_over_ranks)
+        line['cfg5_share'] = c5
+        line['parity'] = c5.pop('parity')
+        line['gpu_launches'] += steps
     # ---- BASELINE config 4: ProtectionService + job-queue sweep over the same calendar ---------------------------
     if not args.skip_sweep:
         line['service_sweep'] = bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd)
@@ -486,10 +517,6 @@ def run_ours(args):
     snap.close()
     if dist is not None:
         dist.destroy_process_group()
-
-
-def th_snapshot_wrapper(snap):
-    return snap
 
 
 def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd=None):
@@ -533,7 +560,7 @@ def bench_sweep(torch, lib, native, snap, cal, dev, sp, stream, flush, peak, qd=
     # row lists through th_conflict_sets(TH_MODE_INCLUSIVE) on the host path (two passes + D2H of the CSR)
     r_s = np.full(U, now, np.int64)
     r_e = r_s + 30 * synth.DAY_US
-    snapshot = th_snapshot_wrapper(snap)
+    snapshot = snap
     r_u = np.arange(U, dtype=np.int64)
     snapshot.conflict_sets(r_u, r_s, r_e, None, 1)          # first host-path call grows the library's staging pool
     reps = []
@@ -693,6 +720,249 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
                                                'ts is probed, not streamed'}}}
 
 
+def bench_cfg5(torch, lib, native, dist, dev, local, rank, world, sp, stream, flush, steps, warmup, peak, peak_src, barrier,
+               max_over_ranks):
+    """BASELINE configs[4] at this job's size: ONE calendar of world x 12.5 M reservations over world x 8192 uuids (100 M /
+    65 536 at 8 GPUs), defined chunk by chunk so that no process ever holds all of it.  `sharding.partition_uuids` cuts it
+    by rows; each rank materialises and loads only its uuid range and the candidates `sharding.owner_rank` routes to it
+    (12.5 M per GPU).  Before timing, a REPLICATED batch over sampled chunks (one inside every rank's range, some
+    straddling a range boundary, 1 % unknown resources) goes through `sharding.Router` and the fused exchange, and every
+    rank decodes ALL ranks' words and compares them with the brute-force oracle."""
+    import ctypes as C
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import sharding, synth
+    from oracle import brute                                      # the checker; nothing timed goes through it
+    t_start = time.perf_counter()
+    U, N = C5_UUIDS * world, C5_ROWS * world
+    gcal = synth.GlobalCalendar(N, U, seed=SEED + 50)
+    bounds = sharding.partition_uuids(gcal.rows_per_uuid_estimate(), world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    cols = ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')
+    qcols = ('uuid_id', 'start', 'end', 'self_id')
+    parts, qparts = [], []
+    for c in gcal.chunks_overlapping(lo, hi):
+        cal_c = gcal.chunk(c)
+        q_c = gcal.chunk_queries(c, len(cal_c['id']), seed=SEED + 60, cal=cal_c)
+        sel = sharding.owner_rank(cal_c['uuid_id'], bounds) == rank
+        parts.append({k: cal_c[k][sel] for k in cols})
+        qsel = sharding.owner_rank(q_c['uuid_id'], bounds) == rank          # the Router's rule, chunk by chunk
+        qparts.append({k: q_c[k][qsel] for k in qcols})
+    mine = synth.concat_columns(parts, cols)
+    q = synth.concat_columns(qparts, qcols)
+    del parts, qparts
+    mine['uuid_id'] = mine['uuid_id'] - lo
+    q['uuid_id'] = q['uuid_id'] - lo
+    n_r, m_r, u_r = int(len(mine['id'])), int(len(q['uuid_id'])), max(hi - lo, 1)
+    gen_s = time.perf_counter() - t_start
+    snap = th.Snapshot(local)
+    t0 = time.perf_counter()
+    snap.load(*[mine[k] for k in cols], n_uuids=u_r)
+    load_s = time.perf_counter() - t0
+    del mine
+    tdev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    qd = [tdev(q[k]) for k in qcols]
+    words = torch.empty((m_r + 31) // 32, dtype=torch.int32, device=dev)
+    m_all = [m_r]
+    n_all = [n_r]
+    if dist is not None:
+        t = torch.tensor([m_r, n_r], dtype=torch.int64, device=dev)
+        g = torch.empty(2 * world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(g, t)
+        g = g.view(world, 2).cpu().numpy()
+        m_all, n_all = [int(x) for x in g[:, 0]], [int(x) for x in g[:, 1]]
+
+    # ---- the parity batch: replicated on every rank, routed by Router, all ranks' words decoded everywhere ---------
+    cpu_ = gcal.chunk_uuids
+    pick = set()
+    for r in range(world):
+        cs = list(gcal.chunks_overlapping(int(bounds[r]), int(bounds[r + 1])))
+        if cs:
+            pick.add(cs[len(cs) // 2])
+    for r in sorted({1, world // 2, world - 1}):
+        if 0 < r < world:
+            pick.add(int(bounds[r]) // cpu_)                 # the chunk a range boundary falls into (or starts)
+    if world == 1:
+        pick.update({0, gcal.n_chunks - 1})
+    pick = sorted(pick)
+    pcal_parts, pq_parts = [], []
+    for c in pick:
+        cal_c = gcal.chunk(c)
+        pcal_parts.append(cal_c)
+        pq_parts.append(gcal.chunk_queries(c, 8000, seed=SEED + 70, unknown_frac=0.01, cal=cal_c))
+    pcal = synth.concat_columns(pcal_parts, cols)
+    pq = synth.concat_columns(pq_parts, qcols)
+    del pcal_parts, pq_parts
+    router = sharding.Router(pq['uuid_id'], bounds)
+    idx = router.local_indices(rank)
+    pqd = [tdev(router.local_uuid(pq['uuid_id'], rank)), tdev(pq['start'][idx]), tdev(pq['end'][idx]),
+           tdev(pq['self_id'][idx])]
+    px = None
+    if world > 1:
+        px = sharding.PeerExchange(local, world, rank, max(max(m_all), int(router.counts.max())))
+        gw = px.conflict_words(snap, *pqd, counts=router.counts)          # check=True: raises if a peer was late
+        gathered = gw.cpu().numpy()
+    else:
+        gathered = snap.conflict_words(*pqd).cpu().numpy().reshape(1, -1)
+    got = router.decode(gathered)
+    t0 = time.perf_counter()
+    want = brute.conflict_bits(pcal, pq['uuid_id'], pq['start'], pq['end'], pq['self_id'])
+    oracle_s = time.perf_counter() - t0
+    mism = int((got != want).sum())
+
+    def total_over_ranks(x: int) -> int:
+        if dist is None:
+            return int(x)
+        t = torch.tensor([int(x)], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        return int(t.item())
+
+    # ---- K3 + all-gather: the per-uuid (current reservation, owner) table of the whole calendar on every rank ----------
+    now5 = synth.T0_US + 1000 * synth.DAY_US
+    dname = 'cuda:%d' % local
+    if dist is not None:
+        gather64 = lambda v: sharding.torch_all_gather_i64(v, dname)
+    else:
+        gather64 = lambda v: np.asarray(v, np.int64).reshape(1, -1)
+    owner_ms = []
+    for _ in range(4):
+        barrier()
+        t0 = time.perf_counter()
+        res_all, own_all = sharding.sharded_current_owner(bounds, rank, lambda: snap.current_owner(now5), gather64)
+        owner_ms.append(1e3 * (time.perf_counter() - t0))
+    want_res, want_own = brute.current_owner(pcal, U, now5)
+    covered = np.zeros(U, bool)
+    for c in pick:
+        covered[c * cpu_:(c + 1) * cpu_] = True
+    mism_owner = int((res_all[covered] != want_res[covered]).sum() + (own_all[covered] != want_own[covered]).sum())
+
+    # ---- K4 + all-gather: window averages of a replicated window list, samples sharded by the same bounds ---------------
+    spu = C5_SAMPLES_PER_UUID
+
+    def chunk_samples(c):
+        return synth.make_samples(cpu_, spu, seed=SEED + 80 + c)
+
+    s_parts = []
+    for c in gcal.chunks_overlapping(lo, hi):
+        sc_ = chunk_samples(c)
+        a, b = max(lo, c * cpu_) - c * cpu_, min(hi, (c + 1) * cpu_) - c * cpu_
+        s_parts.append({k: sc_[k][a * spu:b * spu] for k in ('ts', 'gpu', 'mem')})
+    smp = synth.concat_columns(s_parts, ('ts', 'gpu', 'mem'))
+    del s_parts
+    d_off = tdev(np.arange(u_r + 1, dtype=np.int64) * spu if hi > lo else np.zeros(2, np.int64))
+    d_ts, d_g, d_m = tdev(smp['ts']), tdev(smp['gpu']), tdev(smp['mem'])
+    win = synth.make_window_batch(U, spu, C5_WINDOWS, seed=SEED + 90)
+
+    def local_reduce(wu, ws, we):
+        return tuple(x.cpu().numpy() for x in th.usage_reduce(d_off, d_ts, d_g, d_m, tdev(wu), tdev(ws), tdev(we)))
+
+    win_ms = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        ag, am = sharding.sharded_window_averages(win['uuid_id'], win['start'], win['end'], bounds, rank, local_reduce,
+                                                  gather64)
+        win_ms.append(1e3 * (time.perf_counter() - t0))
+    wsel = np.nonzero(covered[win['uuid_id']])[0][:20000]
+    # oracle over the sampled chunks only: their samples laid out as a CSR over the global uuid space
+    off_g = np.zeros(U + 1, np.int64)
+    cnt_g = np.zeros(U, np.int64)
+    cnt_g[covered] = spu
+    off_g[1:] = np.cumsum(cnt_g)
+    ps = synth.concat_columns([chunk_samples(c) for c in pick], ('ts', 'gpu', 'mem'))
+    sg, sm, cn = brute.usage_reduce(off_g, ps['ts'], ps['gpu'], ps['mem'], win['uuid_id'][wsel], win['start'][wsel],
+                                    win['end'][wsel])
+    want_ag = np.array([brute.floor_avg(a, c) for a, c in zip(sg, cn)], np.int64)
+    want_am = np.array([brute.floor_avg(a, c) for a, c in zip(sm, cn)], np.int64)
+    mism_win = int((ag[wsel] != want_ag).sum() + (am[wsel] != want_am).sum())
+    del d_ts, d_g, d_m, smp, ps
+
+    # ---- timing: the fused step over this rank's 12.5 M routed candidates ------------------------------------------------
+    def step():
+        if px is None:
+            native.check(lib.th_conflict_bitmap(snap._h, m_r, qd[0].data_ptr(), qd[1].data_ptr(), qd[2].data_ptr(),
+                                                qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+        else:
+            px.conflict_words(snap, qd[0], qd[1], qd[2], qd[3], counts=m_all, check=False)
+
+    def plain():
+        native.check(lib.th_conflict_bitmap(snap._h, m_r, qd[0].data_ptr(), qd[1].data_ptr(), qd[2].data_ptr(),
+                                            qd[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+
+    def timed(fn, n, meet):
+        evs = []
+        for _ in range(n):
+            flush.sum()
+            if meet and px is not None:
+                px.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream); fn(); b.record(stream)
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) for a, b in evs]
+
+    for _ in range(max(3, min(warmup, 5))):
+        flush.sum()
+        step()
+    barrier()
+    times = timed(step, steps, True)
+    barrier()
+    if px is not None:
+        px.check()
+    total_ms = max_over_ranks(float(sum(times)))
+    k_ms = float(np.mean(timed(plain, 10, False)))
+    k_ms_max = max_over_ranks(k_ms)
+    # the words the fused step left on this rank against the plain kernel: own row here, every row via the parity batch
+    if px is not None:
+        gw = px.conflict_words(snap, qd[0], qd[1], qd[2], qd[3], counts=m_all)
+        plain(); torch.cuda.synchronize()
+        assert bool(torch.equal(gw[rank, :words.numel()], words)), 'config-5 share: fused words differ from the plain kernel'
+    value = float(sum(m_all)) * steps / (total_ms * 1e-3)
+    single = (float(sum(m_all)) / world) / (k_ms_max * 1e-3)          # one GPU on one share, no exchange
+    alg = m_r * 32 + n_r * 25 + 8 * (u_r + 1) + m_r // 8
+    achieved = alg / (k_ms * 1e-3) / 1e9
+    traffic = _traffic('k2_bitmap_kernel_cfg5_share')
+    out = {'workload': "BASELINE configs[4]: ONE calendar of %d reservations x %d GPU UUIDs sharded by uuid range over %d GPU(s); "
+                       '%d routed candidate conflict queries per step in total' % (gcal.n_rows, U, world, sum(m_all)),
+           'value': value, 'unit': 'queries/s', 'ms_per_step': total_ms / steps, 'steps': steps,
+           'speedup_vs_n1': value / single,
+           'speedup_note': 'value / (queries per GPU / plain-kernel time of one share on one GPU, slowest rank, this run); '
+                           "per_n.1.cfg5_share.value is the same quantity measured by the N = 1 run",
+           'rows_per_rank': n_all, 'queries_per_rank': m_all, 'uuid_bounds': [int(b) for b in bounds],
+           'routing': 'sharding.partition_uuids on rows per uuid; candidates routed by sharding.owner_rank chunk by chunk '
+                      '(what sharding.Router does for a whole batch)',
+           'l2': 'flushed between steps (512 MiB read sweep, outside the timed events)',
+           'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                        'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
+                        'algorithmic_bytes_per_launch': alg, 'kernel_ms': k_ms, 'kernel_ms_slowest_rank': k_ms_max,
+                        'frac_of_nominal_8TBs': achieved / 8000.0,
+                        'dram_over_algorithmic': (traffic / alg) if traffic else None},
+           'gathers': {'current_owner_table': {'ms_wall': float(np.median(owner_ms)), 'uuids': U, 'bytes_gathered': 16 * U,
+                                               'what': 'sharding.sharded_current_owner: K3 on the shard + all-gather of '
+                                                       '(cur_res_id, cur_owner) + host layout, wall clock'},
+                       'window_averages': {'ms_wall': float(np.median(win_ms)), 'windows': C5_WINDOWS,
+                                           'samples_per_gpu': int(u_r * spu), 'bytes_gathered': 16 * C5_WINDOWS,
+                                           'what': 'sharding.sharded_window_averages: Router over the replicated windows, H2D, '
+                                                   'K4 on the sample shard, floor averages, all-gather, host layout, '
+                                                   'wall clock'}},
+           'host_s': {'generate': gen_s, 'first_load_from_host_arrays': load_s, 'parity_oracle': oracle_s},
+           'snapshot_device_bytes': snap.info()['device_bytes'],
+           'parity': {'checked': True, 'ranks': world, 'queries': int(router.m),
+                      'rows_checked_against': int(len(pcal['id'])), 'chunks': [int(c) for c in pick],
+                      'conflicts_expected': int(want.sum()),
+                      'mismatches': total_over_ranks(mism),
+                      'owner_table_mismatches': total_over_ranks(mism_owner),
+                      'window_average_mismatches': total_over_ranks(mism_win), 'windows_checked': int(wsel.size),
+                      'what': 'a replicated batch routed by sharding.Router, evaluated by every rank on its shard of the '
+                              'global calendar, exchanged by the fused kernel; EVERY rank decodes ALL ranks\' words and '
+                              'compares with the brute-force oracle over the sampled chunks (mismatches are summed over '
+                              'ranks); the K3 owner table and the K4 window averages after their all-gathers likewise'}}
+    if px is not None:
+        dist.barrier()
+        px.close()
+    snap.close()
+    return out
+
+
 def main():
     global N_ROWS, N_UUIDS, N_QUERIES
     ap = argparse.ArgumentParser()
@@ -703,6 +973,7 @@ def main():
     ap.add_argument('--skip-usage', action='store_true', help='skip the config-3 usage-reduce measurement')
     ap.add_argument('--skip-sweep', action='store_true', help='skip the config-4 service sweep measurement')
     ap.add_argument('--skip-cpu', action='store_true', help='skip the single-core CPU baseline leg')
+    ap.add_argument('--skip-cfg5', action='store_true', help="skip the config-5 share (global calendar, parity, gathers)")
     ap.add_argument('--workload', default='cfg2', choices=['cfg2', 'cfg5'],
                     help="cfg2 = BASELINE configs[1] (default, the metric's configuration); cfg5 = one rank's share of "
                          'configs[4]: 12.5M reservations x 8192 uuids, 12.5M queries per GPU (100M calendar on 8 GPUs)')
@@ -710,6 +981,7 @@ def main():
     if args.workload == 'cfg5':
         N_ROWS, N_UUIDS, N_QUERIES = 12_500_000, 8192, 12_500_000
         args.skip_sweep = True
+        args.skip_cfg5 = True
     if args.impl == 'reference':
         run_reference(args)
     else:

@@ -185,8 +185,11 @@ int th_usage_reduce_u8(int device, int64_t s, int64_t n_uuids, const int64_t *uu
  * with the step's epoch, into every rank's slots over NVLink, and an unpack kernel on `stream` polls the slots and
  * writes *out_gathered, this rank's compact [world][words_per_rank] words (valid until the step after next).
  * m_per_rank (HOST array, world entries, or NULL = every rank has m queries) says how much each rank contributes.
- * Query arrays are DEVICE pointers.  th_peer_check synchronises `stream` and reports a missed arrival as
- * TH_EINTERNAL.  With wait = 0 the call only enqueues the kernel; th_peer_wait enqueues the receive half later.
+ * Query arrays are DEVICE pointers, or page-locked host memory (all four columns), which the kernel then streams
+ * over PCIe itself.  The gathered words are valid only once th_peer_check has returned TH_OK: it synchronises
+ * `stream` and reports a missed arrival (a peer more than TH_PEER_TIMEOUT_MS behind, default 2000; the words of that
+ * step then read as 0) as TH_EINTERNAL, once.  With wait = 0 the call only enqueues the kernel; th_peer_wait enqueues
+ * the receive half later.
  * th_peer_connect(local_ptrs != NULL) wires buffers of the SAME process together (several ranks emulated on one
  * GPU in tests); th_peer_local_base returns the buffer address for that purpose. */
 typedef struct th_peer th_peer;

@@ -65,10 +65,13 @@ struct __align__(16) ThP4 { i64 owner; i64 mall; }; // mall = max end over ALL r
 // (seg[u], seg[u + 1]).  nt = n + n_uuids positions in total.
 //
 // Time grid: cell (u, b) covers starts in [t0 + (b << shift), t0 + ((b + 1) << shift)) of uuid u (the sentinel
-// counts as bucket 0).  A cell is 16 bytes = ONE probe: the first position of the bucket, how many rows it
-// holds, and the running maximum m1 of everything before it -- so a lower bound that falls into an empty
-// bucket (the common case at ~1 cell per row) is answered without touching the rows at all.
-struct __align__(16) ThCell { int pos; int cnt; i64 m1_before; };
+// counts as bucket 0).  A cell is 32 bytes = ONE probe (a single 256-bit load, LDG.E.256 -- new with sm_100): the
+// first position of the bucket, how many rows it holds, the running maximum m1 of everything before it, and the
+// bucket's FIRST row {start, m1}.  At ~1.5 cells per row half of the buckets are empty and a third hold one row, so
+// most lower bounds are settled by the cell's own 32-byte sector without touching the row arrays at all (at
+// config-5 size every scattered probe costs a 64-byte HBM atom: one atom per query instead of two or three).
+struct __align__(32) ThCell { int pos; int cnt; i64 m1_before; i64 start0; i64 m1_0; };
+struct ThCellV { i64 pc, m1_before, start0, m1_0; };   // as loaded: pc = pos | cnt << 32
 struct ThGrid {
     const ThCell *cells;   // [n_uuids * nb]
     i64 t0;
@@ -117,6 +120,8 @@ struct ThPeerOut {
     u32 *my_out;
     int *err;
     i64 expect[TH_MAX_PEERS];    // bitmap words each rank contributes this step
+    i64 recv_words;              // max over expect[]: the word range the CTAs split between them for the receive half
+    u64 timeout_ns;              // how long a receiver waits for a peer's word before it reports TH_EINTERNAL
 };
 struct ThPeerCounts { i64 words[TH_MAX_PEERS]; };   // bitmap words each rank contributes this step
 struct th_peer {
@@ -165,6 +170,14 @@ __device__ __forceinline__ longlong2 th_ld16_if(const void *p, bool pred, longlo
     return v;
 }
 
+__device__ __forceinline__ u64 th_globaltimer_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// bound of the exchange's receive half (TH_PEER_TIMEOUT_MS in the environment, default 2000)
+u64 th_peer_timeout_ns();
+
 __device__ __forceinline__ u32 th_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
 // same, at a compile-time byte offset from `base`: neighbouring probes share ONE 64-bit address computation
@@ -182,6 +195,27 @@ __device__ __forceinline__ longlong2 th_ld16_if_off(const void *base, bool pred,
     return v;
 }
 
+// 32-byte read-only load (sm_100: LDG.E.256); `p` must be 32-byte aligned.  Executes only when `pred` holds.
+__device__ __forceinline__ ThCellV th_ld32_if(const void *p, bool pred, ThCellV dflt) {
+    ThCellV v = dflt;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.s32 p, %4, 0;\n"
+        "@p ld.global.nc.v4.b64 {%0, %1, %2, %3}, [%5];\n"
+        "}\n"
+        : "+l"(v.pc), "+l"(v.m1_before), "+l"(v.start0), "+l"(v.m1_0)
+        : "r"((int)pred), "l"(p));
+    return v;
+}
+__device__ __forceinline__ ThCellV th_ld32(const void *p) {
+    ThCellV v;
+    asm volatile("ld.global.nc.v4.b64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(v.pc), "=l"(v.m1_before), "=l"(v.start0), "=l"(v.m1_0)
+                 : "l"(p));
+    return v;
+}
+
 // ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass registers, grouped for multi-stage rings -----
 __device__ __forceinline__ void th_cp_async16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(th_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
@@ -190,37 +224,6 @@ __device__ __forceinline__ void th_cp_async_commit() { asm volatile("cp.async.co
 template <int N>
 __device__ __forceinline__ void th_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS UBLKCP) ---------------------
-__device__ __forceinline__ void th_mbar_init(unsigned long long *bar, u32 count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(th_smem_addr(bar)), "r"(count));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void th_mbar_expect_tx(unsigned long long *bar, u32 bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(th_smem_addr(bar)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void th_bulk_g2s(void *smem_dst, const void *gmem_src, u32 bytes, unsigned long long *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     th_smem_addr(smem_dst)),
-                 "l"(gmem_src), "r"(bytes), "r"(th_smem_addr(bar))
-                 : "memory");
-}
-// orders this thread's earlier generic-proxy accesses to shared memory (e.g. reads of a ring stage, made
-// visible to it by __syncwarp / __syncthreads) before later async-proxy (TMA) writes to the same bytes
-__device__ __forceinline__ void th_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void th_mbar_wait(unsigned long long *bar, u32 phase) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "TH_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra TH_DONE_%=;\n"
-        "bra TH_WAIT_%=;\n"
-        "TH_DONE_%=:\n"
-        "}\n" ::"r"(th_smem_addr(bar)),
-        "r"(phase)
-        : "memory");
-}
 __device__ __forceinline__ i64 th_idc_id(i64 idc) { return idc & TH_I64_MAX; }
 __device__ __forceinline__ bool th_idc_cancelled(i64 idc) { return idc < 0; }
 
@@ -235,19 +238,22 @@ __device__ __forceinline__ int th_grid_prefix_end(const ThGrid &g, const ThP1 *_
         const u64 d = ((u64)key - (u64)g.t0) >> g.shift;
         b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
     }
-    const longlong2 c = th_ld16(&g.cells[u * g.nb + b]);
-    int lo = (int)(c.x & 0xffffffffll);
-    const int cnt = (int)(c.x >> 32);
+    const ThCellV c = th_ld32(&g.cells[u * g.nb + b]);
+    int lo = (int)(c.pc & 0xffffffffll);
+    const int cnt = (int)(c.pc >> 32);
     int hi = lo + cnt;
     {
-        // the bucket's first four rows in one round trip (a bucket holds ~1 row on average): rows are start-sorted, so
-        // the ones on the left of `key` are a prefix; only longer buckets go on to bisect the rest
+        // the bucket's first row comes with the cell; rows 1..3 in one more round trip only when the bucket has them
+        // and row 0 lies on the left of `key` (rows are start-sorted, so the ones on the left are a prefix); only
+        // longer buckets go on to bisect the rest
+        const bool in0 = cnt > 0 && (STRICT ? c.start0 < key : c.start0 <= key);
+        if (!in0 || cnt == 1) return lo + (in0 ? 1 : 0);
         const longlong2 far = make_longlong2(TH_I64_MAX, 0);
         const ThP1 *r = p1 + lo;
-        const longlong2 e0 = th_ld16_if_off<0>(r, cnt > 0, far), e1 = th_ld16_if_off<16>(r, cnt > 1, far);
+        const longlong2 e1 = th_ld16_if_off<16>(r, cnt > 1, far);
         const longlong2 e2 = th_ld16_if_off<32>(r, cnt > 2, far), e3 = th_ld16_if_off<48>(r, cnt > 3, far);
         auto left = [&](const longlong2 &e, int j) { return cnt > j && (STRICT ? e.x < key : e.x <= key); };
-        const int k = (int)left(e0, 0) + (int)left(e1, 1) + (int)left(e2, 2) + (int)left(e3, 3);
+        const int k = 1 + (int)left(e1, 1) + (int)left(e2, 2) + (int)left(e3, 3);
         if (k < 4 || cnt <= 4) return lo + k;
         lo += 4;
     }

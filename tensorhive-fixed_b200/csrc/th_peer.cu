@@ -11,6 +11,20 @@
 // overwrites slots of step k that somebody still polls.
 #include "th_common.cuh"
 #include <string.h>
+#include <stdlib.h>
+
+// How long a receiver polls for a peer's words before the step is reported as failed.  Rank skew is normal (a GC pause,
+// a first-call module load, host staging on one rank), so the default is generous; a dead peer still ends the kernel.
+u64 th_peer_timeout_ns() {
+    static const u64 v = [] {
+        const char *e = getenv("TH_PEER_TIMEOUT_MS");
+        long long ms = e ? atoll(e) : 2000;
+        if (ms < 1) ms = 1;
+        if (ms > 600000) ms = 600000;
+        return (u64)ms * 1000000ull;
+    }();
+    return v;
+}
 
 extern "C" int th_peer_create(int device, int world, int rank, int64_t words_per_rank, th_peer **out,
                               void *handle_out_64) {

@@ -8,7 +8,7 @@
 //
 // Bitmap kernel: the rows of a uuid with start < qe are a prefix of its segment, so the verdict is "does the
 // running maximum m1 of non-cancelled `end` over that prefix exceed qs".  The prefix end is found through the
-// snapshot's time grid (th_common.cuh): one 16-byte cell, then at most a handful of 16-byte {start, m1} rows.
+// snapshot's time grid (th_common.cuh): one 32-byte cell, then -- rarely -- a handful of 16-byte {start, m1} rows.
 // One lane per query, one ballot per warp = one 32-bit bitmap word per warp, stored coalesced.
 //
 // Set kernels: one warp per query.  The warp walks the candidate prefix backwards 32 rows at a time with
@@ -34,10 +34,11 @@ constexpr int BM_MAXW = 2048;   // bitmap words a CTA buffers for the fused exch
 //            cp.async copies (two per lane) into a per-warp 4-stage ring; warps never synchronise with each
 //            other.  (TMA bulk copies, one mbarrier per stage, were measured too: same latency hiding but ~80
 //            more warp instructions per tile for issue + barrier handling, and the kernel is issue bound);
-//   level 2  ONE 16-byte grid cell {pos, cnt, m1_before}.  m1 only grows along a segment, so if the rows
-//            before the bucket already end after qs the verdict is "conflict" and level 3 is skipped;
-//   level 3  the first four 16-byte {start, m1} rows of the bucket (a bucket holds ~1 row on average) and,
-//            for self-updates only, the {a1, m2} entries of the five rows the answer can land on.
+//   level 2  ONE 32-byte grid cell {pos, cnt, m1_before, start0, m1_0}, a single 256-bit load (LDG.E.256).  m1 only
+//            grows along a segment, so if the rows before the bucket already end after qs the verdict is "conflict";
+//            buckets with at most one row (5 of 6 at ~1.5 cells per row) are settled by the cell as well;
+//   level 3  rows 1..3 of the bucket as 16-byte {start, m1} probes, and, for self-updates whose prefix maximum
+//            exceeds qs, the {a1, m2} entries of the rows the answer can land on.
 // Buckets with more than four rows fall back to a binary search over the rest (about 1 % of the lanes).
 constexpr int BM_WARPS = BM_THREADS / 32;
 constexpr int BM_STAGES = 4;
@@ -54,36 +55,43 @@ __device__ __forceinline__ const ThCell *k2_cell_of(const ThGrid &g, i64 n_uuids
     return g.cells + (u * g.nb + b);
 }
 
-// level 3: verdict from the cell and (if needed) the bucket's rows
+// level 3: verdict from the cell and (if needed) the bucket's rows.  The cell carries the bucket's first row, so the
+// row arrays are touched only when (a) the bucket holds two or more rows, its first row starts before qe and the running
+// maximum up to that row does not settle the answer, or (b) the candidate is a self-update whose prefix maximum exceeds
+// qs, so that the {a1, m2} entry of the landing row has to say whether that maximum is the candidate's own row.
 template <int MODE>
-__device__ __forceinline__ bool k2_resolve(const longlong2 c, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2,
+__device__ __forceinline__ bool k2_resolve(const ThCellV c, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2,
                                            const ThP4 *__restrict__ p4, i64 qs, i64 qe, i64 self) {
-    const int pos = (int)(c.x & 0xffffffffll);
-    const int cnt = (int)(c.x >> 32);
+    const int pos = (int)(c.pc & 0xffffffffll);
+    const int cnt = (int)(c.pc >> 32);
+    static_assert(BM_PROBE == 4, "the probe offsets below are written out for four rows");
     if (MODE == TH_MODE_STRICT) {
         const bool ws = self >= 0;
-        if (!ws && c.y > qs) return true;             // decided by the rows before the bucket
+        if (!ws && c.m1_before > qs) return true;     // decided by the rows before the bucket
+        const bool in0 = cnt > 0 && c.start0 < qe;    // rows are start-sorted: the ones before qe are a prefix
+        const bool more = in0 && cnt > 1;             // rows 1.. of the bucket may lie before qe as well
+        const i64 m1c = in0 ? c.m1_0 : c.m1_before;   // running maximum as far as the cell knows it
+        // m1 only grows along a segment: once it exceeds qs a candidate without self-exclusion is settled
+        const bool rows = more && (ws || m1c <= qs);
+        const bool two = ws && (more || m1c > qs);    // {a1, m2} wanted (m1 <= qs is "no conflict" for self-updates too)
         const longlong2 far = make_longlong2(TH_I64_MAX, 0);          // {start, m1}: never before qe
         const longlong2 none = make_longlong2(-1, TH_I64_MIN);       // {a1, m2}
         longlong2 e[BM_PROBE], t[BM_PROBE + 1];
-        static_assert(BM_PROBE == 4, "the probe offsets below are written out for four rows");
         const ThP1 *r1 = p1 + pos;             // one address per array; the probes use immediate offsets from it
         const ThP2 *r2 = p2 + pos;
-        e[0] = th_ld16_if_off<0>(r1, cnt > 0, far);
-        e[1] = th_ld16_if_off<16>(r1, cnt > 1, far);
-        e[2] = th_ld16_if_off<32>(r1, cnt > 2, far);
-        e[3] = th_ld16_if_off<48>(r1, cnt > 3, far);
-        t[0] = th_ld16_if_off<-16>(r2, ws && pos > 0, none);
-        t[1] = th_ld16_if_off<0>(r2, ws && cnt > 0, none);
-        t[2] = th_ld16_if_off<16>(r2, ws && cnt > 1, none);
-        t[3] = th_ld16_if_off<32>(r2, ws && cnt > 2, none);
-        t[4] = th_ld16_if_off<48>(r2, ws && cnt > 3, none);
-        // rows are start-sorted, so the ones before qe are a prefix of the bucket
-        int k = 0;
-        i64 m1 = c.y;
-        longlong2 tt = t[0];
+        e[1] = th_ld16_if_off<16>(r1, rows, far);
+        e[2] = th_ld16_if_off<32>(r1, rows && cnt > 2, far);
+        e[3] = th_ld16_if_off<48>(r1, rows && cnt > 3, far);
+        t[0] = th_ld16_if_off<-16>(r2, two && !in0 && pos > 0, none);
+        t[1] = th_ld16_if_off<0>(r2, two && in0, none);
+        t[2] = th_ld16_if_off<16>(r2, two && more, none);
+        t[3] = th_ld16_if_off<32>(r2, two && more && cnt > 2, none);
+        t[4] = th_ld16_if_off<48>(r2, two && more && cnt > 3, none);
+        int k = in0 ? 1 : 0;
+        i64 m1 = m1c;
+        longlong2 tt = in0 ? t[1] : t[0];
 #pragma unroll
-        for (int j = 0; j < BM_PROBE; ++j)
+        for (int j = 1; j < BM_PROBE; ++j)
             if (e[j].x < qe) { k = j + 1; m1 = e[j].y; tt = t[j + 1]; }
         if (k == BM_PROBE && cnt > BM_PROBE) {        // long bucket: finish with a binary search
             int lo = pos + BM_PROBE, hi = pos + cnt;
@@ -98,26 +106,27 @@ __device__ __forceinline__ bool k2_resolve(const longlong2 c, const ThP1 *__rest
         return (ws && tt.x == self) ? (tt.y > qs) : (m1 > qs);
     } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
         // mall (running maximum of `end` over ALL rows, P4) is at least m1 (non-cancelled rows only), so the cell's
-        // m1_before settles "yes" early; otherwise the same speculative probes as above, on {start} and {mall}.
-        if (c.y >= qs) return true;
+        // m1_before settles "yes" early; otherwise speculative probes on {start} (row 0 from the cell) and {mall}.
+        if (c.m1_before >= qs) return true;
+        const bool in0 = cnt > 0 && c.start0 <= qe;
+        const bool more = in0 && cnt > 1;
         const longlong2 far = make_longlong2(TH_I64_MAX, 0);
         const longlong2 low = make_longlong2(-1, TH_I64_MIN);          // {owner, mall}
         const ThP1 *r1 = p1 + pos;
         const ThP4 *r4 = p4 + pos;
         longlong2 e[BM_PROBE], w[BM_PROBE + 1];
-        e[0] = th_ld16_if_off<0>(r1, cnt > 0, far);
-        e[1] = th_ld16_if_off<16>(r1, cnt > 1, far);
-        e[2] = th_ld16_if_off<32>(r1, cnt > 2, far);
-        e[3] = th_ld16_if_off<48>(r1, cnt > 3, far);
-        w[0] = th_ld16_if_off<-16>(r4, pos > 0, low);
-        w[1] = th_ld16_if_off<0>(r4, cnt > 0, low);
-        w[2] = th_ld16_if_off<16>(r4, cnt > 1, low);
-        w[3] = th_ld16_if_off<32>(r4, cnt > 2, low);
-        w[4] = th_ld16_if_off<48>(r4, cnt > 3, low);
-        int k = 0;
-        i64 mall = w[0].y;
+        e[1] = th_ld16_if_off<16>(r1, more, far);
+        e[2] = th_ld16_if_off<32>(r1, more && cnt > 2, far);
+        e[3] = th_ld16_if_off<48>(r1, more && cnt > 3, far);
+        w[0] = th_ld16_if_off<-16>(r4, !in0 && pos > 0, low);
+        w[1] = th_ld16_if_off<0>(r4, in0, low);
+        w[2] = th_ld16_if_off<16>(r4, more, low);
+        w[3] = th_ld16_if_off<32>(r4, more && cnt > 2, low);
+        w[4] = th_ld16_if_off<48>(r4, more && cnt > 3, low);
+        int k = in0 ? 1 : 0;
+        i64 mall = in0 ? w[1].y : w[0].y;
 #pragma unroll
-        for (int j = 0; j < BM_PROBE; ++j)
+        for (int j = 1; j < BM_PROBE; ++j)
             if (e[j].x <= qe) { k = j + 1; mall = w[j + 1].y; }
         if (k == BM_PROBE && cnt > BM_PROBE) {        // long bucket: finish with a binary search
             int lo = pos + BM_PROBE, hi = pos + cnt;
@@ -168,7 +177,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         }
         th_cp_async_commit();
     };
-    auto fetch = [&](i64 tile, u32 it, i64 &u, i64 &qs, i64 &qe, i64 &self, longlong2 &cell) {
+    auto fetch = [&](i64 tile, u32 it, i64 &u, i64 &qs, i64 &qe, i64 &self, ThCellV &cell) {
         const int st = it % BM_STAGES;
         if (tile < full_tiles) {
             th_cp_async_wait<BM_STAGES - 1>();
@@ -187,7 +196,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
         }
         stage_in(tile_of(it + BM_STAGES), st);
-        cell = th_ld16_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, make_longlong2(0, 0));   // no uuids: no grid
+        cell = th_ld32_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, ThCellV{0, 0, 0, 0});   // no uuids: no grid
     };
 
 #pragma unroll
@@ -218,7 +227,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     u32 it = 0;
     for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
         i64 u, qs, qe, self;
-        longlong2 cell;
+        ThCellV cell;
         fetch(tile, it, u, qs, qe, self, cell);
         const i64 i = tile * 32 + lane;
         // (qe = INT64_MIN cannot lie after any start, not even the sentinel's: no row, no conflict)
@@ -247,18 +256,27 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         }
     }
     if (po.n > 0 && po.unpack) {
-        // Receive half, fused: a CTA that has sent its own words turns to a share of the incoming slots, waits for
-        // each to show this step's epoch and writes the compact word.  Early finishers start polling while the
-        // stragglers (here and on the other GPUs) still compute, and no second launch sits on the critical path.
-        const i64 total = (i64)po.n * po.wpr;
-        for (i64 idx = (i64)blockIdx.x * BM_THREADS + threadIdx.x; idx < total; idx += (i64)gridDim.x * BM_THREADS) {
-            const int r = (int)(idx / po.wpr);
-            const i64 j = idx - (i64)r * po.wpr;
+        // Receive half, fused: a CTA that has sent its own words turns to the SAME word range of every rank.  The ranks
+        // run the same grid over the same tile ranges, so the peer CTA that owns this range finished at about the same
+        // time: the wait is one NVLink flight, not the slowest CTA of the slowest rank (polling the whole slot array from
+        // every CTA cost 6-10 us per step: the early finishers' polls competed with the CTAs still answering queries).
+        const i64 per_r = (po.recv_words + gridDim.x - 1) / gridDim.x;
+        const i64 r_begin = (i64)blockIdx.x * per_r;
+        const i64 r_cnt = r_begin < po.recv_words ? (r_begin + per_r < po.recv_words ? per_r : po.recv_words - r_begin) : 0;
+        for (i64 k = threadIdx.x; k < (i64)po.n * r_cnt; k += BM_THREADS) {
+            const int r = (int)(k / r_cnt);
+            const i64 j = r_begin + (k - (i64)r * r_cnt);
+            const i64 idx = (i64)r * po.wpr + j;
             u32 w = 0;
             if (j < po.expect[r]) {
                 u64 v = po.my_slots[idx];
-                for (u64 spins = 0; (u32)(v >> 32) != po.epoch; ++spins) {
-                    if (spins > (1ull << 22)) { *po.err = 1; break; }
+                u64 t0 = 0;
+                for (u32 spins = 0; (u32)(v >> 32) != po.epoch; ++spins) {
+                    if ((spins & 63u) == 63u) {                    // bounded by wall time, checked every 64 polls
+                        const u64 now = th_globaltimer_ns();
+                        if (t0 == 0) t0 = now;
+                        else if (now - t0 > po.timeout_ns) { *po.err = 1; v = 0; break; }   // late peer: word reads 0
+                    }
                     __nanosleep(64);
                     v = po.my_slots[idx];
                 }
@@ -266,13 +284,20 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             }
             po.my_out[idx] = w;
         }
+        // slots beyond what any rank contributes this step read as 0
+        const i64 tail = po.wpr - po.recv_words;
+        for (i64 k = (i64)blockIdx.x * BM_THREADS + threadIdx.x; k < (i64)po.n * tail; k += (i64)gridDim.x * BM_THREADS) {
+            const int r = (int)(k / tail);
+            po.my_out[(i64)r * po.wpr + po.recv_words + (k - (i64)r * tail)] = 0;
+        }
     }
 }
 
 // receivers: poll every expected slot until it carries this step's epoch, and write the compact words the caller
 // reads (bounded spin; sets *err on timeout).  Slots a rank does not use this step read as 0.
 __global__ void __launch_bounds__(256) k2_ll_unpack_kernel(const volatile u64 *__restrict__ slots, u32 *__restrict__ out,
-                                                           int world, i64 wpr, ThPeerCounts counts, u32 epoch, int *err) {
+                                                           int world, i64 wpr, ThPeerCounts counts, u32 epoch,
+                                                           u64 timeout_ns, int *err) {
     const i64 total = (i64)world * wpr;
     for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (i64)gridDim.x * blockDim.x) {
         const int r = (int)(idx / wpr);
@@ -280,8 +305,13 @@ __global__ void __launch_bounds__(256) k2_ll_unpack_kernel(const volatile u64 *_
         u32 w = 0;
         if (j < counts.words[r]) {
             u64 v = slots[idx];
-            for (u64 spins = 0; (u32)(v >> 32) != epoch; ++spins) {
-                if (spins > (1ull << 22)) { *err = 1; break; }
+            u64 t0 = 0;
+            for (u32 spins = 0; (u32)(v >> 32) != epoch; ++spins) {
+                if ((spins & 63u) == 63u) {
+                    const u64 now = th_globaltimer_ns();
+                    if (t0 == 0) t0 = now;
+                    else if (now - t0 > timeout_ns) { *err = 1; v = 0; break; }
+                }
                 __nanosleep(64);
                 v = slots[idx];
             }
@@ -572,6 +602,25 @@ int th_exclusive_scan_i32(const int *d_cnt, i64 m, i64 *d_offsets, i64 *d_totals
     return TH_OK;
 }
 
+// Page-locked (cudaHostAlloc / cudaHostRegister), device-mapped host columns can be read by the kernel in place.
+// Returns 1 and the device-side aliases when EVERY non-NULL pointer is such memory, 0 when none is, -1 on a mix.
+static int k2_map_pinned(const void *const *cols, int n, const void **mapped) {
+    int host = 0, other = 0;
+    for (int c = 0; c < n; ++c) {
+        mapped[c] = cols[c];
+        if (cols[c] == nullptr) continue;
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, cols[c]) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer != nullptr) {
+            mapped[c] = a.devicePointer;
+            ++host;
+        } else {
+            cudaGetLastError();
+            ++other;
+        }
+    }
+    return host == 0 ? 0 : (other == 0 ? 1 : -1);
+}
+
 extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t *q_uuid, const int64_t *q_start,
                                   const int64_t *q_end, const int64_t *q_self_id, int mode, uint32_t *out_bits_u32,
                                   int mem, void *stream) {
@@ -595,18 +644,8 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     bool zero_copy = false;
     if (mem == TH_MEM_HOST && !getenv("TH_NO_ZERO_COPY")) {
         const void *cols[4] = {q_uuid, q_start, q_end, q_self_id};
-        const void *mapped[4] = {nullptr, nullptr, nullptr, nullptr};
-        zero_copy = true;
-        for (int c = 0; c < 4 && zero_copy; ++c) {
-            if (cols[c] == nullptr) continue;
-            cudaPointerAttributes a;
-            if (cudaPointerGetAttributes(&a, cols[c]) != cudaSuccess || a.type != cudaMemoryTypeHost || a.devicePointer == nullptr) {
-                cudaGetLastError();
-                zero_copy = false;
-            } else {
-                mapped[c] = a.devicePointer;
-            }
-        }
+        const void *mapped[4];
+        zero_copy = k2_map_pinned(cols, 4, mapped) == 1;
         if (zero_copy) { d_u = mapped[0]; d_s = mapped[1]; d_e = mapped[2]; d_f = mapped[3]; }
     }
     if (!zero_copy) {
@@ -764,7 +803,7 @@ static int k2_launch_unpack(th_peer *peer, cudaStream_t st) {
     (void)used;
     k2_ll_unpack_kernel<<<blocks, 256, 0, st>>>(th_peer_slots(peer->base, peer->world, peer->words_per_rank, parity),
                                                 th_peer_out(peer, parity), peer->world, peer->words_per_rank,
-                                                peer->counts, peer->epoch,
+                                                peer->counts, peer->epoch, th_peer_timeout_ns(),
                                                 (int *)th_peer_misc(peer->base, peer->world, peer->words_per_rank));
     TH_CUDA(cudaGetLastError());
     return TH_OK;
@@ -795,16 +834,21 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_conflict_bitmap_exchange: cannot select device %d", h->device); return TH_ECUDA; }
     cudaStream_t st = (cudaStream_t)stream;
-    const u32 epoch = ++peer->epoch == 0 ? ++peer->epoch : peer->epoch;      // 0 means "empty slot"
+    // 0 means "empty slot"; on wrap-around skip to 2 so that consecutive steps keep alternating slot generations
+    if (++peer->epoch == 0) peer->epoch = 2;
+    const u32 epoch = peer->epoch;
     const int parity = (int)(epoch & 1u);
     ThPeerOut po;
     po.n = world; po.rank = peer->rank; po.epoch = epoch;
     po.word_off = (i64)peer->rank * wpr;
+    po.recv_words = 0;
     for (int p = 0; p < world; ++p) {
         po.dst[p] = th_peer_slots(peer->peer_base[p], world, wpr, parity);
         po.flags[p] = nullptr;
         po.expect[p] = peer->counts.words[p];
+        if (po.expect[p] > po.recv_words) po.recv_words = po.expect[p];
     }
+    po.timeout_ns = th_peer_timeout_ns();
     // wait = 1: the receive half runs inside the K2 kernel (needs every rank's kernel to be running at the same time,
     // i.e. one rank per GPU); wait = 0: only the send half is enqueued and th_peer_wait adds the unpack kernel later
     // (ranks emulated on one GPU, where a kernel must never wait for one that is queued behind it).
@@ -813,7 +857,12 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
     po.my_slots = th_peer_slots(peer->base, world, wpr, parity);
     po.my_out = th_peer_out(peer, parity);
     po.err = (int *)th_peer_misc(peer->base, world, wpr);
-    if (m > 0) TH_TRY(k2_launch(h, m, q_uuid, q_start, q_end, q_self_id, mode, nullptr, po, st));
+    // query columns: device memory, or page-locked host memory that the kernel streams over PCIe itself
+    const void *cols[4] = {q_uuid, q_start, q_end, q_self_id};
+    const void *mapped[4];
+    const int pinned = m > 0 ? k2_map_pinned(cols, 4, mapped) : 0;
+    TH_REQUIRE(pinned >= 0, "th_conflict_bitmap_exchange: query columns mix page-locked host memory with other memory");
+    if (m > 0) TH_TRY(k2_launch(h, m, mapped[0], mapped[1], mapped[2], mapped[3], mode, nullptr, po, st, pinned == 1 ? 1 : 0));
     if (wait && m == 0) TH_TRY(k2_launch_unpack(peer, st));
     if (out_gathered) *out_gathered = th_peer_out(peer, parity);
     return TH_OK;
@@ -868,9 +917,14 @@ extern "C" int th_peer_wait(th_peer *peer, void *stream) {
 extern "C" int th_peer_check(th_peer *peer, void *stream) {
     TH_REQUIRE(peer != nullptr && peer->base, "th_peer_check: peer group not created");
     int e = 0;
-    TH_CUDA(cudaMemcpyAsync(&e, th_peer_misc(peer->base, peer->world, peer->words_per_rank), sizeof(int),
-                            cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    int *flag = (int *)th_peer_misc(peer->base, peer->world, peer->words_per_rank);
+    TH_CUDA(cudaMemcpyAsync(&e, flag, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     TH_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-    if (e) { th_set_error("th_peer_check: a rank's words did not arrive within the unpack kernel's bound"); return TH_EINTERNAL; }
+    if (e) {
+        TH_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), (cudaStream_t)stream));      // reported once
+        th_set_error("th_peer_check: a rank's words did not arrive within TH_PEER_TIMEOUT_MS; the words of that step "
+                     "read as 0 and must not be used");
+        return TH_EINTERNAL;
+    }
     return TH_OK;
 }

@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(256) ld_grid_kernel(const ThP1 *__restrict__ p
             for (i64 c = cur + 1; c <= n_cells; ++c) first[c] = (int)nt;
     }
 }
-// first[] -> 16-byte cells {pos, cnt, m1 of the row before the bucket (same uuid) or INT64_MIN}
+// first[] -> 32-byte cells {pos, cnt, m1 of the row before the bucket (same uuid) or INT64_MIN, first row {start, m1}}
 __global__ void __launch_bounds__(256) ld_cells_kernel(const int *__restrict__ first, const ThP1 *__restrict__ p1,
                                                        i64 n_cells, int nb, ThCell *cells) {
     for (i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x; c < n_cells; c += (i64)gridDim.x * blockDim.x) {
@@ -182,6 +182,9 @@ __global__ void __launch_bounds__(256) ld_cells_kernel(const int *__restrict__ f
         x.pos = first[c];
         x.cnt = first[c + 1] - x.pos;
         x.m1_before = (c % nb == 0) ? TH_I64_MIN : p1[x.pos - 1].m1;   // bucket 0 starts at the sentinel
+        x.start0 = TH_I64_MAX;                                          // empty bucket: no row before any key
+        x.m1_0 = x.m1_before;
+        if (x.cnt > 0) { const ThP1 r = p1[x.pos]; x.start0 = r.start; x.m1_0 = r.m1; }
         cells[c] = x;
     }
 }

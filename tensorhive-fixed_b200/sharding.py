@@ -252,10 +252,16 @@ class PeerExchange:
         arr = (self._C.c_void_p * self.world)(*[self._C.c_void_p(int(b)) for b in bases])
         self._native.check(self._lib.th_peer_connect(self._h, None, arr))
 
-    def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True, counts=None):
-        """CUDA int64 tensors in; returns an int32 CUDA tensor view [world, words_per_rank] of the gathered words
-        (rank r's words for its own queries sit in row r).  ``counts[r]`` = number of queries rank r contributes
-        this step (``Router.counts``); omit it when every rank has the same number."""
+    def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True, counts=None,
+                       check: bool = True):
+        """int64 tensors in -- CUDA tensors, or page-locked host tensors (``.pin_memory()``), which the kernel streams
+        over PCIe itself; returns an int32 CUDA tensor view [world, words_per_rank] of the gathered words (rank r's
+        words for its own queries sit in row r).  ``counts[r]`` = number of queries rank r contributes this step
+        (``Router.counts``); omit it when every rank has the same number.
+
+        ``check=True`` (default) synchronises the stream and raises ``NativeError(TH_EINTERNAL)`` when a peer's words
+        did not arrive in time (the words of such a step read as 0 and must not be used).  A caller that pipelines
+        steps passes ``check=False`` and calls :meth:`check` before it consumes the words."""
         import torch
         C = self._C
         m = int(q_uuid.numel())
@@ -268,6 +274,8 @@ class PeerExchange:
             snapshot._h, self._h, m, C.c_void_p(q_uuid.data_ptr()), C.c_void_p(q_start.data_ptr()),
             C.c_void_p(q_end.data_ptr()), C.c_void_p(q_self.data_ptr()) if q_self is not None else None, int(mode),
             cnt, 1 if wait else 0, C.byref(out), stream))
+        if check and wait:
+            self.check()
         view = self._views.get(out.value)          # two generations -> two cached views
         if view is None:
             view = torch.as_tensor(_DevWords(out.value, self.world * self.words_per_rank),

@@ -72,7 +72,7 @@ def make_calendar(n: int, n_uuids: int, seed: int, skew: float = 0.0, shuffle_id
             'n_uuids': n_uuids}
 
 
-def make_queries(cal: dict, m: int, seed: int) -> dict:
+def make_queries(cal: dict, m: int, seed: int, unknown_frac: float = 0.01) -> dict:
     """Candidate reservations: 50 % perturbations of an existing row in the four shapes of the reference's
     test (inside / left / right / enclosing, tests/unit/models/test_reservation_model.py:10-37), 25 %
     placed at random (mostly gaps), 15 % exactly touching a row, 10 % self-updates (self_id = row id)."""
@@ -110,7 +110,7 @@ def make_queries(cal: dict, m: int, seed: int) -> dict:
     qe = np.where(s, re_ + off, qe)
     self_id = np.where(s, rid, self_id)
     # a few queries for resources the calendar has never seen
-    unknown = rng.random(m) < 0.01
+    unknown = rng.random(m) < unknown_frac
     ru = np.where(unknown, n_uuids + 3, ru)
     return {'uuid_id': ru.astype(np.int64), 'start': qs.astype(np.int64), 'end': qe.astype(np.int64),
             'self_id': self_id.astype(np.int64)}
@@ -208,3 +208,65 @@ def make_job_tasks(cal: dict, jobs: int, seed: int, n_users: int = 1000) -> dict
     uuid = rng.integers(0, n_uuids, size=t, dtype=np.int64)
     uuid[rng.random(t) < 0.02] = -1
     return {'job_id': job_id, 'uuid_id': uuid, 'owner': job_owner[job_id], 'tasks_per_job': per.astype(np.int64)}
+
+
+# ---- one calendar too large for one host process: generated chunk by chunk (BASELINE configs[4]) -----------------------
+class GlobalCalendar:
+    """A calendar of ``n_uuids`` GPUs and about ``n_rows`` reservations defined CHUNK BY CHUNK (``chunk_uuids`` uuids per
+    chunk, every chunk from its own seed), so that each rank of a multi-GPU job can materialise exactly the uuid range it
+    owns -- and any rank can materialise any other chunk to check the answers that arrive from its peers -- without a
+    process ever holding all rows.  Chunk sizes vary by +-25 % (mild popularity skew), so
+    the uuid partition is balanced by rows, not by uuid count.  Reservation ids are globally unique."""
+
+    def __init__(self, n_rows: int, n_uuids: int, seed: int, chunk_uuids: int = 256):
+        assert n_uuids % chunk_uuids == 0
+        self.n_uuids, self.chunk_uuids, self.seed = int(n_uuids), int(chunk_uuids), int(seed)
+        self.n_chunks = n_uuids // chunk_uuids
+        rng = np.random.default_rng(seed)
+        weight = rng.uniform(0.75, 1.25, size=self.n_chunks)
+        rows = np.floor(weight / weight.sum() * n_rows).astype(np.int64)
+        rows[0] += n_rows - int(rows.sum())
+        self.chunk_rows = rows
+        self.id_base = np.concatenate([[0], np.cumsum(rows)])
+        self.n_rows = int(rows.sum())
+
+    def rows_per_uuid_estimate(self) -> np.ndarray:
+        """What the partitioner balances on: a chunk's rows spread evenly over its uuids."""
+        return np.repeat(self.chunk_rows / self.chunk_uuids, self.chunk_uuids)
+
+    def chunk(self, c: int) -> dict:
+        """Rows of chunk ``c`` with GLOBAL uuid codes and ids."""
+        cal = make_calendar(int(self.chunk_rows[c]), self.chunk_uuids, seed=self.seed + 1000 + c)
+        cal['uuid_id'] = cal['uuid_id'] + c * self.chunk_uuids
+        cal['id'] = cal['id'] + int(self.id_base[c])
+        cal['n_uuids'] = self.n_uuids
+        return cal
+
+    def chunk_queries(self, c: int, m: int, seed: int, unknown_frac: float = 0.0, cal: dict = None) -> dict:
+        """``m`` candidates against chunk ``c`` (global uuid codes; unknown resources get code n_uuids + 3)."""
+        cal = cal if cal is not None else self.chunk(c)
+        local = dict(cal)
+        local['n_uuids'] = self.n_uuids
+        return make_queries(local, m, seed=seed + c, unknown_frac=unknown_frac)
+
+    def chunks_overlapping(self, lo: int, hi: int):
+        return range(lo // self.chunk_uuids, (max(hi, lo + 1) - 1) // self.chunk_uuids + 1) if hi > lo else range(0)
+
+
+def concat_columns(parts, keys) -> dict:
+    return {k: (np.concatenate([p[k] for p in parts]) if parts else np.zeros(0, np.int64)) for k in keys}
+
+
+def make_window_batch(n_uuids: int, samples_per_uuid: int, w: int, seed: int, cadence_us: int = 1_000_000) -> dict:
+    """Vectorised window list over a regular-cadence log (every uuid: ``samples_per_uuid`` samples from T0): lengths
+    U[20 s, 180 s], starts anywhere in the logged span (some windows run past either end), 2 % before the log."""
+    rng = np.random.default_rng(seed)
+    wu = rng.integers(0, n_uuids, size=w, dtype=np.int64)
+    span = samples_per_uuid * cadence_us
+    ws = T0_US + rng.integers(-100_000_000, span, size=w, dtype=np.int64)
+    ws = np.where(rng.random(w) < 0.5, ws - ws % cadence_us, ws)         # half of the starts exactly on a sample
+    we = ws + rng.integers(20_000_000, 180_000_001, size=w, dtype=np.int64)
+    empty = rng.random(w) < 0.02
+    ws = np.where(empty, T0_US - 10 * HOUR_US, ws)
+    we = np.where(empty, T0_US - 9 * HOUR_US, we)
+    return {'uuid_id': wu, 'start': ws, 'end': we}
