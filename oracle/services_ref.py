@@ -6,8 +6,10 @@ TEST INFRASTRUCTURE, NOT PRODUCT CODE: only ``tests/``, ``__graft_entry__.smoke(
 The reference's service code cannot be imported here (it needs SQLAlchemy, gevent, pssh, ...; see
 SURVEY.md section 8c), so the loops are restated over plain dicts/objects with the SQL oracle
 (``sql_ref.SqlCalendar``) standing in for the four ``Reservation.*`` queries.  Each function names the
-reference lines it follows.  None of these paths has a reference test: **parity unpinned by reference
-tests**; the source text is the anchor.
+reference lines it follows.  None of these paths has a reference test; they are pinned instead by vectors
+obtained by EXECUTING the reference's own source files under import stand-ins
+(``tests/golden/make_reference_exec_vectors.py`` -> ``tests/golden/reference_exec_vectors.json``), to which
+``tests/test_oracle_exec_vectors.py`` holds every function below.
 """
 from __future__ import annotations
 
@@ -207,6 +209,36 @@ def avg(data):
         return sum(data) // len(data)
     except ZeroDivisionError:
         return float(-1)
+
+
+# -- UsageLoggingService.log_current_usage (:159-171) + Log.updated_log (:85-105) + handle_expired_logs (:196-229) ------
+def usage_logger_replay(cal: SqlCalendar, ticks, end_us: int):
+    """The usage logger tick by tick over in-memory lists instead of JSON files.  ``ticks`` = [{'now_us', 'gpus':
+    {uuid: {'metrics': {'utilization': {'value'}, 'mem_util': {'value'}}}}}], then one final tick at ``end_us`` with no
+    GPUs.  Per tick (do_run :143-157): every reservation in current_events() whose GPU is present in the infrastructure
+    (extract_specific_gpu_data :231-240 raises otherwise, caught at :170) gets a log; a sample is appended only when
+    BOTH metrics are not None (:95); then every log whose reservation has ended (``end < now``, :207) is summarised with
+    ``avg`` and dropped.  Returns sorted [[id, gpu_util_avg, mem_util_avg], ...] in the order ``save()`` would see them."""
+    logs: Dict[int, Dict[str, list]] = {}
+    saved = []
+    for tick in list(ticks) + [{'now_us': end_us, 'gpus': {}}]:
+        now = tick['now_us']
+        for rid in cal.current_events(now):
+            (_i, uuid, _s, _e, _u, _c) = cal.row(rid)
+            gpu = tick['gpus'].get(uuid)
+            if not gpu:
+                continue
+            log = logs.setdefault(rid, {'g': [], 'm': []})
+            g, m = gpu['metrics']['utilization']['value'], gpu['metrics']['mem_util']['value']
+            if g is not None and m is not None:
+                log['g'].append(g)
+                log['m'].append(m)
+        for rid in sorted(logs):
+            (_i, _uu, _s, e, _u, _c) = cal.row(rid)
+            if e < now:
+                saved.append([rid, avg(logs[rid]['g']), avg(logs[rid]['m'])])
+                del logs[rid]
+    return sorted(saved)
 
 
 class TaskRow:

@@ -43,6 +43,29 @@ cudaError_t th_malloc_async(void **p, size_t bytes, cudaStream_t st) {
     return cudaMallocFromPoolAsync(p, bytes, pool, st);
 }
 
+// ---- per-thread streams for host-array calls ------------------------------------------------------------------
+namespace {
+struct ThreadStreams {
+    cudaStream_t s[64];
+    ThreadStreams() { for (auto &x : s) x = nullptr; }
+    ~ThreadStreams() {
+        // the thread ends: its streams have no work left (every host-array call synchronises before returning)
+        for (auto x : s) if (x) cudaStreamDestroy(x);
+    }
+};
+thread_local ThreadStreams g_thread_streams;
+}  // namespace
+
+cudaStream_t th_call_stream(void *stream, int mem, int device) {
+    if (stream != nullptr || mem != TH_MEM_HOST || device < 0 || device >= 64) return (cudaStream_t)stream;
+    cudaStream_t &s = g_thread_streams.s[device];
+    if (s == nullptr && cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
+        s = nullptr;                 // fall back to the default stream rather than fail the call
+    }
+    return s;
+}
+
 // ---- ThScratch ---------------------------------------------------------------------------------------
 int ThScratch::alloc(void **out, size_t bytes) {
     if (count >= (int)(sizeof(ptrs) / sizeof(ptrs[0]))) {

@@ -291,6 +291,13 @@ struct DeviceGuard {
     ~DeviceGuard() { cudaSetDevice(prev); }
 };
 
+// The stream a call runs on: the caller's, except that a TH_MEM_HOST call given NULL gets a private non-blocking stream of
+// the CALLING THREAD on `device` (created on first use; `device` must be current).  Host-array calls return only after
+// synchronising their stream, so nothing orders them against other streams -- and on the legacy default stream the
+// service threads (3-4 of them plus greenlets) would serialise against each other and against
+// every other stream of the process.
+cudaStream_t th_call_stream(void *stream, int mem, int device);
+
 // ---- host-side scratch: stream-ordered device buffers used to stage TH_MEM_HOST calls -----------------
 struct ThScratch {
     cudaStream_t st;

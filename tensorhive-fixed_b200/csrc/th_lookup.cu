@@ -214,7 +214,7 @@ extern "C" int th_current_owner(const th_snapshot *h, int64_t now_us, int64_t *o
     TH_REQUIRE(out_res_id && out_owner, "th_current_owner: NULL output");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_current_owner: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zu = (size_t)h->n_uuids;
     void *d_res, *d_own;
@@ -239,7 +239,7 @@ extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_
     TH_REQUIRE(uuids && out_first_id && out_first_start && out_first_owner && out_count, "th_upcoming: NULL array");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_upcoming: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zk = (size_t)k;
     const void *d_u;
@@ -272,7 +272,7 @@ extern "C" int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int
     TH_REQUIRE(task_uuid && task_owner && out_flag_u8, "th_upcoming_owner_flags: NULL array");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_upcoming_owner_flags: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zt = (size_t)t;
     const void *d_u, *d_o;
@@ -299,7 +299,7 @@ extern "C" int th_violation_join(const th_snapshot *h, int64_t now_us, int stric
     TH_REQUIRE(proc_uuid && proc_owner && out_flag_u8 && out_res_id, "th_violation_join: NULL array");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_violation_join: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zp = (size_t)p, zu = (size_t)h->n_uuids;
     // scratch: the per-uuid "current reservation" table the join probes

@@ -104,7 +104,7 @@ extern "C" int th_sort_pairs(int device, int64_t n, const int64_t *k_hi, const i
     int prev = 0;
     TH_CUDA(cudaGetDevice(&prev));
     if (prev != device) TH_CUDA(cudaSetDevice(device));
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, device);
     int rc = TH_OK;
     {
         ThScratch sc(st);

@@ -16,12 +16,16 @@
 // can match; a second pass re-walks the examined range forwards and compacts matches with ballots.
 #include "th_common.cuh"
 #include <stdlib.h>
+#include <atomic>
 
 namespace {
 
 constexpr int BM_THREADS = 256;
 #ifndef BM_MIN_BLOCKS
 #define BM_MIN_BLOCKS 4
+#endif
+#ifndef BM_PIPE
+#define BM_PIPE 0
 #endif
 constexpr int BM_MAXW = 2048;   // bitmap words a CTA buffers for the fused exchange (8 KB)
 
@@ -224,15 +228,7 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     // Also measured and dropped: probes without default values (every use guarded by the probe's own predicate, saving
     // ~36 moves per tile) and per-lane precomputed staging addresses: ptxas then needs 64 registers plus 56 bytes of
     // spill (predicate pressure), 28.6 us cold / 19.8 us warm / 279 us at 16 M queries.
-    u32 it = 0;
-    for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
-        i64 u, qs, qe, self;
-        ThCellV cell;
-        fetch(tile, it, u, qs, qe, self, cell);
-        const i64 i = tile * 32 + lane;
-        // (qe = INT64_MIN cannot lie after any start, not even the sentinel's: no row, no conflict)
-        const bool hit = (i < m) && (u >= 0 && u < n_uuids) && qe > TH_I64_MIN &&
-                         k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
+    auto emit = [&](i64 tile, bool hit) {
         const u32 word = __ballot_sync(0xffffffffu, hit);
         if (lane == 0) {
             if (out_bits) out_bits[tile] = word;
@@ -242,7 +238,43 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
                 for (int p = 0; p < po.n; ++p) po.dst[p][po.word_off + tile] = slot;
             }
         }
+    };
+#if BM_PIPE
+    // Two tiles in flight per warp: the cell of tile k + 1 is requested before the rows of tile k are probed, so an
+    // iteration exposes one round trip to L2 / HBM instead of two.  The loads are volatile asm, which keeps their order.
+    {
+        u32 it = 0;
+        i64 tile = tile_of(0);
+        i64 u = 0, qs = 0, qe = 0, self = -1;
+        ThCellV cell = {0, 0, 0, 0};
+        bool have = tile < t_end;
+        if (have) fetch(tile, it, u, qs, qe, self, cell);
+        while (have) {
+            const i64 ntile = tile_of(it + 1);
+            const bool nhave = ntile < t_end;
+            i64 nu = 0, nqs = 0, nqe = 0, nself = -1;
+            ThCellV ncell = {0, 0, 0, 0};
+            if (nhave) fetch(ntile, it + 1, nu, nqs, nqe, nself, ncell);
+            const i64 i = tile * 32 + lane;
+            const bool hit = (i < m) && (u >= 0 && u < n_uuids) && qe > TH_I64_MIN &&
+                             k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
+            emit(tile, hit);
+            tile = ntile; u = nu; qs = nqs; qe = nqe; self = nself; cell = ncell; have = nhave; ++it;
+        }
     }
+#else
+    u32 it = 0;
+    for (i64 tile = tile_of(0); tile < t_end; tile = tile_of(++it)) {
+        i64 u, qs, qe, self;
+        ThCellV cell;
+        fetch(tile, it, u, qs, qe, self, cell);
+        const i64 i = tile * 32 + lane;
+        // (qe = INT64_MIN cannot lie after any start, not even the sentinel's: no row, no conflict)
+        const bool hit = (i < m) && (u >= 0 && u < n_uuids) && qe > TH_I64_MIN &&
+                         k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
+        emit(tile, hit);
+    }
+#endif
     if (buffered) {
         // Fused exchange: the CTA's run of words goes straight into every rank's slot array over NVLink as coalesced
         // 8-byte {word, epoch} stores (256-byte packets; a 4-byte store per word and tile was measured at +3 us per
@@ -561,17 +593,26 @@ static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d
                      int mode, u32 *d_bits, const ThPeerOut &po, cudaStream_t st, int ctas_per_sm = 0) {
     const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp at least one tile
     // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
-    static int occ[2] = {0, 0};
+    // (per device and mode; the query is a pure function of both, so racing first uses write the same value)
+    static std::atomic<int> occ_cache[64][2];
+    static std::atomic<int> sms_cache[64];
     const int oi = mode == TH_MODE_STRICT ? 0 : 1;
-    if (occ[oi] == 0) {
+    const int di = h->device >= 0 && h->device < 64 ? h->device : 0;
+    int occ = occ_cache[di][oi].load(std::memory_order_relaxed);
+    if (occ == 0) {
         int v = 0;
         if (mode == TH_MODE_STRICT) TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_STRICT>, BM_THREADS, 0));
         else TH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k2_bitmap_kernel<TH_MODE_INCLUSIVE>, BM_THREADS, 0));
-        occ[oi] = v > 0 ? v : 1;
+        occ = v > 0 ? v : 1;
+        occ_cache[di][oi].store(occ, std::memory_order_relaxed);
     }
-    int n_sms = TH_NUM_SMS;
-    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, h->device);
-    const i64 resident = (i64)n_sms * (ctas_per_sm > 0 && ctas_per_sm < occ[oi] ? ctas_per_sm : occ[oi]);
+    int n_sms = sms_cache[di].load(std::memory_order_relaxed);
+    if (n_sms == 0) {
+        n_sms = TH_NUM_SMS;
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, h->device);
+        sms_cache[di].store(n_sms, std::memory_order_relaxed);
+    }
+    const i64 resident = (i64)n_sms * (ctas_per_sm > 0 && ctas_per_sm < occ ? ctas_per_sm : occ);
     const unsigned blocks = (unsigned)(n_tiles < resident ? (n_tiles > 0 ? n_tiles : 1) : resident);
     int al16 = ((((uintptr_t)d_u | (uintptr_t)d_s | (uintptr_t)d_e | (uintptr_t)d_f) & 15) == 0) ? 1 : 0;
     if (getenv("TH_K2_DIRECT")) al16 = 0;
@@ -633,7 +674,7 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     TH_REQUIRE(mode != TH_MODE_STRICT || q_self_id, "th_conflict_bitmap: q_self_id is NULL");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_conflict_bitmap: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zm = (size_t)m, words = (zm + 31) / 32;
     const void *d_u, *d_s, *d_e, *d_f = nullptr;
@@ -690,7 +731,7 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_REQUIRE(capacity == 0 || (out_ids && out_cancelled_u8), "th_conflict_sets: NULL output with capacity > 0");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_conflict_sets: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zm = (size_t)m;
     *out_needed = 0;

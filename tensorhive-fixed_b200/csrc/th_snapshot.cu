@@ -424,7 +424,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
     TH_REQUIRE(n == 0 || n_uuids > 0, "th_snapshot_load: rows given but n_uuids == 0");
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_snapshot_load: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
 
     // A reload whose table fits the buffers of the previous one reuses them (cudaMalloc/cudaFree of ~80 MB cost
     // more than the sort itself); otherwise everything is released and reallocated.
@@ -609,7 +609,7 @@ extern "C" int th_snapshot_export(const th_snapshot *h, int64_t *id, int64_t *uu
     TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_snapshot_export: bad mem flag %d", mem);
     DeviceGuard guard(h->device);
     if (!guard.ok) { th_set_error("th_snapshot_export: cannot select device %d", h->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
     ThScratch sc(st);
     const size_t zn = (size_t)h->n, zu = (size_t)h->n_uuids + 1;
     void *d_id, *d_uuid, *d_start, *d_end, *d_owner, *d_canc, *d_seg;
@@ -658,7 +658,7 @@ extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src,
     TH_REQUIRE(n_delete == 0 || delete_ids, "th_snapshot_apply_delta: delete_ids is NULL");
     DeviceGuard guard(src->device);
     if (!guard.ok) { th_set_error("th_snapshot_apply_delta: cannot select device %d", src->device); return TH_ECUDA; }
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, src->device);
     ThScratch sc(st);
     const size_t zu = (size_t)n_upsert, zd = (size_t)n_delete;
     const void *u_id, *u_uuid, *u_start, *u_end, *u_owner, *u_canc, *d_del;
@@ -724,5 +724,5 @@ extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src,
     // the gathers above read `src`; if dst == src the rebuild below overwrites it only after them (stream order)
     // survivors come out of the source in (uuid, start, id) order: only the upserted rows are sorted, then merged in
     return th_load_impl(dst, n_new, n_uuids, (const int64_t *)c_id, (const int64_t *)c_uuid, (const int64_t *)c_start,
-                        (const int64_t *)c_end, (const int64_t *)c_owner, c_canc, TH_MEM_DEVICE, stream, n_keep);
+                        (const int64_t *)c_end, (const int64_t *)c_owner, c_canc, TH_MEM_DEVICE, (void *)st, n_keep);
 }

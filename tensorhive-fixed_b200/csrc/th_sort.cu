@@ -18,6 +18,7 @@
 // The digit plan covers only the key bits that can differ (callers pass bit widths), so a
 // (4096-uuid, 47-bit start) key runs 6 + 2 passes, not 12.
 #include "th_common.cuh"
+#include <atomic>
 
 namespace {
 
@@ -312,13 +313,14 @@ int th_radix_sort(ThRec *a, ThRec *b, i64 n, int k0_bits, int k1_bits, ThRec **s
         return TH_OK;
     }
 
-    static bool attr_set[64] = {false};
+    // once per device; the attribute call is idempotent, so two threads racing on the first use is harmless
+    static std::atomic<bool> attr_set[64];
     int dev = 0;
     TH_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
+    if (dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
         TH_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(RsSmem)));
-        attr_set[dev] = true;
+        if (dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
 
     const u32 tiles = (u32)((n + RS_TILE - 1) / RS_TILE);

@@ -313,7 +313,7 @@ static int usage_reduce_impl(int elem, int device, int64_t s, int64_t n_uuids, c
     int prev = 0;
     TH_CUDA(cudaGetDevice(&prev));
     if (mem == TH_MEM_HOST && prev != device) TH_CUDA(cudaSetDevice(device));
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = th_call_stream(stream, mem, device);
     int rc = TH_OK;
     {
         ThScratch sc(st);

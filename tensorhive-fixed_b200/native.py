@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'lib', 'libth_b200.so')
+# TH_B200_LIB (diagnostics only): load another build of the same library, e.g. an experiment variant under lib/variants/
+LIB_PATH = os.environ.get('TH_B200_LIB') or os.path.join(_HERE, 'lib', 'libth_b200.so')
 
 MEM_HOST, MEM_DEVICE = 0, 1
 
