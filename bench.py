@@ -647,6 +647,29 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
     torch.cuda.synchronize()
     ms = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in evs])))
     barrier()
+    # the same 10 M windows in RANDOM order (a reservation table in id order is not sorted by (uuid, start); the generator
+    # above deals windows to uuids in runs with increasing starts, i.e. a stream): results must be the same set
+    perm = torch.randperm(S_WINDOWS, device=dev)
+    wu_s, ws_s, we_s = wu[perm].contiguous(), ws[perm].contiguous(), we[perm].contiguous()
+    outs_s = [i64(S_WINDOWS) for _ in range(5)]
+
+    def k4_shuffled_step():
+        native.check(lib.th_usage_reduce(local, s_total, S_UUIDS, off.data_ptr(), ts.data_ptr(), gpu.data_ptr(),
+                                         mem.data_ptr(), S_WINDOWS, wu_s.data_ptr(), ws_s.data_ptr(), we_s.data_ptr(),
+                                         outs_s[0].data_ptr(), outs_s[1].data_ptr(), outs_s[2].data_ptr(),
+                                         outs_s[3].data_ptr(), outs_s[4].data_ptr(), 1, sp))
+
+    for _ in range(2):
+        k4_shuffled_step()
+    evs_s = []
+    for _ in range(max(3, steps // 4)):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream); k4_shuffled_step(); b.record(stream)
+        evs_s.append((a, b))
+    torch.cuda.synchronize()
+    ms_shuffled = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in evs_s])))
+    shuffled_same = all(bool(torch.equal(x[perm], y)) for x, y in zip(outs, outs_s))
+    del wu_s, ws_s, we_s, outs_s, perm
     # SURVEY section 8d counts 24 B per sample (ts, gpu, mem) and defines the reported "usage-reduce GB/s" as that figure
     # over time.  The kernel never streams the ts column (it is probed: 2 x 128 B per window), so against the roofline
     # only what it must move is counted: 16 B per sample, the window columns in, five int64 results out, the uuid table.
@@ -711,6 +734,10 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
                          'dram_GBs_from_ncu_traffic': (traffic / (ms * 1e-3) / 1e9) if traffic else None,
                          'frac_survey_8d_bytes': gbs_survey / peak},
             'cpu_baseline': cpu,
+            'windows_shuffled': {'ms_per_step': ms_shuffled, 'roofline_frac': alg / (ms_shuffled * 1e-3) / 1e9 / peak,
+                                 'slowdown_vs_sorted_windows': ms_shuffled / ms, 'results_identical': shuffled_same,
+                                 'note': 'the same 10M windows in random order (as a reservation table in id order would '
+                                         'present them) instead of grouped by uuid with increasing starts'},
             'narrow_u8': {'ms_per_step': ms8, 'samples_per_s': world * s_total / (ms8 * 1e-3),
                           'speedup_vs_int64_columns': ms / ms8, 'results_identical_to_int64_path': same,
                           'roofline': {'kernel': 'k4_usage_u8_kernel', 'bound': 'hbm', 'achieved': gbs8, 'peak': peak,

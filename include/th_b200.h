@@ -16,7 +16,9 @@
  *     th_conflict_bitmap reads page-locked (cudaHostAlloc / cudaHostRegister) TH_MEM_HOST columns in place:
  *     the kernel streams them over PCIe itself, no staging copy (TH_NO_ZERO_COPY=1 in the environment
  *     forces the staged path).
- *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - `stream` is a cudaStream_t passed as void*.  NULL means: with TH_MEM_DEVICE the legacy default stream; with
+ *     TH_MEM_HOST a private non-blocking stream of the CALLING THREAD, so that service threads making host-array
+ *     calls neither serialise against each other nor synchronise with the process's other streams.
  *   - a loaded snapshot is immutable; any number of threads may query it concurrently.  Loading is
  *     not concurrent with queries on the same handle (swap handles instead -- see DESIGN.md).
  *   - time is int64 microseconds since the Unix epoch (naive UTC), the grain of the reference's
@@ -61,6 +63,11 @@ typedef struct th_snapshot th_snapshot;
 int th_version(void);
 const char *th_last_error(void);
 
+/* Diagnostics (no counterpart in the reference): bytes the library's stream-ordered staging pool on `device` has
+ * reserved from the driver, bytes of it in use right now, and the high-water mark of the latter since it was last
+ * reset (reset_high != 0 resets it after reading).  Any pointer may be NULL. */
+int th_pool_stats(int device, int64_t *reserved_bytes, int64_t *used_bytes, int64_t *used_high_bytes, int reset_high);
+
 /* Handle lifecycle.  The handle owns the device copy of the `reservations` table
  * (class Reservation columns, tensorhive/models/Reservation.py:14-37). */
 int th_snapshot_create(int device, th_snapshot **out);
@@ -70,7 +77,9 @@ int th_snapshot_destroy(th_snapshot *h);
  * segment offsets and running maxima of `end` are built.  Replaces what SQLite does on every call in
  * the reference -- a full scan of `reservations` (no index exists; tensorhive/database.py:19-23,
  * migrations ce624ab2c458:35-46) -- and the ORDER BY _start of Reservation.py:117.
- * cancelled_u8[i] = 1 iff `is_cancelled is not None and is_cancelled` (Reservation.py:81-83). */
+ * cancelled_u8[i] = 1 iff `is_cancelled is not None and is_cancelled` (Reservation.py:81-83).
+ * ids must be unique and >= 0 (the primary key).  A load that is refused (bad uuid range, negative or duplicate ids,
+ * INT64_MIN start, grid too large) leaves a previously loaded snapshot untouched and queryable. */
 int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
                      const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
                      const uint8_t *cancelled_u8, int mem, void *stream);
@@ -80,7 +89,8 @@ int th_snapshot_load(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *
  * delta: `dst` becomes `src` without the rows whose id is upserted or deleted, plus the upserted rows (insert, update
  * and cancel are all upserts), re-indexed on the device.  Only the delta crosses PCIe.  dst may be src (in place; then
  * no query may run on it meanwhile) or a second handle (readers keep using src until the caller swaps).  n_uuids may
- * grow but not shrink. */
+ * grow but not shrink.  Every id may appear at most once in the delta (upserts and deletes together): collapse a
+ * batch first (last change wins); TH_EINVAL otherwise, and `dst` is left as it was. */
 int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src, int64_t n_uuids, int64_t n_upsert, const int64_t *id,
                             const int64_t *uuid_id, const int64_t *start_us, const int64_t *end_us, const int64_t *owner,
                             const uint8_t *cancelled_u8, int64_t n_delete, const int64_t *delete_ids, int mem,
@@ -176,6 +186,27 @@ int th_usage_reduce_u8(int device, int64_t s, int64_t n_uuids, const int64_t *uu
                        const uint8_t *gpu_util_u8, const uint8_t *mem_util_u8, int64_t w, const int64_t *win_uuid,
                        const int64_t *win_start, const int64_t *win_end, int64_t *out_sum_gpu, int64_t *out_sum_mem,
                        int64_t *out_count, int64_t *out_avg_gpu, int64_t *out_avg_mem, int mem, void *stream);
+
+/* Device-resident usage log, replacing the per-reservation JSON files that the usage logger
+ * re-reads and re-writes on every tick (tensorhive/core/services/UsageLoggingService.py:85-116, 159-171).  One region per
+ * GPU uuid inside device columns (ts int64, gpu_util / mem_util uint8).  th_ring_append takes one monitoring tick (or any
+ * batch) as HOST arrays -- a sample is appended by the caller only when both metrics are present (:92-99); timestamps of
+ * a uuid must not decrease; uuid codes beyond the current count extend the ring -- and costs one small H2D copy plus one
+ * scatter kernel whatever the log's length (a full region doubles first).  th_ring_reduce is th_usage_reduce_u8 over the
+ * ring in place (handle_expired_logs :196-229 for a list of windows): nothing is re-uploaded but a 32-byte entry per uuid
+ * after appends.  While a uuid's log is an exact arithmetic run (ts[k] = t0 + k * cadence) its timestamps are treated as
+ * delta-encoded: both window ends follow from divisions and the ts column is not read.  Calls on one ring serialise on
+ * an internal lock.  th_ring_info: any pointer may be NULL. */
+typedef struct th_ring th_ring;
+int th_ring_create(int device, int64_t samples_per_uuid_hint, th_ring **out);
+int th_ring_destroy(th_ring *r);
+int th_ring_append(th_ring *r, int64_t k, const int64_t *uuid, const int64_t *ts_us, const uint8_t *gpu_util_u8,
+                   const uint8_t *mem_util_u8, void *stream);
+int th_ring_reduce(th_ring *r, int64_t w, const int64_t *win_uuid, const int64_t *win_start, const int64_t *win_end,
+                   int64_t *out_sum_gpu, int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu,
+                   int64_t *out_avg_mem, int mem, void *stream);
+int th_ring_info(th_ring *r, int64_t *n_uuids, int64_t *samples, int64_t *capacity, int64_t *device_bytes,
+                 int64_t *regular_uuids, int64_t *relayouts);
 
 /* Multi-GPU exchange (no counterpart in the reference, which is single-process CPU code).
  * One process per GPU; rank r owns a contiguous uuid range.  th_peer_create allocates this rank's slot buffer (two

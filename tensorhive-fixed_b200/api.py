@@ -243,10 +243,12 @@ class Snapshot:
                             ('out_flags', out_flags, torch.uint8), ('out_res_id', out_res_id, torch.int64)):
             if not (_is_torch_cuda(t) and t.dtype == dt and t.is_contiguous()):
                 raise TypeError('%s must be a contiguous CUDA tensor of %s' % (name, dt))
+            if t.device.index != self.device:          # the C entry point cannot tell: a tensor of another GPU would fault
+                raise ValueError('%s lives on cuda:%s, the snapshot on cuda:%d' % (name, t.device.index, self.device))
         p = int(proc_uuid.numel())
         if not (proc_owner.numel() == p and out_flags.numel() == p and out_res_id.numel() == p):
             raise ValueError('all four arrays must have the same length')
-        stream = C.c_void_p(torch.cuda.current_stream(proc_uuid.device).cuda_stream)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         native.check(self._lib.th_violation_join_static(self._h, int(now_us), 1 if strict else 0, p,
                                                         C.c_void_p(proc_uuid.data_ptr()), C.c_void_p(proc_owner.data_ptr()),
                                                         C.c_void_p(out_flags.data_ptr()), C.c_void_p(out_res_id.data_ptr()),

@@ -43,6 +43,31 @@ cudaError_t th_malloc_async(void **p, size_t bytes, cudaStream_t st) {
     return cudaMallocFromPoolAsync(p, bytes, pool, st);
 }
 
+// Diagnostics: what the library's staging pool on `device` holds (0s when no call has needed it yet).
+extern "C" int th_pool_stats(int device, int64_t *reserved_bytes, int64_t *used_bytes, int64_t *used_high_bytes,
+                             int reset_high) {
+    TH_REQUIRE(device >= 0 && device < 64, "th_pool_stats: device %d outside [0, 64)", device);
+    cudaMemPool_t pool;
+    {
+        std::lock_guard<std::mutex> lock(g_pool_mutex);
+        pool = g_pools[device];
+    }
+    unsigned long long r = 0, u = 0, hi = 0;
+    if (pool != nullptr) {
+        TH_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &r));
+        TH_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &u));
+        TH_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &hi));
+        if (reset_high) {
+            unsigned long long zero = 0;
+            TH_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &zero));
+        }
+    }
+    if (reserved_bytes) *reserved_bytes = (int64_t)r;
+    if (used_bytes) *used_bytes = (int64_t)u;
+    if (used_high_bytes) *used_high_bytes = (int64_t)hi;
+    return TH_OK;
+}
+
 // ---- per-thread streams for host-array calls ------------------------------------------------------------------
 namespace {
 struct ThreadStreams {

@@ -27,6 +27,9 @@ constexpr int BM_THREADS = 256;
 #ifndef BM_PIPE
 #define BM_PIPE 0
 #endif
+#ifndef BM_CELL_LD      // how the 32-byte cell is read: 0 = one LDG.256, 1 = two LDG.128, 2 = LDG.128 + second half on demand
+#define BM_CELL_LD 0
+#endif
 constexpr int BM_MAXW = 2048;   // bitmap words a CTA buffers for the fused exchange (8 KB)
 
 // One lane per query, persistent warps.  Two things bound this kernel, and neither is bytes: (1) a memory
@@ -200,7 +203,22 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
         }
         stage_in(tile_of(it + BM_STAGES), st);
+#if BM_CELL_LD == 0
         cell = th_ld32_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, ThCellV{0, 0, 0, 0});   // no uuids: no grid
+#else
+        {
+            const ThCell *cp = k2_cell_of(g, n_uuids, u, qe);
+            const longlong2 a = th_ld16_if_off<0>(cp, n_uuids > 0, make_longlong2(0, 0));
+#if BM_CELL_LD == 1
+            const longlong2 b = th_ld16_if_off<16>(cp, n_uuids > 0, make_longlong2(0, 0));
+#else
+            // the first row only matters when the bucket has one and the rows before it do not already settle the verdict
+            const bool want = n_uuids > 0 && (int)(a.x >> 32) > 0 && (MODE != TH_MODE_STRICT || self >= 0 || a.y <= qs);
+            const longlong2 b = th_ld16_if_off<16>(cp, want, make_longlong2(TH_I64_MAX, a.y));
+#endif
+            cell.pc = a.x; cell.m1_before = a.y; cell.start0 = b.x; cell.m1_0 = b.y;
+        }
+#endif
     };
 
 #pragma unroll

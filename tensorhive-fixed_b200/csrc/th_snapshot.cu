@@ -76,6 +76,13 @@ __global__ void __launch_bounds__(256) ld_idrec_kernel(const i64 *__restrict__ i
     }
 }
 
+// records sorted by id: any two neighbours with the same id? (ids must be unique: the merge, the id ranking of the row
+// lists and the `id != self` exclusion all rely on it)
+__global__ void __launch_bounds__(256) ld_dup_kernel(const ThRec *__restrict__ rec, i64 n, int *flag) {
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n; i += (i64)gridDim.x * blockDim.x)
+        if (rec[i].k0 == rec[i + 1].k0) *flag = 1;
+}
+
 // records keyed by (uuid, start - min_start); `order` (optional) gives the ascending-id visiting order
 __global__ void __launch_bounds__(256) ld_keyrec_kernel(const i64 *__restrict__ uuid, const i64 *__restrict__ start,
                                                         const ThRec *__restrict__ order, i64 n, i64 min_start,
@@ -409,6 +416,18 @@ __global__ void __launch_bounds__(256) dl_append_kernel(i64 n_up, i64 base, cons
 
 }  // namespace
 
+// time grid: power-of-two bucket width chosen for ~1.5 cells per row (TH_GRID_CELLS_PER_ROW_X4 / 4)
+static void ld_grid_plan(i64 n, i64 n_uuids, u64 span, int *shift_out, i64 *nb_out) {
+    i64 x4 = 6;
+    if (const char *env = getenv("TH_GRID_CELLS_PER_ROW_X4")) { x4 = atoll(env); if (x4 < 1) x4 = 1; if (x4 > 64) x4 = 64; }
+    i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
+    if (target < 1) target = 1;
+    int shift = 0;
+    while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
+    *shift_out = shift;
+    *nb_out = (i64)(span >> shift) + 1;
+}
+
 // `presorted` >= 0: rows [0, presorted) are already in (uuid, start, id) order (th_snapshot_apply_delta hands over
 // the survivors of the source snapshot that way); only the rows behind them are sorted, then the two runs are merged.
 static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
@@ -426,31 +445,37 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
     if (!guard.ok) { th_set_error("th_snapshot_load: cannot select device %d", h->device); return TH_ECUDA; }
     cudaStream_t st = th_call_stream(stream, mem, h->device);
 
-    // A reload whose table fits the buffers of the previous one reuses them (cudaMalloc/cudaFree of ~80 MB cost
-    // more than the sort itself); otherwise everything is released and reallocated.
     const i64 nt = n + n_uuids;
     const size_t zn = (size_t)n, znt = (size_t)(nt > 0 ? nt : 1);
-    h->loaded = 0;
-    if (znt > (size_t)h->cap_nt || n_uuids + 1 > h->cap_uuids) {
-        th_snapshot_release_internal(h);
-        TH_CUDA(cudaMalloc((void **)&h->seg, sizeof(int) * (size_t)(n_uuids + 1)));
-        TH_CUDA(cudaMalloc((void **)&h->p1, sizeof(ThP1) * znt));
-        TH_CUDA(cudaMalloc((void **)&h->p2, sizeof(ThP2) * znt));
-        TH_CUDA(cudaMalloc((void **)&h->p3, sizeof(ThP3) * znt));
-        TH_CUDA(cudaMalloc((void **)&h->p4, sizeof(ThP4) * znt));
-        TH_CUDA(cudaMalloc((void **)&h->uuid, sizeof(u32) * znt));
-        h->cap_nt = (i64)znt;
-        h->cap_uuids = n_uuids + 1;
-    }
-    h->n_uuids = n_uuids;
-    h->max_id = 0;
-    size_t bytes = sizeof(int) * (size_t)h->cap_uuids + (sizeof(ThP1) * 4 + sizeof(u32)) * (size_t)h->cap_nt;
+    // Everything up to the payload gather works on scratch only: the handle is not touched before the input has been
+    // validated and sorted, so a rejected (re)load -- bad uuid range, negative or duplicate ids, out of memory for the
+    // scratch -- leaves a previously loaded snapshot exactly as it was.
+    auto claim_buffers = [&]() -> int {
+        // A reload whose table fits the buffers of the previous one reuses them (cudaMalloc/cudaFree of ~80 MB cost
+        // more than the sort itself); otherwise everything is released and reallocated.
+        h->loaded = 0;
+        if (znt > (size_t)h->cap_nt || n_uuids + 1 > h->cap_uuids) {
+            th_snapshot_release_internal(h);
+            TH_CUDA(cudaMalloc((void **)&h->seg, sizeof(int) * (size_t)(n_uuids + 1)));
+            TH_CUDA(cudaMalloc((void **)&h->p1, sizeof(ThP1) * znt));
+            TH_CUDA(cudaMalloc((void **)&h->p2, sizeof(ThP2) * znt));
+            TH_CUDA(cudaMalloc((void **)&h->p3, sizeof(ThP3) * znt));
+            TH_CUDA(cudaMalloc((void **)&h->p4, sizeof(ThP4) * znt));
+            TH_CUDA(cudaMalloc((void **)&h->uuid, sizeof(u32) * znt));
+            h->cap_nt = (i64)znt;
+            h->cap_uuids = n_uuids + 1;
+        }
+        h->n_uuids = n_uuids;
+        return TH_OK;
+    };
+    i64 new_max_id = 0;
 
     ThScratch sc(st);
     int passes_total = 0;
     i64 min_start = 0, max_start = 0;
     const int ugrid = th_grid_for(n_uuids + 1, 256, 8);
     if (n == 0) {
+        TH_TRY(claim_buffers());
         ld_seg_empty_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg);
         TH_CUDA(cudaGetLastError());
     } else {
@@ -482,7 +507,14 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         TH_REQUIRE(stats.min_start > TH_I64_MIN, "th_snapshot_load: start_us == INT64_MIN is reserved");
         min_start = stats.min_start;
         max_start = stats.max_start;
-        h->max_id = stats.max_id;
+        {   // the time grid must fit too, and that is known now: refuse before the handle is touched
+            int gs = 0;
+            i64 gnb = 1;
+            ld_grid_plan(n, n_uuids, (u64)max_start - (u64)min_start, &gs, &gnb);
+            TH_REQUIRE(n_uuids * gnb < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)",
+                       (long long)(n_uuids * gnb));
+        }
+        new_max_id = stats.max_id;
 
         ThRec *ra = nullptr, *rb = nullptr;
         TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));
@@ -526,6 +558,13 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             TH_CUDA(cudaGetLastError());
             TH_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &sorted, &passes, st));
             passes_total += passes;
+            int *d_dup = nullptr, dup = 0;
+            TH_TRY(sc.alloc((void **)&d_dup, sizeof(int)));
+            TH_CUDA(cudaMemsetAsync(d_dup, 0, sizeof(int), st));
+            ld_dup_kernel<<<grid, 256, 0, st>>>(sorted, n, d_dup);
+            TH_CUDA(cudaMemcpyAsync(&dup, d_dup, sizeof(int), cudaMemcpyDeviceToHost, st));
+            TH_CUDA(cudaStreamSynchronize(st));
+            TH_REQUIRE(dup == 0, "th_snapshot_load: reservation ids are not unique");
             order = sorted;
             ThRec *rc_buf = nullptr;
             TH_TRY(sc.alloc((void **)&rc_buf, sizeof(ThRec) * zn));
@@ -540,12 +579,15 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
                              th_bits_for((u64)stats.max_uuid), &sorted, &passes, st));
         passes_total += passes;
         }
-        // 3. payload gather + sentinel positions
+        // 3. payload gather + sentinel positions: from here on the handle's own buffers are written
+        TH_TRY(claim_buffers());
         ld_finalize_kernel<<<grid, 256, 0, st>>>(sorted, n, n_uuids, stats.min_start, (const i64 *)d_id,
                                                  (const i64 *)d_end, (const i64 *)d_owner, (const u8 *)d_canc, h->p1,
                                                  h->p3, h->p4, h->uuid, h->seg);
         TH_CUDA(cudaGetLastError());
     }
+    h->max_id = new_max_id;
+    size_t bytes = sizeof(int) * (size_t)h->cap_uuids + (sizeof(ThP1) * 4 + sizeof(u32)) * (size_t)h->cap_nt;
     if (nt > 0) {
         ld_sentinel_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, h->p2, h->p3, h->p4, h->uuid);
         TH_CUDA(cudaGetLastError());
@@ -561,15 +603,10 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             sc_fix_kernel<<<grid_nt, SC_THREADS, 0, st>>>(h->uuid, h->seg, nt, agg, h->p1, h->p2, h->p4);
             TH_CUDA(cudaGetLastError());
         }
-        // 5. time grid: power-of-two bucket width chosen for ~1-2 cells per row (TH_GRID_CELLS_PER_ROW_X4 / 4)
-        const u64 span = (u64)max_start - (u64)min_start;
-        i64 x4 = 6;
-        if (const char *env = getenv("TH_GRID_CELLS_PER_ROW_X4")) { x4 = atoll(env); if (x4 < 1) x4 = 1; if (x4 > 64) x4 = 64; }
-        i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
-        if (target < 1) target = 1;
+        // 5. time grid
         int shift = 0;
-        while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
-        const i64 nb = (i64)(span >> shift) + 1;
+        i64 nb = 1;
+        ld_grid_plan(n, n_uuids, (u64)max_start - (u64)min_start, &shift, &nb);
         const i64 n_cells = n_uuids * nb;
         TH_REQUIRE(n_cells < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)", (long long)n_cells);
         int *first = nullptr;
@@ -680,7 +717,16 @@ extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src,
                                                                        n_delete, ka);
         TH_CUDA(cudaGetLastError());
         int passes = 0;
-        TH_TRY(th_radix_sort(ka, kb, n_kill, 63, 0, &kill, &passes, st));
+        TH_TRY(th_radix_sort(ka, kb, n_kill, 64, 0, &kill, &passes, st));      // as u64: a negative id sorts last, matches nothing
+    }
+    // ids must be unique over the whole delta: two upserts of one id would both land in the table, and an id that is
+    // upserted AND deleted has no defined order (callers collapse their batch first; Calendar.apply_delta does)
+    int *d_dup = nullptr;
+    TH_TRY(sc.alloc((void **)&d_dup, sizeof(int)));
+    TH_CUDA(cudaMemsetAsync(d_dup, 0, sizeof(int), st));
+    if (n_kill > 1) {
+        ld_dup_kernel<<<th_grid_for(n_kill, 256, 8), 256, 0, st>>>(kill, n_kill, d_dup);
+        TH_CUDA(cudaGetLastError());
     }
     // survivors
     const i64 nt = src->nt;
@@ -695,8 +741,11 @@ extern "C" int th_snapshot_apply_delta(th_snapshot *dst, const th_snapshot *src,
     }
     TH_TRY(th_exclusive_scan_i32(keep, nt, off, totals, sc, st));
     i64 tot[2] = {0, 0};
+    int dup = 0;
     TH_CUDA(cudaMemcpyAsync(tot, totals, 16, cudaMemcpyDeviceToHost, st));
+    TH_CUDA(cudaMemcpyAsync(&dup, d_dup, sizeof(int), cudaMemcpyDeviceToHost, st));
     TH_CUDA(cudaStreamSynchronize(st));
+    TH_REQUIRE(dup == 0, "th_snapshot_apply_delta: an id appears more than once in the delta (upserts + deletes)");
     const i64 n_keep = tot[0];
     const i64 n_new = n_keep + n_upsert;
     TH_REQUIRE(n_new < (1ll << 30), "th_snapshot_apply_delta: %lld rows exceed the 2^30 limit", (long long)n_new);

@@ -229,7 +229,10 @@ __device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *
 // ELEM = bytes per utilisation sample (8: int64 columns, 1: uint8 columns); VEC = the columns are 16-byte aligned;
 // TAB = `tab` holds the per-uuid entries (otherwise each window derives its entry from off / ts itself -- used when
 // there are far more uuids than windows).
-template <int ELEM, bool VEC, bool TAB, int G, int W>
+// REG = entries with a NEGATIVE slope field describe an exact arithmetic run, ts[k] = t_lo + k * cadence with cadence = -inv
+// (the sample ring establishes that while it appends, th_ring.cu): both range ends follow from two divisions and the ts
+// column is not touched at all.
+template <int ELEM, bool VEC, bool TAB, int G, int W, bool REG = false>
 __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
                                                               const UsSeg *__restrict__ tab, const i64 *__restrict__ ts,
                                                               const void *__restrict__ gpu_v, const void *__restrict__ mem_v,
@@ -256,7 +259,16 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
             } else {
                 e = us_make_seg(off, ts, u);
             }
-            if (e.n > 0) {
+            if (REG && e.inv < 0.0) {
+                const i64 c = (i64)(-e.inv);
+                a = ws <= e.t_lo ? 0 : (ws - e.t_lo + c - 1) / c;        // first k with t_lo + k c >= ws
+                b = we < e.t_lo ? 0 : (we - e.t_lo) / c + 1;              // one past the last k with t_lo + k c <= we
+                a = a < e.n ? a : e.n;
+                b = b < e.n ? b : e.n;
+                if (b < a) b = a;
+                a += e.lo;
+                b += e.lo;
+            } else if (e.n > 0) {
                 us_range<G, W>(ts + e.lo, e, ws, we, gl, gmask, a, b);
                 a += e.lo;
                 b += e.lo;
@@ -299,6 +311,44 @@ void us_launch(bool tab_mode, int grid, cudaStream_t st, i64 s, i64 n_uuids, con
 }
 
 }  // namespace
+
+// Reduction over a log whose per-uuid entries the caller has already built on the device (th_ring.cu): `tab` holds
+// n_uuids UsSeg-layout entries {lo, n, t_lo, inv or -cadence}; the sample columns are uint8, 16-byte aligned, with
+// `cap` addressable elements.  Window arrays and outputs follow `mem` as everywhere else.
+int th_usage_reduce_table_u8(int device, const void *tab, int64_t n_uuids, int64_t cap, const int64_t *ts_us,
+                             const uint8_t *gpu_u8, const uint8_t *mem_u8, int64_t w, const int64_t *win_uuid,
+                             const int64_t *win_start, const int64_t *win_end, int64_t *out_sum_gpu,
+                             int64_t *out_sum_mem, int64_t *out_count, int64_t *out_avg_gpu, int64_t *out_avg_mem,
+                             int mem, cudaStream_t st) {
+    if (w == 0) return TH_OK;
+    TH_REQUIRE(win_uuid && win_start && win_end, "th_ring_reduce: NULL window array");
+    ThScratch sc(st);
+    const size_t zw = (size_t)w;
+    const void *d_wu, *d_ws, *d_we;
+    void *d_sg, *d_sm, *d_c, *d_ag, *d_am;
+    TH_TRY(sc.in(win_uuid, 8 * zw, mem, &d_wu));
+    TH_TRY(sc.in(win_start, 8 * zw, mem, &d_ws));
+    TH_TRY(sc.in(win_end, 8 * zw, mem, &d_we));
+    TH_TRY(sc.out(out_sum_gpu, 8 * zw, mem, &d_sg));
+    TH_TRY(sc.out(out_sum_mem, 8 * zw, mem, &d_sm));
+    TH_TRY(sc.out(out_count, 8 * zw, mem, &d_c));
+    TH_TRY(sc.out(out_avg_gpu, 8 * zw, mem, &d_ag));
+    TH_TRY(sc.out(out_avg_mem, 8 * zw, mem, &d_am));
+    const int grid = th_grid_for(w, US_THREADS / 4, 64);
+    k4_usage_kernel<1, true, true, 4, 8, true><<<grid, US_THREADS, 0, st>>>(
+        (i64)cap, (i64)n_uuids, (const i64 *)nullptr, (const UsSeg *)tab, (const i64 *)ts_us, (const void *)gpu_u8,
+        (const void *)mem_u8, (i64)w, (const i64 *)d_wu, (const i64 *)d_ws,
+        (const i64 *)d_we, (i64 *)d_sg, (i64 *)d_sm, (i64 *)d_c, (i64 *)d_ag, (i64 *)d_am);
+    TH_CUDA(cudaGetLastError());
+    TH_TRY(th_copy_back(out_sum_gpu, d_sg, 8 * zw, mem, st));
+    TH_TRY(th_copy_back(out_sum_mem, d_sm, 8 * zw, mem, st));
+    TH_TRY(th_copy_back(out_count, d_c, 8 * zw, mem, st));
+    TH_TRY(th_copy_back(out_avg_gpu, d_ag, 8 * zw, mem, st));
+    TH_TRY(th_copy_back(out_avg_mem, d_am, 8 * zw, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    (void)device;
+    return TH_OK;
+}
 
 static int usage_reduce_impl(int elem, int device, int64_t s, int64_t n_uuids, const int64_t *uuid_offsets,
                              const int64_t *ts_us, const void *gpu_util, const void *mem_util, int64_t w,

@@ -181,19 +181,19 @@ class Reservation:
         if not uuids:
             return []
         k = len(uuids)
-        _off, ids, canc = cal.sets(uuids, [now] * k, [now] * k, MODE_INCLUSIVE)
+        _off, ids, canc, rows = cal.sets(uuids, [now] * k, [now] * k, MODE_INCLUSIVE)
         keep = np.asarray(ids)[np.asarray(canc) == 0]
         if resource_id is None:
             keep = np.sort(keep)        # one scan over the whole table returns rowid = ascending id order
-        return cal.rows_for(keep)
+        return [rows[int(i)] for i in keep]
 
     # -- Reservation.py:106-118 -------------------------------------------------------------------------------------
     @classmethod
     def upcoming_events_for_resource(cls, resource_id: str, period_after: timedelta) -> List['Reservation']:
         cal = _cal()
         now = cal.now_us()
-        _off, ids, _canc = cal.sets([resource_id], [now], [now + _period_us(period_after)], MODE_UPCOMING)
-        return cal.rows_for(ids)
+        _off, ids, _canc, rows = cal.sets([resource_id], [now], [now + _period_us(period_after)], MODE_UPCOMING)
+        return [rows[int(i)] for i in ids]
 
     # -- Reservation.py:132-148 ----------------------------------------------------------------------------------------
     @classmethod
@@ -206,8 +206,48 @@ class Reservation:
         if not uu:
             return []
         k = len(uu)
-        _off, ids, _canc = cal.sets(uu, [dt_to_us(start)] * k, [dt_to_us(end)] * k, MODE_INCLUSIVE)
-        return cal.rows_for(np.sort(np.asarray(ids)))
+        _off, ids, _canc, rows = cal.sets(uu, [dt_to_us(start)] * k, [dt_to_us(end)] * k, MODE_INCLUSIVE)
+        return [rows[int(i)] for i in np.sort(np.asarray(ids))]
+
+
+    # -- CRUDModel.py:21-50: the write path ----------------------------------------------------------------------------
+    def save(self):
+        """``check_assertions()`` (which runs would_interfere on the device), then commit: the row goes to the snapshot as
+        a one-row delta (``th_snapshot_apply_delta``), a new row first getting the id AUTOINCREMENT would give it.  The
+        check and the commit happen under the calendar's writer lock, so two racing saves cannot both pass the check.
+        AssertionError is logged and re-raised, as in the reference."""
+        cal = _cal()
+        with cal._writer:
+            try:
+                self.check_assertions()
+            except AssertionError as e:
+                log.error(e)
+                raise
+            if self.id is None:
+                self.id = cal.next_id()
+            if self.created_at is None:
+                self.created_at = cal.clock()
+            cal.apply_delta(upserts=[self])
+        log.debug('Saved {}'.format(self))
+        return self
+
+    def destroy(self):
+        if self.id is not None:
+            _cal().apply_delta(deleted_ids=[self.id])
+        log.debug('Deleted {}'.format(self))
+        return self
+
+    @classmethod
+    def get(cls, id):
+        """CRUDModel.get (:52-66): the row with this id or ``NoResultFound``."""
+        try:
+            return _cal().rows_for([id])[0]
+        except KeyError:
+            raise NoResultFound('There is no record {} with id={}!'.format(cls.__name__, id))
+
+
+class NoResultFound(Exception):
+    """Stands in for sqlalchemy.orm.exc.NoResultFound (what CRUDModel.get raises, CRUDModel.py:61-64)."""
 
 
 # =========================================================================================================
@@ -299,67 +339,173 @@ class UsageLog:
 
 
 class UsageRing:
-    """Append-only columnar sample store, one growing segment per GPU uuid: what the usage
-    logger writes instead of re-reading and re-writing one JSON file per reservation on every tick
+    """Append-only columnar sample store ON THE DEVICE, one growing region per GPU uuid: what
+    the usage logger writes instead of re-reading and re-writing one JSON file per reservation on every tick
     (UsageLoggingService.py:85-116).  A sample is kept under the rule of ``Log.updated_log`` (:92-99): only when BOTH
     gpu_util and mem_util are not None.  Timestamps must not decrease per uuid (the service appends ``utcnow()``).
-    Utilisation is stored as uint8 (percentages), timestamps as int64 microseconds; ``averages`` hands the columns to
-    K4's narrow path and returns what ``handle_expired_logs`` (:196-229) stores per reservation."""
+    Utilisation is stored as uint8 (percentages), timestamps as int64 microseconds.
+
+    ``append`` / ``append_tick`` cost one small host -> device copy and one scatter kernel whatever the log's length
+    (``th_ring_append``); ``averages`` runs K4's narrow path over the ring in place (``th_ring_reduce``) -- the log is
+    never concatenated, never re-uploaded -- and returns what ``handle_expired_logs`` (:196-229) stores per reservation."""
 
     def __init__(self, device: int = 0, initial_capacity: int = 1024):
+        import ctypes as C
+        from . import native
+        self._C, self._native = C, native
+        self._lib = native.load()
         self.device = int(device)
-        self._cap0 = max(int(initial_capacity), 1)
+        self._h = C.c_void_p(0)
+        native.check(self._lib.th_ring_create(self.device, int(initial_capacity), C.byref(self._h)))
         self._codes: Dict[str, int] = {}
-        self._ts: List[np.ndarray] = []
-        self._gpu: List[np.ndarray] = []
-        self._mem: List[np.ndarray] = []
-        self._len: List[int] = []
+
+    def close(self):
+        if self._h:
+            self._lib.th_ring_destroy(self._h)
+            self._h = self._C.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> dict:
+        C = self._C
+        v = [C.c_int64(0) for _ in range(6)]
+        self._native.check(self._lib.th_ring_info(self._h, *[C.byref(x) for x in v]))
+        keys = ('n_uuids', 'samples', 'capacity', 'device_bytes', 'regular_uuids', 'relayouts')
+        return {k: x.value for k, x in zip(keys, v)}
 
     def __len__(self):
-        return int(sum(self._len))
+        return self.info()['samples']
 
-    def append(self, resource_id: str, ts, gpu_util, mem_util) -> bool:
-        """One monitoring tick of one GPU; returns False (and stores nothing) when either metric is unsupported."""
-        if gpu_util is None or mem_util is None:
-            return False
+    def code(self, resource_id: str) -> int:
         k = self._codes.get(resource_id)
         if k is None:
-            k = self._codes[resource_id] = len(self._ts)
-            self._ts.append(np.empty(self._cap0, np.int64))
-            self._gpu.append(np.empty(self._cap0, np.uint8))
-            self._mem.append(np.empty(self._cap0, np.uint8))
-            self._len.append(0)
-        n = self._len[k]
-        t = dt_to_us(ts) if isinstance(ts, _dt.datetime) else int(ts)
-        assert n == 0 or t >= self._ts[k][n - 1], 'samples of one GPU must be appended in time order'
-        assert 0 <= int(gpu_util) <= 255 and 0 <= int(mem_util) <= 255, 'utilisation is a percentage'
-        if n == len(self._ts[k]):
-            for col in (self._ts, self._gpu, self._mem):
-                grown = np.empty(2 * n, col[k].dtype)
-                grown[:n] = col[k]
-                col[k] = grown
-        self._ts[k][n], self._gpu[k][n], self._mem[k][n] = t, int(gpu_util), int(mem_util)
-        self._len[k] = n + 1
-        return True
+            k = self._codes[resource_id] = len(self._codes)
+        return k
 
-    def columns(self):
-        """(uuid_codes, offsets[U + 1], ts, gpu_u8, mem_u8): the CSR layout K4 reads."""
-        off = np.zeros(len(self._len) + 1, np.int64)
-        off[1:] = np.cumsum(self._len)
-        cat = lambda cols, dt: (np.concatenate([c[:n] for c, n in zip(cols, self._len)]) if cols else np.zeros(0, dt))
-        return dict(self._codes), off, cat(self._ts, np.int64), cat(self._gpu, np.uint8), cat(self._mem, np.uint8)
+    def append_tick(self, samples) -> int:
+        """One monitoring tick: ``samples`` = iterable of ``(resource_id, ts, gpu_util, mem_util)``.  Entries with an
+        unsupported metric (None) are dropped; returns how many were stored.  One H2D copy + one kernel for the tick."""
+        uu, ts, g, m = [], [], [], []
+        for resource_id, t, gpu_util, mem_util in samples:
+            if gpu_util is None or mem_util is None:
+                continue
+            assert 0 <= int(gpu_util) <= 255 and 0 <= int(mem_util) <= 255, 'utilisation is a percentage'
+            uu.append(self.code(resource_id))
+            ts.append(dt_to_us(t) if isinstance(t, _dt.datetime) else int(t))
+            g.append(int(gpu_util))
+            m.append(int(mem_util))
+        if not uu:
+            return 0
+        a = [np.array(uu, np.int64), np.array(ts, np.int64), np.array(g, np.uint8), np.array(m, np.uint8)]
+        rc = self._lib.th_ring_append(self._h, len(uu), *[self._C.c_void_p(x.ctypes.data) for x in a], None)
+        if rc == -1 and 'backwards' in self._native.last_error():
+            raise AssertionError('samples of one GPU must be appended in time order')
+        self._native.check(rc)
+        return len(uu)
+
+    def append(self, resource_id: str, ts, gpu_util, mem_util) -> bool:
+        """One sample of one GPU; returns False (and stores nothing) when either metric is unsupported."""
+        return self.append_tick([(resource_id, ts, gpu_util, mem_util)]) == 1
+
+    def reduce(self, win_uuid, win_start, win_end):
+        """(sum_gpu, sum_mem, count, avg_gpu, avg_mem) per window: numpy arrays in / out, or CUDA tensors in / out."""
+        a = api._Args(win_uuid, win_start, win_end)
+        w = int(len(win_uuid))
+        outs = [a.out(w) for _ in range(5)]
+        self._native.check(self._lib.th_ring_reduce(self._h, w, a.inp(win_uuid), a.inp(win_start), a.inp(win_end),
+                                                    outs[0][1], outs[1][1], outs[2][1], outs[3][1], outs[4][1], a.mem,
+                                                    a.stream()))
+        return tuple(o[0] for o in outs)
 
     def averages(self, reservations: List[Reservation]):
         if not reservations:
             return []
-        codes, off, ts, gpu, mem = self.columns()
-        if len(off) == 1:
-            return [(float(-1), float(-1))] * len(reservations)
-        wu = np.array([codes.get(r.resource_id, -1) for r in reservations], np.int64)
+        wu = np.array([self._codes.get(r.resource_id, -1) for r in reservations], np.int64)
         ws = np.array([dt_to_us(r.start) for r in reservations], np.int64)
         we = np.array([dt_to_us(r.end) for r in reservations], np.int64)
-        _sg, _sm, cnt, ag, am = api.usage_reduce_u8(off, ts, gpu, mem, wu, ws, we, device=self.device)
+        _sg, _sm, cnt, ag, am = self.reduce(wu, ws, we)
         return [(float(-1), float(-1)) if cnt[j] == 0 else (int(ag[j]), int(am[j])) for j in range(len(reservations))]
+
+
+class UsageLoggingService:
+    """UsageLoggingService.do_run (tensorhive/core/services/UsageLoggingService.py:143-229) on the sample ring.
+
+    ``log_current_usage`` (:159-171): for every reservation in ``current_events()`` whose GPU the infrastructure
+    reports (``extract_specific_gpu_data`` :231-240 raises otherwise; the reference logs the error and goes on), the
+    tick's utilisation pair is stored -- once per GPU and tick in the ring, instead of once per reservation in a JSON
+    file that is re-read and re-written -- under the rule of ``Log.updated_log`` (:92-99: both metrics not None).
+    ``handle_expired_logs`` (:196-229): every reservation that has a log and has ended (``end < now``) gets
+    ``gpu_util_avg`` / ``mem_util_avg`` = ``avg`` of its samples (ONE K4 launch for all of them: the samples of its GPU
+    with ``start <= ts <= end``) and is saved; exceptions are logged, not raised, as there."""
+
+    def __init__(self, interval=0.0, infrastructure_manager=None, ring: 'UsageRing' = None):
+        self.interval = interval
+        self.infrastructure_manager = infrastructure_manager
+        self.ring = ring if ring is not None else UsageRing(device=_cal().device if _calendar is not None else 0)
+        self._open: Dict[int, object] = {}          # reservation id -> row, the analogue of "<id>.json exists"
+
+    @staticmethod
+    def extract_specific_gpu_data(uuid: str, infrastructure: Dict) -> Dict:
+        assert isinstance(infrastructure, dict)
+        assert isinstance(uuid, str) and len(uuid) == 40
+        for hostname in infrastructure.keys():
+            gpu_data = infrastructure[hostname].get('GPU').get(uuid)
+            if gpu_data:
+                return gpu_data
+        raise KeyError(uuid + ' has not been found!')
+
+    def log_current_usage(self):
+        cal = _cal()
+        now = cal.clock()
+        infrastructure = self.infrastructure_manager.infrastructure
+        seen = {}
+        for reservation in Reservation.current_events():
+            uuid = reservation.resource_id
+            if uuid not in seen:
+                try:
+                    gpu_data = self.extract_specific_gpu_data(uuid=uuid, infrastructure=infrastructure)
+                    self.ring.append(uuid, now, gpu_data['metrics']['utilization']['value'],
+                                     gpu_data['metrics']['mem_util']['value'])
+                    seen[uuid] = True
+                except Exception as e:                                   # noqa: BLE001 -- :170-171
+                    log.error(e)
+                    seen[uuid] = False
+            if seen[uuid]:
+                self._open[reservation.id] = reservation                 # "<id>.json" exists from now on (:108-110)
+
+    def handle_expired_logs(self):
+        time_now = _cal().clock()
+        expired = []
+        for rid in sorted(self._open):
+            try:
+                reservation = Reservation.get(id=rid)
+            except NoResultFound:
+                del self._open[rid]                                      # log of a vanished reservation: cleaned up (:224-226)
+                continue
+            if reservation.end < time_now:
+                expired.append(reservation)
+        if not expired:
+            return []
+        averages = self.ring.averages(expired)
+        saved = []
+        for reservation, (ag, am) in zip(expired, averages):
+            try:
+                reservation.gpu_util_avg = ag
+                reservation.mem_util_avg = am
+                reservation.save()
+                saved.append(reservation)
+                del self._open[reservation.id]                           # the log is cleaned up only after a save (:218-223)
+            except Exception as e:                                       # noqa: BLE001 -- :227-228
+                log.debug(e)
+        return saved
+
+    def do_run(self):
+        self.log_current_usage()
+        return self.handle_expired_logs()
 
 
 # =========================================================================================================
@@ -403,35 +549,35 @@ class ProtectionService:
     def collect_violations(self, current_infrastructure: Dict[str, Dict]) -> Dict[str, Dict[str, Dict]]:
         """{hostname: {intruder: violation_data}} exactly as the nested loops of do_run (:85-102) build it."""
         cal = _cal()
-        snap, uuids, by_id = cal.state()
         names = cal.usernames()
         unknown: Dict[object, int] = {}
-        # flatten in the reference's iteration order
-        where, pu, po = [], [], []
-        for hostname in current_infrastructure:
-            for gpu_id in current_infrastructure[hostname]:
-                processes = current_infrastructure[hostname][gpu_id]
-                if self.strict_reservations or (processes is not None and len(processes)):
-                    code = uuids.lookup(gpu_id)
-                    for process in processes:
-                        owner = process['owner']
-                        if owner in names and owner is not None:
-                            oid = names[owner]
-                        else:
-                            oid = unknown.setdefault(owner, -2 - len(unknown))
-                        where.append((hostname, gpu_id, process))
-                        pu.append(code)
-                        po.append(oid)
         result = {hostname: {} for hostname in current_infrastructure}
-        if not where:
-            return result
-        flags, res_ids = snap.violation_join(cal.now_us(), self.strict_reservations, np.array(pu, np.int64),
-                                             np.array(po, np.int64))
-        for k, (hostname, gpu_id, process) in enumerate(where):
-            if not flags[k] or hostname is None:
-                continue
-            reservation = by_id[int(res_ids[k])] if res_ids[k] >= 0 else None
-            self.store_violation(result[hostname], process, hostname, reservation, gpu_id)
+        with cal.reading() as (snap, uuids, by_id):       # table, dictionary and rows of ONE version
+            # flatten in the reference's iteration order
+            where, pu, po = [], [], []
+            for hostname in current_infrastructure:
+                for gpu_id in current_infrastructure[hostname]:
+                    processes = current_infrastructure[hostname][gpu_id]
+                    if self.strict_reservations or (processes is not None and len(processes)):
+                        code = uuids.lookup(gpu_id)
+                        for process in processes:
+                            owner = process['owner']
+                            if owner in names and owner is not None:
+                                oid = names[owner]
+                            else:
+                                oid = unknown.setdefault(owner, -2 - len(unknown))
+                            where.append((hostname, gpu_id, process))
+                            pu.append(code)
+                            po.append(oid)
+            if not where:
+                return result
+            flags, res_ids = snap.violation_join(cal.now_us(), self.strict_reservations, np.array(pu, np.int64),
+                                                 np.array(po, np.int64))
+            for k, (hostname, gpu_id, process) in enumerate(where):
+                if not flags[k] or hostname is None:
+                    continue
+                reservation = by_id[int(res_ids[k])] if res_ids[k] >= 0 else None
+                self.store_violation(result[hostname], process, hostname, reservation, gpu_id)
         return result
 
     def store_violation(self, storage, process, hostname, reservation, gpu_id):
@@ -522,7 +668,6 @@ class JobSchedulingService:
         """JobSchedulingService.py:76-104: minutes until the next reservation per GPU (0 = occupied now,
         None = nothing upcoming).  One th_upcoming launch for every GPU that is not running a task."""
         cal = _cal()
-        snap, uuids, _ = cal.state()
         ret: Dict[str, Dict] = {}
         ask = []
         for host in hosts_with_gpu_occupation:
@@ -539,8 +684,9 @@ class JobSchedulingService:
             return ret
         now_dt = cal.clock()
         now = dt_to_us(now_dt)
-        codes = np.array([uuids.lookup(g) for _h, g in ask], np.int64)
-        _fid, fstart, _fown, count = snap.upcoming(now, _period_us(self.considered_future_period), codes)
+        with cal.reading() as (snap, uuids, _):
+            codes = np.array([uuids.lookup(g) for _h, g in ask], np.int64)
+            _fid, fstart, _fown, count = snap.upcoming(now, _period_us(self.considered_future_period), codes)
         for k, (host, gpu_id) in enumerate(ask):
             if count[k] > 0:
                 start = us_to_dt(int(fstart[k]))
@@ -561,19 +707,19 @@ class JobSchedulingService:
                                           allow_own: bool = True) -> List[bool]:
         """JobSchedulingService.py:117-132 for a whole job list in one launch."""
         cal = _cal()
-        snap, uuids, _ = cal.state()
-        tu, to, tj = [], [], []
-        for j, job in enumerate(jobs):
-            for task in job.tasks:
-                gpu_id = Scheduler.get_assigned_gpu_uid(task, hosts)
-                tu.append(uuids.lookup(gpu_id))
-                to.append(_owner_id(job.user))
-                tj.append(j)
         out = [False] * len(jobs)
-        if not tu:
-            return out
-        flags = snap.upcoming_owner_flags(cal.now_us(), _period_us(considered_future_period), np.array(tu, np.int64),
-                                          np.array(to, np.int64), OWNER_OTHER if allow_own else OWNER_ANY)
+        with cal.reading() as (snap, uuids, _):
+            tu, to, tj = [], [], []
+            for j, job in enumerate(jobs):
+                for task in job.tasks:
+                    gpu_id = Scheduler.get_assigned_gpu_uid(task, hosts)
+                    tu.append(uuids.lookup(gpu_id))
+                    to.append(_owner_id(job.user))
+                    tj.append(j)
+            if not tu:
+                return out
+            flags = snap.upcoming_owner_flags(cal.now_us(), _period_us(considered_future_period), np.array(tu, np.int64),
+                                              np.array(to, np.int64), OWNER_OTHER if allow_own else OWNER_ANY)
         for k, j in enumerate(tj):
             if flags[k]:
                 out[j] = True
@@ -585,19 +731,19 @@ class GreedyScheduler(Scheduler):
         """scheduling.py:29-62.  The per-task "does the job's owner have an upcoming reservation here" test is
         one batched K5 launch; the taken-hosts pass is sequential by definition and stays on the host."""
         cal = _cal()
-        snap, uuids, _ = cal.state()
         jobs = list(jobs_to_hardware)
         tu, to, index = [], [], {}
-        for j, job in enumerate(jobs):
-            for t, task in enumerate(job.tasks):
-                uid = Scheduler.get_assigned_gpu_uid(task, hardware_to_slots)
-                index[(j, t)] = len(tu)
-                tu.append(uuids.lookup(uid))
-                to.append(_owner_id(job.user))
         own = np.zeros(0, np.uint8)
-        if tu:
-            own = snap.upcoming_owner_flags(cal.now_us(), SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS * 60 * 1_000_000,
-                                            np.array(tu, np.int64), np.array(to, np.int64), OWNER_SAME)
+        with cal.reading() as (snap, uuids, _):
+            for j, job in enumerate(jobs):
+                for t, task in enumerate(job.tasks):
+                    uid = Scheduler.get_assigned_gpu_uid(task, hardware_to_slots)
+                    index[(j, t)] = len(tu)
+                    tu.append(uuids.lookup(uid))
+                    to.append(_owner_id(job.user))
+            if tu:
+                own = snap.upcoming_owner_flags(cal.now_us(), SCHEDULE_QUEUED_JOBS_WHEN_FREE_MINS * 60 * 1_000_000,
+                                                np.array(tu, np.int64), np.array(to, np.int64), OWNER_SAME)
         scheduled_jobs, taken_hosts = [], []
         for j, job in enumerate(jobs):
             scheduled_tasks = 0

@@ -24,6 +24,7 @@ _i64, _int = C.c_int64, C.c_int
 SIGNATURES = {
     'th_version': (_int, []),
     'th_last_error': (C.c_char_p, []),
+    'th_pool_stats': (_int, [_int, _i64p, _i64p, _i64p, _int]),
     'th_snapshot_create': (_int, [_int, C.POINTER(_vp)]),
     'th_snapshot_destroy': (_int, [_vp]),
     'th_snapshot_load': (_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
@@ -49,6 +50,11 @@ SIGNATURES = {
     'th_peer_barrier': (_int, [_vp, _vp]),
     'th_usage_reduce_u8': (_int, [_int, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _int, _vp]),
+    'th_ring_create': (_int, [_int, _i64, C.POINTER(_vp)]),
+    'th_ring_destroy': (_int, [_vp]),
+    'th_ring_append': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    'th_ring_reduce': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
+    'th_ring_info': (_int, [_vp, _i64p, _i64p, _i64p, _i64p, _i64p, _i64p]),
     'th_sort_pairs': (_int, [_int, _i64, _vp, _vp, _vp, _int, _vp]),
     'th_synth_samples': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp]),
     'th_synth_windows': (_int, [_int, _i64, _i64, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp]),

@@ -313,7 +313,7 @@ def run_world(ref, w):
 def make_usage_world(seed, n_gpus=3, ticks=90):
     rng = np.random.default_rng(3000 + seed)
     t0 = synth.T0_US + seed * synth.DAY_US
-    tick_us = 60_000_000
+    tick_us = 600_000_000                 # 10 min: every reservation lasts >= 30 min (Reservation.py:39)
     uuids = [synth.uuid_string(100 + g) for g in range(n_gpus)] + [synth.uuid_string(900)]     # the last one never reports
     rows, rid = [], 1
     for g, uuid in enumerate(uuids):
@@ -333,7 +333,7 @@ def make_usage_world(seed, n_gpus=3, ticks=90):
         r[0] = k + 1                                                                                # ids in shuffled order
     tick_list = []
     for k in range(ticks):
-        now = t0 + k * tick_us + int(rng.integers(0, 2_000_000))
+        now = t0 + k * tick_us + int(rng.integers(0, 20_000_000))
         gpus = {}
         for g, uuid in enumerate(uuids[:-1]):
             if rng.random() < 0.04:
@@ -365,6 +365,8 @@ def run_usage_world(ref, w):
 
 
 def main():
+    import logging
+    logging.disable(logging.CRITICAL)      # the reference logs every GPU it cannot find (UsageLoggingService.py:171)
     os.environ['TZ'] = 'UTC'            # utc2local (core/utils/time.py:5-9) reads the process time zone
     time.tzset()
     ref = load_reference()

@@ -158,3 +158,53 @@ def test_calendar_apply_delta_through_the_dropin(lib_built):
         cal.apply_delta(upserts=[mk(1, gpu, 0, 60, None)])
     assert cand.would_interfere() is True
     cal.close()
+
+
+def test_duplicate_ids_are_refused_and_leave_the_snapshot_as_it_was(lib_built):
+    """The primary key is unique: a load or a delta that breaks that is refused (TH_EINVAL) BEFORE the handle is touched,
+    so the previous snapshot stays queryable; Calendar.apply_delta collapses a batch first (last change wins)."""
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from tensorhive_fixed_b200.calendar import Calendar
+    cal = synth.make_calendar(5000, 8, seed=11)
+    table = {k: cal[k].copy() for k in COLS}
+    snap = _fresh(th, table, 8)
+    before = snap.export()
+    two = {k: np.concatenate([table[k][:1], table[k][:1]]) for k in COLS}
+    two['end'][1] += 5
+    with pytest.raises(th.NativeError) as e:                       # one id upserted twice
+        snap.apply_delta(snap, 8, *[two[k] for k in COLS], np.zeros(0, np.int64))
+    assert e.value.code == -1 and 'more than once' in str(e.value)
+    with pytest.raises(th.NativeError):                            # one id upserted and deleted
+        snap.apply_delta(snap, 8, *[table[k][:1] for k in COLS], table['id'][:1].copy())
+    bad = {k: table[k].copy() for k in COLS}
+    bad['id'][7] = bad['id'][4000]                                  # duplicate id in a full load (ids not ascending)
+    with pytest.raises(th.NativeError) as e:
+        snap.load(*[bad[k] for k in COLS], n_uuids=8)
+    assert 'not unique' in str(e.value)
+    bad = {k: table[k].copy() for k in COLS}
+    bad['uuid_id'][3] = 8                                           # uuid code out of range
+    with pytest.raises(th.NativeError):
+        snap.load(*[bad[k] for k in COLS], n_uuids=8)
+    after = snap.export()                                           # every refusal left the old table in place
+    assert all(np.array_equal(before[k], after[k]) for k in before)
+    q = synth.make_queries(cal, 2000, seed=12)
+    from oracle import brute
+    assert np.array_equal(snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id']),
+                          brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id']))
+    # a negative id in the delete list matches nothing
+    snap.apply_delta(snap, 8, *[table[k][:0] for k in COLS], np.array([-5], np.int64))
+    assert all(np.array_equal(before[k], snap.export()[k]) for k in before)
+    snap.close()
+
+    # the calendar collapses a batch: update + cancel of the same reservation -> the cancel; changed + destroyed -> gone
+    rows = [{'id': 1, 'user_id': 1, 'resource_id': 'G' * 40, 'start': 0, 'end': 100, 'is_cancelled': None},
+            {'id': 2, 'user_id': 1, 'resource_id': 'G' * 40, 'start': 200, 'end': 300, 'is_cancelled': None}]
+    c = Calendar(rows)
+    c.apply_delta(upserts=[dict(rows[0], end=150), dict(rows[0], end=150, is_cancelled=True), dict(rows[1], end=400)],
+                  deleted_ids=[2])
+    ex = c.state()[0].export()
+    assert ex['id'].tolist() == [1] and ex['end'].tolist() == [150] and ex['cancelled'].tolist() == [1]
+    with pytest.raises(ValueError):
+        c.apply_delta(upserts=[dict(rows[0], id=-3)])
+    c.close()

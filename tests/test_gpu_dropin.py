@@ -275,6 +275,7 @@ def test_usage_ring_follows_the_logger_rules(dropin):
                                   start=t0, end=t0 + timedelta(hours=1)))              # a GPU that never reports
     ring = dropin.UsageRing(initial_capacity=4)                                        # forces the buffers to grow
     lists = {r.id: ([], []) for r in res}
+    dropped = 0
     for tick in range(0, 900 * 60, 47):                                                # one sample every 47 s
         now = t0 + timedelta(seconds=tick, microseconds=int(rng.integers(0, 1000)))
         for g in gpus:
@@ -282,6 +283,7 @@ def test_usage_ring_follows_the_logger_rules(dropin):
             mu = None if rng.random() < 0.05 else int(rng.integers(0, 101))
             kept = ring.append(g, now, gu, mu)
             assert kept == (gu is not None and mu is not None)
+            dropped += 0 if kept else 1
             if kept:
                 for r in res:                                                          # the reference's per-reservation log
                     if r.resource_id == g and r.start <= now <= r.end:
@@ -292,7 +294,9 @@ def test_usage_ring_follows_the_logger_rules(dropin):
         want = (ref.avg(lists[r.id][0]), ref.avg(lists[r.id][1]))
         assert (ag, am) == want and type(ag) is type(want[0]), r.id
     assert got[-1] == (-1.0, -1.0) and any(a >= 0 for a, _ in got)
-    assert len(ring) == sum(len(c) for c in ring.columns()[2:3])
+    info = ring.info()
+    assert len(ring) == info['samples'] == sum(1 for _ in range(0, 900 * 60, 47)) * 3 - dropped
+    assert info['n_uuids'] == 3 and info['relayouts'] >= 5 and info['regular_uuids'] == 0      # jittered stamps: probed
     assert dropin.UsageRing().averages(res[:2]) == [(-1.0, -1.0)] * 2
     with pytest.raises(AssertionError):
         ring.append(gpus[0], t0, 1, 1)                                                 # time must not run backwards
@@ -354,3 +358,101 @@ def test_bulk_column_load_on_the_device(dropin):
     got = dropin.Reservation.filter_by_uuids_and_time_range([probe.resource_id], probe.start, probe.end)
     assert probe.id in [r.id for r in got] and all(r.resource_id == probe.resource_id for r in got)
     a.close(); b.close()
+
+
+def test_save_move_save_and_destroy(dropin):
+    """The reference's own sequence (tests/unit/models/test_reservation_model.py:10-64) through save(): a colliding
+    candidate raises on save; against a cancelled base it saves, gets the next id, and can then be moved over its own old
+    slot (self-exclusion by id); destroy() removes it.  CRUDModel.py:21-50."""
+    base = dropin.Reservation(id=1, user_id=1, title='TEST TITLE', description='TEST_DESCRIPTION', resource_id=GPU,
+                              start=NOW, end=NOW + timedelta(minutes=60))
+    cal, _ = _calendar(dropin, [])
+    cal.refresh([base])
+    mk = lambda s, e: dropin.Reservation(user_id=3, title='TEST TITLE', description='TEST_DESCRIPTION', resource_id=GPU,
+                                         start=NOW + timedelta(minutes=s), end=NOW + timedelta(minutes=e))
+    shapes = [(5, 55), (-5, 55), (5, 65), (-5, 65)]
+    for s, e in shapes:                                              # :10-37 every shape collides with the live row
+        with pytest.raises(AssertionError):
+            mk(s, e).save()
+    assert [r.id for r in dropin.Reservation.current_events(GPU)] == [1]
+    base.is_cancelled = True
+    base.save()                                                      # the cancel itself is a save of row 1
+    assert dropin.Reservation.current_events(GPU) == []
+    cand = mk(*shapes[0])
+    cand.save()                                                      # :40-64 against the cancelled base: no collision
+    assert cand.id == 2 and dropin.Reservation.get(2) is cand
+    for s, e in shapes[1:]:
+        cand.start, cand.end = NOW + timedelta(minutes=s), NOW + timedelta(minutes=e)
+        cand.save()                                                  # overlaps only its own previous slot
+        assert cand.id == 2
+    other = mk(30, 90)
+    with pytest.raises(AssertionError):
+        other.save()                                                 # but another user's row now collides with it
+    assert other.id is None
+    cand.destroy()
+    with pytest.raises(dropin.NoResultFound):
+        dropin.Reservation.get(2)
+    other.save()
+    assert other.id == 3                                             # AUTOINCREMENT never reuses an id
+    assert [r.id for r in dropin.Reservation.filter_by_uuids_and_time_range([GPU], NOW, NOW + timedelta(hours=2))] == [1, 3]
+    cal.close()
+
+
+def test_usage_ring_stays_on_the_device_and_knows_regular_runs(dropin):
+    """The device-resident ring (th_ring_*): a tick costs one small copy whatever the log's length; uuids whose stamps
+    form an exact arithmetic run are reduced without reading the ts column, and a single off-grid stamp turns a uuid back
+    into a probed one -- all with the answers of th_usage_reduce_u8 over the same samples."""
+    import time as _time
+    import tensorhive_fixed_b200 as th
+    from oracle import brute
+    cal, _ = _calendar(dropin, [])
+    rng = np.random.default_rng(21)
+    n_gpus, ticks = 40, 3000
+    names = ['GPU-%036d' % k for k in range(n_gpus)]
+    ring = dropin.UsageRing(initial_capacity=16)
+    t0 = 1_800_000_000_000_000
+    ts_all = np.zeros((n_gpus, ticks), np.int64)
+    g_all = rng.integers(0, 101, size=(n_gpus, ticks)).astype(np.uint8)
+    m_all = rng.integers(0, 101, size=(n_gpus, ticks)).astype(np.uint8)
+    per_tick = []
+    for k in range(ticks):
+        stamp = t0 + k * 1_000_000
+        batch = []
+        for u in range(n_gpus):
+            t = stamp + (int(rng.integers(0, 900_000)) if u >= 30 else 0)       # GPUs 30.. are stamped off the grid
+            if u == 7 and k == 2000:
+                t += 1                                                             # one late stamp breaks GPU 7's run
+            ts_all[u, k] = t
+            batch.append((names[u], t, int(g_all[u, k]), int(m_all[u, k])))
+        a = _time.perf_counter()
+        assert ring.append_tick(batch) == n_gpus
+        per_tick.append(_time.perf_counter() - a)
+    info = ring.info()
+    assert info['samples'] == n_gpus * ticks and info['n_uuids'] == n_gpus
+    assert info['regular_uuids'] == 29                                             # 0..29 on the grid, minus GPU 7
+    # the cost of a tick does not grow with the log (regions double: a handful of re-layouts in 3000 ticks)
+    early, late = np.median(per_tick[200:700]), np.median(per_tick[-500:])
+    assert late < 3 * early + 2e-4, (early, late)
+    assert info['relayouts'] <= 12
+    w = 4000
+    wu = rng.integers(-1, n_gpus + 2, size=w).astype(np.int64)
+    ws = t0 + rng.integers(-50, ticks, size=w).astype(np.int64) * 1_000_000 + rng.integers(0, 2, size=w) * rng.integers(0, 10**6, size=w)
+    we = ws + rng.integers(0, 400, size=w).astype(np.int64) * 1_000_000 + rng.integers(0, 2, size=w) * rng.integers(0, 10**6, size=w)
+    we[::50] = ws[::50] - 5                                                        # end before start: empty
+    got = ring.reduce(wu, ws, we)
+    # the same samples as plain CSR columns through the existing entry point, and through the oracle
+    off = np.arange(n_gpus + 1, dtype=np.int64) * ticks
+    code = np.array([ring.code(n) for n in names])
+    assert np.array_equal(code, np.arange(n_gpus))
+    want = th.usage_reduce_u8(off, ts_all.reshape(-1), g_all.reshape(-1), m_all.reshape(-1), wu, ws, we)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    sg, sm, cnt = brute.usage_reduce(off, ts_all.reshape(-1), g_all.reshape(-1).astype(np.int64),
+                                     m_all.reshape(-1).astype(np.int64), wu[:600], ws[:600], we[:600])
+    assert np.array_equal(got[0][:600], sg) and np.array_equal(got[1][:600], sm) and np.array_equal(got[2][:600], cnt)
+    # CUDA tensors in, CUDA tensors out: nothing but the windows moves
+    import torch
+    dgot = ring.reduce(*[torch.from_numpy(x).cuda() for x in (wu, ws, we)])
+    assert all(np.array_equal(a.cpu().numpy(), b) for a, b in zip(dgot, got))
+    ring.close()
+    cal.close()

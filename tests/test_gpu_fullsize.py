@@ -99,3 +99,58 @@ def test_config5_one_rank_share(lib_built):
     has_live &= np.diff(np.asarray(off)) > 0
     assert np.array_equal(has_live, got[some])
     snap.close()
+
+
+def test_config4_full_size_service_sweep(lib_built):
+    """BASELINE configs[3] at full size: 1 M live GPU processes and 100 k queued jobs (~250 k tasks) against the 1 M-row
+    calendar.  The violation join is checked for EVERY process (the oracle's per-uuid owner table is vectorised); the
+    job-task flags against the brute-force row lists on a sampled uuid set plus whole-batch identities.
+    Reference: ProtectionService.py:84-102, JobSchedulingService.py:117-132, scheduling.py:48-53."""
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    n, u = 1_000_000, 4096
+    cal = synth.make_calendar(n, u, seed=20260102)
+    now = int(np.median(cal['start']))
+    period = 30 * synth.MIN_US
+    procs = synth.make_processes(cal, 1_000_000, now, seed=20260108)
+    tasks = synth.make_job_tasks(cal, 100_000, seed=20260109)
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=u)
+    want_res, want_own = brute.current_owner(cal, u, now)
+    pu, po = procs['uuid_id'], procs['owner']
+    r, o = want_res[pu], want_own[pu]
+    for strict in (False, True):
+        flags, res = snap.violation_join(now, strict, pu, po)
+        viol = (r >= 0) & (o >= 0) & (po != o)
+        want_flag = viol | ((r < 0) if strict else False)
+        assert np.array_equal(np.asarray(flags) != 0, want_flag), strict
+        assert np.array_equal(np.asarray(res), np.where(viol, r, -1)), strict
+    assert 0.05 < (np.asarray(flags) != 0).mean() < 0.95
+    tu, to = tasks['uuid_id'], tasks['owner']
+    assert len(tu) > 200_000
+    any_f = np.asarray(snap.upcoming_owner_flags(now, period, tu, to, th.OWNER_ANY)) != 0
+    oth_f = np.asarray(snap.upcoming_owner_flags(now, period, tu, to, th.OWNER_OTHER)) != 0
+    same_f = np.asarray(snap.upcoming_owner_flags(now, period, tu, to, th.OWNER_SAME)) != 0
+    assert np.array_equal(any_f, oth_f | same_f)                       # every upcoming row is the owner's or somebody else's
+    _fid, _fs, _fo, count = snap.upcoming(now, period, np.arange(u, dtype=np.int64))
+    has_up = np.asarray(count) > 0
+    assert np.array_equal(any_f, np.where(tu >= 0, has_up[np.clip(tu, 0, u - 1)], False))
+    assert not any_f[tu < 0].any()                                     # tasks without an assigned GPU never interfere
+    # sampled uuids: the row lists of upcoming_events_for_resource from the brute-force oracle, task by task
+    pick = np.random.default_rng(5).choice(u, size=96, replace=False)
+    sets = brute.conflict_sets(cal, pick, np.full(96, now, np.int64), np.full(96, now + period, np.int64),
+                               np.full(96, -1, np.int64), brute.UPCOMING)
+    owner_of = dict(zip(cal['id'].tolist(), cal['owner'].tolist()))
+    owners = {int(g): [owner_of[i] for i in ids] for g, ids in zip(pick, sets)}
+    sel = np.nonzero(np.isin(tu, pick))[0]
+    assert sel.size > 3000
+    for k in sel:
+        ow = owners[int(tu[k])]
+        assert any_f[k] == (len(ow) > 0)
+        assert oth_f[k] == any(x != to[k] for x in ow)
+        assert same_f[k] == any(x == to[k] for x in ow)
+    fid, fs, fo, cnt = (np.asarray(a) for a in snap.upcoming(now, period, pick))
+    wid, wst, wow, wc = brute.upcoming_summary(cal, pick, now, period)
+    assert np.array_equal(fid, wid) and np.array_equal(fs, wst) and np.array_equal(fo, wow) and np.array_equal(cnt, wc)
+    snap.close()

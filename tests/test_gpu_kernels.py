@@ -114,10 +114,11 @@ def test_conflict_bitmap_matches_brute_force(th, synth, brute, n, u, m, skew):
 
 
 def test_config1_against_the_sql_oracle(th, synth):
-    """BASELINE config 1 (10k reservations, 64 uuids) through the reference's SQL, sampled queries."""
+    """BASELINE config 1 (10k reservations, 64 uuids, 10k candidates) through the reference's SQL IN FULL:
+    every candidate's verdict and row list against the WHERE clause of Reservation.py:121-129 run by sqlite3."""
     from oracle.sql_ref import SqlCalendar
     cal = synth.make_calendar(10_000, 64, seed=20260101)
-    q = synth.make_queries(cal, 2000, seed=20260102)
+    q = synth.make_queries(cal, 10_000, seed=20260102)
     rows = [(int(cal['id'][i]), synth.uuid_string(int(cal['uuid_id'][i])), int(cal['start'][i]), int(cal['end'][i]),
              int(cal['owner'][i]), None if cal['cancelled_raw'][i] < 0 else int(cal['cancelled_raw'][i]))
             for i in range(10_000)]
@@ -126,7 +127,7 @@ def test_config1_against_the_sql_oracle(th, synth):
     got = snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id'])
     off, ids, canc = snap.conflict_sets(q['uuid_id'], q['start'], q['end'], q['self_id'], th.MODE_STRICT)
     lists = csr_to_lists(off, ids)
-    for i in range(2000):
+    for i in range(10_000):
         sid = None if q['self_id'][i] < 0 else int(q['self_id'][i])
         r = sql.would_interfere_rows(synth.uuid_string(int(q['uuid_id'][i])), int(q['start'][i]), int(q['end'][i]), sid)
         assert bool(got[i]) == any(not c for _, c in r), i

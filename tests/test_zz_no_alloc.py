@@ -42,12 +42,32 @@ def test_static_join_matches_the_allocating_join_on_two_calls_in_a_row(lib_built
         pu[::97] = 512 + 5            # processes on GPUs the calendar has never seen
         calls.append((now, strict, p, pu, po, torch.full((p,), 7, dtype=torch.uint8, device=dev),
                       torch.full((p,), -99, dtype=torch.int64, device=dev)))
+    # First use on this device: the library looks up the array's address and the driver loads the two kernels' code
+    # (lazily, on first launch) -- set-up that a caller does once, before it enters its no-allocation regime.
+    now, strict, p, pu, po, flags, res = calls[0]
+    rc = lib.th_violation_join_static(snap._h, now, 0, 1, pu.data_ptr(), po.data_ptr(), flags.data_ptr(), res.data_ptr(),
+                                      stream)
+    assert rc == 0, native.last_error()
+    flags.fill_(7); res.fill_(-99)
     torch.cuda.synchronize()
+    # The property in the name: nothing is allocated while the two calls run.  Watched from three sides -- the driver's
+    # free-memory figure, the library's own staging pool (high-water mark reset just before) and torch's allocator.
+    reserved0, used0, high = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    native.check(lib.th_pool_stats(0, C.byref(reserved0), C.byref(used0), C.byref(high), 1))
+    free0, _total = torch.cuda.mem_get_info(dev)
+    torch_allocs0 = torch.cuda.memory_stats(dev).get('allocation.all.allocated', 0)
     for now, strict, p, pu, po, flags, res in calls:      # two calls in a row, same built-in table
         rc = lib.th_violation_join_static(snap._h, now, 1 if strict else 0, p, pu.data_ptr(), po.data_ptr(),
                                           flags.data_ptr(), res.data_ptr(), stream)
         assert rc == 0, native.last_error()
     torch.cuda.synchronize()
+    reserved1, used1 = C.c_int64(0), C.c_int64(0)
+    native.check(lib.th_pool_stats(0, C.byref(reserved1), C.byref(used1), C.byref(high), 0))
+    free1, _total = torch.cuda.mem_get_info(dev)
+    assert free1 == free0, 'device free memory changed by %d bytes across the two static calls' % (free0 - free1)
+    assert reserved1.value == reserved0.value and used1.value == used0.value
+    assert high.value == used0.value, 'the staging pool served %d bytes during the static calls' % high.value
+    assert torch.cuda.memory_stats(dev).get('allocation.all.allocated', 0) == torch_allocs0
     seen = []
     for now, strict, p, pu, po, flags, res in calls:
         want_flags, want_res = snap.violation_join(now, strict, pu, po)       # the existing entry point

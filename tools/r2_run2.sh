@@ -2,6 +2,7 @@
 cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
 V=tensorhive-fixed_b200/lib/variants
+timeout 900 python -m pytest tests/test_gpu_exec_vectors.py tests/test_gpu_dropin.py tests/test_gpu_delta.py -x -q > gpurun_out/r2_pytest2.log 2>&1; tail -5 gpurun_out/r2_pytest2.log
 for name in base pipe min5 pipe5 pipe3; do
   if [ $name = base ]; then unset TH_B200_LIB; else export TH_B200_LIB=$PWD/$V/libth_b200_$name.so; fi
   echo "== $name" >> gpurun_out/r2_variants.log
