@@ -100,7 +100,8 @@ test_protection_service = G.test_protection_service_violations_match_the_referen
 test_job_scheduling = G.test_job_scheduling_checks_match_the_reference_loops
 test_bulk_revalidation = G.test_bulk_revalidation_batches_would_interfere
 test_usage_log = G.test_usage_log_averages
-test_usage_ring = G.test_usage_ring_follows_the_logger_rules
+test_save_destroy = G.test_save_move_save_and_destroy
+# (the sample ring lives on the device: its tests are GPU tests)
 test_calendar_view = G.test_calendar_view_controller
 
 
