@@ -116,6 +116,14 @@ int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t *q_uuid, c
                        const int64_t *q_end, const int64_t *q_self_id, int mode, uint32_t *out_bits_u32, int mem,
                        void *stream);
 
+/* th_conflict_bitmap over a narrower wire format (same reference method, Reservation.py:120-130): the host path is bound
+ * by the bytes that cross PCIe, so uuid codes and self ids travel as uint32 columns.  q_self_id_u32[i] = 0xFFFFFFFF means
+ * "not saved yet"; the column may be NULL when no candidate is a self-update (20 bytes per query, else 24, against 32).
+ * Reservation ids must be below 2^32 - 1.  Bitmaps are identical to th_conflict_bitmap's. */
+int th_conflict_bitmap_packed(const th_snapshot *h, int64_t m, const uint32_t *q_uuid_u32, const int64_t *q_start,
+                              const int64_t *q_end, const uint32_t *q_self_id_u32, int mode, uint32_t *out_bits_u32,
+                              int mem, void *stream);
+
 /* The row lists behind the verdicts, CSR: out_offsets[m + 1], then ids and their cancelled flags.
  *   TH_MODE_STRICT     rows of Reservation.py:121-129 `.all()`  (cancelled rows INCLUDED, ascending id)
  *   TH_MODE_INCLUSIVE  rows of filter_by_uuids_and_time_range :148 / current_events :102 before its

@@ -165,6 +165,30 @@ class Snapshot:
                                                   a.inp(q_self), int(mode), wp, a.mem, a.stream()))
         return words
 
+    def conflict_words_packed(self, q_uuid_u32, q_start, q_end, q_self_u32=None, mode: int = MODE_STRICT):
+        """``conflict_words`` from the narrow wire format: uuid codes and self ids as uint32 (0xFFFFFFFF = no self id,
+        ``q_self_u32=None`` = no candidate is a self-update): 20-24 bytes per query cross PCIe instead of 32."""
+        a = _Args(q_uuid_u32, q_start, q_end, q_self_u32)
+        m = int(len(q_uuid_u32))
+        words, wp = a.out((m + 31) // 32, np.uint32)
+        native.check(self._lib.th_conflict_bitmap_packed(self._h, m, a.inp(q_uuid_u32, np.uint32), a.inp(q_start),
+                                                         a.inp(q_end), a.inp(q_self_u32, np.uint32), int(mode), wp, a.mem,
+                                                         a.stream()))
+        return words
+
+    @staticmethod
+    def pack_queries(q_uuid, q_self=None):
+        """int64 uuid codes / self ids (-1 = none) -> the uint32 columns of the packed format.  Codes outside
+        [0, 2^32 - 2] (unknown resources) become 0xFFFFFFFE, which no snapshot has; ids must be below 2^32 - 1."""
+        u = np.asarray(q_uuid, np.int64)
+        pu = np.where((u < 0) | (u > 0xfffffffe), 0xfffffffe, u).astype(np.uint32)
+        if q_self is None:
+            return pu, None
+        f = np.asarray(q_self, np.int64)
+        if f.size and int(f.max()) >= 0xffffffff:
+            raise ValueError('the packed format carries ids below 2^32 - 1')
+        return pu, np.where(f < 0, 0xffffffff, f).astype(np.uint32)
+
     def conflict_bitmap(self, q_uuid, q_start, q_end, q_self=None, mode: int = MODE_STRICT) -> np.ndarray:
         """bool[m]: the value ``Reservation.would_interfere`` returns for each candidate."""
         return unpack_bits(self.conflict_words(q_uuid, q_start, q_end, q_self, mode), int(len(q_uuid)))

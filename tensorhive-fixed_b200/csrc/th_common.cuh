@@ -142,10 +142,32 @@ static inline u32 *th_peer_misc(void *base, int world, i64 wpr) { return (u32 *)
 static inline u32 *th_peer_bflags(void *base, int world, i64 wpr) { return th_peer_misc(base, world, wpr) + 8; }
 static inline u32 *th_peer_out(const th_peer *p, int parity) { return p->out + (size_t)parity * p->world * p->words_per_rank; }
 
+// L2 sector-promotion hint for scattered probes.  Measured on B200 (tools/micro/probe_gran.cu, ncu dram__bytes_read): ONE
+// scattered 16- or 32-byte read costs ~110 bytes of DRAM traffic with every plain flavour of ld.global (.nc, .cg, .cv,
+// L1::no_allocate, cp.async; cudaLimitMaxL2FetchGranularity 32 / 64 / 128 makes no difference) -- the L2 fills the whole
+// 128-byte line -- and 59 bytes with the .L2::64B qualifier (SASS LDG.E.LTC64B).  Every index probe of this library
+// carries it: at config-5 size the interval search is bound by exactly those bytes.
+#ifndef TH_L2H
+#define TH_L2H ".L2::64B"
+#endif
+
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ longlong2 th_ld16(const void *p) {
     // read-only 128-bit load; the index entries are immutable while a snapshot is live
-    return __ldg(reinterpret_cast<const longlong2 *>(p));
+    longlong2 v;
+    asm volatile("ld.global.nc" TH_L2H ".v2.s64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    return v;
+}
+// read-only 64-bit probe with the same hint
+__device__ __forceinline__ i64 th_ld8(const i64 *p) {
+    i64 v;
+    asm volatile("ld.global.nc" TH_L2H ".s64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint4 th_ld16u(const void *p) {
+    uint4 v;
+    asm volatile("ld.global.nc" TH_L2H ".v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
 }
 // streaming 64-bit load (read once, do not keep in L1)
 __device__ __forceinline__ i64 th_ld_stream(const i64 *p) {
@@ -163,7 +185,7 @@ __device__ __forceinline__ longlong2 th_ld16_if(const void *p, bool pred, longlo
         "{\n"
         ".reg .pred p;\n"
         "setp.ne.s32 p, %2, 0;\n"
-        "@p ld.global.nc.v2.s64 {%0, %1}, [%3];\n"
+        "@p ld.global.nc" TH_L2H ".v2.s64 {%0, %1}, [%3];\n"
         "}\n"
         : "+l"(v.x), "+l"(v.y)
         : "r"((int)pred), "l"(p));
@@ -188,7 +210,7 @@ __device__ __forceinline__ longlong2 th_ld16_if_off(const void *base, bool pred,
         "{\n"
         ".reg .pred p;\n"
         "setp.ne.s32 p, %2, 0;\n"
-        "@p ld.global.nc.v2.s64 {%0, %1}, [%3+%4];\n"
+        "@p ld.global.nc" TH_L2H ".v2.s64 {%0, %1}, [%3+%4];\n"
         "}\n"
         : "+l"(v.x), "+l"(v.y)
         : "r"((int)pred), "l"(base), "n"(OFF));
@@ -202,7 +224,7 @@ __device__ __forceinline__ ThCellV th_ld32_if(const void *p, bool pred, ThCellV 
         "{\n"
         ".reg .pred p;\n"
         "setp.ne.s32 p, %4, 0;\n"
-        "@p ld.global.nc.v4.b64 {%0, %1, %2, %3}, [%5];\n"
+        "@p ld.global.nc" TH_L2H ".v4.b64 {%0, %1, %2, %3}, [%5];\n"
         "}\n"
         : "+l"(v.pc), "+l"(v.m1_before), "+l"(v.start0), "+l"(v.m1_0)
         : "r"((int)pred), "l"(p));
@@ -210,7 +232,7 @@ __device__ __forceinline__ ThCellV th_ld32_if(const void *p, bool pred, ThCellV 
 }
 __device__ __forceinline__ ThCellV th_ld32(const void *p) {
     ThCellV v;
-    asm volatile("ld.global.nc.v4.b64 {%0, %1, %2, %3}, [%4];"
+    asm volatile("ld.global.nc" TH_L2H ".v4.b64 {%0, %1, %2, %3}, [%4];"
                  : "=l"(v.pc), "=l"(v.m1_before), "=l"(v.start0), "=l"(v.m1_0)
                  : "l"(p));
     return v;
@@ -259,7 +281,7 @@ __device__ __forceinline__ int th_grid_prefix_end(const ThGrid &g, const ThP1 *_
     }
     while (lo < hi) {
         const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-        const i64 s = __ldg(&p1[mid].start);
+        const i64 s = th_ld8(&p1[mid].start);
         const bool left = STRICT ? (s < key) : (s <= key);
         if (left) lo = mid + 1; else hi = mid;
     }

@@ -25,7 +25,7 @@ __device__ __forceinline__ int lk_current_row(const ThGrid &g, i64 u, const ThP1
     int c1 = th_grid_prefix_end<false>(g, p1, u, now);   // rows with start <= now
     i64 best_id = TH_I64_MAX;
     int best_row = -1;
-    while (c1 > lo && __ldg(&p1[c1 - 1].m1) >= now) {
+    while (c1 > lo && th_ld8(&p1[c1 - 1].m1) >= now) {
         const int c0 = c1 - 32 > lo ? c1 - 32 : lo;
         const int j = c0 + lane;
         if (j < c1) {
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(LK_THREADS) k3_current_kernel(ThGrid g, const 
         const int row = lk_current_row(g, u, p1, p3, seg[u] + 1, now, lane, &id);   // seg[u] = sentinel
         if (lane == 0) {
             out_res[u] = row >= 0 ? id : -1;
-            out_owner[u] = row >= 0 ? __ldg(&p4[row].owner) : -1;
+            out_owner[u] = row >= 0 ? th_ld8(&p4[row].owner) : -1;
         }
     }
 }
@@ -92,12 +92,12 @@ __device__ __forceinline__ UpAcc lk_upcoming(const ThGrid &g, i64 u, const ThP1 
         bool mt = false;
         if (j < c1) {
             const longlong2 e = th_ld16(&p3[j]);        // {end, idc}
-            const i64 s = __ldg(&p1[j].start);
+            const i64 s = th_ld8(&p1[j].start);
             mt = !th_idc_cancelled(e.y) && (s >= now || e.x > now);
         }
         bool oh = false;
         if (WANT_OWNER && mt) {
-            const i64 o = __ldg(&p4[j].owner);
+            const i64 o = th_ld8(&p4[j].owner);
             oh = test == TH_OWNER_ANY ? true : (test == TH_OWNER_OTHER ? (o != owner) : (o == owner));
         }
         const u32 bal = __ballot_sync(gmask, mt) & gmask;
@@ -133,9 +133,9 @@ __global__ void __launch_bounds__(LK_THREADS) k3_upcoming_kernel(ThGrid g, const
         if (gl == 0) {
             if (a.count > 0) {
                 const int r = a.first_row;
-                o_id[q] = th_idc_id(__ldg(&p3[r].idc));
-                o_start[q] = __ldg(&p1[r].start);
-                o_owner[q] = __ldg(&p4[r].owner);
+                o_id[q] = th_idc_id(th_ld8(&p3[r].idc));
+                o_start[q] = th_ld8(&p1[r].start);
+                o_owner[q] = th_ld8(&p4[r].owner);
             } else {
                 o_id[q] = -1; o_start[q] = -1; o_owner[q] = -1;
             }

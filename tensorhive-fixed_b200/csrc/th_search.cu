@@ -139,21 +139,26 @@ __device__ __forceinline__ bool k2_resolve(const ThCellV c, const ThP1 *__restri
             int lo = pos + BM_PROBE, hi = pos + cnt;
             while (lo < hi) {
                 const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
-                if (__ldg(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
+                if (th_ld8(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
             }
             // lo >= 1: bucket 0 starts with the sentinel, later buckets are preceded by it
-            mall = __ldg(&p4[lo - 1].mall);
+            mall = th_ld8(&p4[lo - 1].mall);
         }
         return mall >= qs;
     }
 }
 
-template <int MODE>
+// PACKED = the wire format of th_conflict_bitmap_packed: uuid codes and self ids as uint32 columns (0xFFFFFFFF = no self
+// id; q_self may be NULL = no candidate is a self-update), 24 or 20 bytes per query instead of 32.
+template <int MODE, bool PACKED = false>
 __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     ThGrid g, const ThP1 *__restrict__ p1, const ThP2 *__restrict__ p2, const ThP4 *__restrict__ p4, i64 n_uuids, i64 m,
-    const i64 *__restrict__ q_uuid, const i64 *__restrict__ q_start, const i64 *__restrict__ q_end,
-    const i64 *__restrict__ q_self, int cols_aligned16, u32 *__restrict__ out_bits, ThPeerOut po) {
+    const void *__restrict__ q_uuid_v, const i64 *__restrict__ q_start, const i64 *__restrict__ q_end,
+    const void *__restrict__ q_self_v, int cols_aligned16, u32 *__restrict__ out_bits, ThPeerOut po) {
     __shared__ __align__(128) i64 sq[BM_WARPS][BM_STAGES][4][32];
+    const i64 *q_uuid = static_cast<const i64 *>(q_uuid_v), *q_self = static_cast<const i64 *>(q_self_v);
+    const u32 *q_uuid32 = static_cast<const u32 *>(q_uuid_v), *q_self32 = static_cast<const u32 *>(q_self_v);
+    const bool with_self = MODE == TH_MODE_STRICT && (!PACKED || q_self_v != nullptr);
     constexpr int NCOL = MODE == TH_MODE_STRICT ? 4 : 3;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const i64 full_tiles = cols_aligned16 ? m / 32 : 0;      // warp tiles that are staged through shared memory
@@ -175,11 +180,20 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     auto stage_in = [&](i64 tile, int st) {
         if (tile < t_end && tile < full_tiles) {
             const i64 base = tile * 32;
+            if (!PACKED) {
 #pragma unroll
-            for (int c = lane; c < NCOL * 16; c += 32) {
-                const int col = c >> 4, off = (c & 15) * 2;      // 16 chunks per column, 2 elements per chunk
-                const i64 *src = (col == 0 ? q_uuid : col == 1 ? q_end : col == 2 ? q_start : q_self) + base + off;
-                th_cp_async16(&sq[warp][st][col][off], src);
+                for (int c = lane; c < NCOL * 16; c += 32) {
+                    const int col = c >> 4, off = (c & 15) * 2;      // 16 chunks per column, 2 elements per chunk
+                    const i64 *src = (col == 0 ? q_uuid : col == 1 ? q_end : col == 2 ? q_start : q_self) + base + off;
+                    th_cp_async16(&sq[warp][st][col][off], src);
+                }
+            } else {
+                // 48 chunks: end (16), start (16), uuid u32 (8), self u32 (8, skipped when there is no self column)
+                th_cp_async16(&sq[warp][st][lane < 16 ? 1 : 2][(lane & 15) * 2],
+                              (lane < 16 ? q_end : q_start) + base + (lane & 15) * 2);
+                if (lane < 8) th_cp_async16(reinterpret_cast<u32 *>(&sq[warp][st][0][0]) + lane * 4, q_uuid32 + base + lane * 4);
+                else if (lane < 16 && with_self)
+                    th_cp_async16(reinterpret_cast<u32 *>(&sq[warp][st][3][0]) + (lane - 8) * 4, q_self32 + base + (lane - 8) * 4);
             }
         }
         th_cp_async_commit();
@@ -189,18 +203,30 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         if (tile < full_tiles) {
             th_cp_async_wait<BM_STAGES - 1>();
             __syncwarp();                                   // the other lanes' chunks are visible too
-            u = sq[warp][st][0][lane];
             qe = sq[warp][st][1][lane];
             qs = sq[warp][st][2][lane];
-            self = MODE == TH_MODE_STRICT ? sq[warp][st][3][lane] : -1;
+            if (!PACKED) {
+                u = sq[warp][st][0][lane];
+                self = MODE == TH_MODE_STRICT ? sq[warp][st][3][lane] : -1;
+            } else {
+                u = (i64)reinterpret_cast<const u32 *>(&sq[warp][st][0][0])[lane];
+                const u32 f = with_self ? reinterpret_cast<const u32 *>(&sq[warp][st][3][0])[lane] : 0xffffffffu;
+                self = f == 0xffffffffu ? -1 : (i64)f;
+            }
             __syncwarp();                                   // every lane has read the stage: refill it
         } else {   // ragged last tile or unaligned caller buffers
             const i64 i = tile * 32 + lane;
             const i64 ic = i < m ? i : m - 1;
-            u = th_ld_stream(&q_uuid[ic]);
             qe = th_ld_stream(&q_end[ic]);
             qs = th_ld_stream(&q_start[ic]);
-            self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
+            if (!PACKED) {
+                u = th_ld_stream(&q_uuid[ic]);
+                self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
+            } else {
+                u = (i64)__ldg(&q_uuid32[ic]);
+                const u32 f = with_self ? __ldg(&q_self32[ic]) : 0xffffffffu;
+                self = f == 0xffffffffu ? -1 : (i64)f;
+            }
         }
         stage_in(tile_of(it + BM_STAGES), st);
 #if BM_CELL_LD == 0
@@ -388,8 +414,8 @@ __device__ __forceinline__ bool cs_match(int mode, i64 start, i64 end, i64 idc, 
 
 // warp-uniform: can any row of [lo, c1) still match?  (looks at the running maximum stored at c1 - 1)
 __device__ __forceinline__ bool cs_more(int mode, const RowView &v, int c1, i64 qs) {
-    if (mode == TH_MODE_STRICT) return __ldg(&v.p4[c1 - 1].mall) > qs;
-    if (mode == TH_MODE_INCLUSIVE) return __ldg(&v.p4[c1 - 1].mall) >= qs;
+    if (mode == TH_MODE_STRICT) return th_ld8(&v.p4[c1 - 1].mall) > qs;
+    if (mode == TH_MODE_INCLUSIVE) return th_ld8(&v.p4[c1 - 1].mall) >= qs;
     const longlong2 e = th_ld16(&v.p1[c1 - 1]);   // {start, m1}: rows at or after qs always match
     return e.x >= qs || e.y > qs;
 }
@@ -427,7 +453,7 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
                 bool mt = false;
                 if (j < c1) {
                     const longlong2 e = th_ld16(&v.p3[j]);   // {end, idc}
-                    const i64 s = (mode == TH_MODE_UPCOMING) ? __ldg(&v.p1[j].start) : 0;
+                    const i64 s = (mode == TH_MODE_UPCOMING) ? th_ld8(&v.p1[j].start) : 0;
                     mt = cs_match(mode, s, e.x, e.y, qs, self);
                 }
                 cnt += __popc(__ballot_sync(gmask, mt) & gmask);
@@ -462,7 +488,7 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64
             longlong2 e = make_longlong2(0, 0);
             if (j < pend) {
                 e = th_ld16(&v.p3[j]);
-                const i64 s = (mode == TH_MODE_UPCOMING) ? __ldg(&v.p1[j].start) : 0;
+                const i64 s = (mode == TH_MODE_UPCOMING) ? th_ld8(&v.p1[j].start) : 0;
                 mt = cs_match(mode, s, e.x, e.y, qs, self);
             }
             const u32 bal = __ballot_sync(gmask, mt) & gmask;
@@ -608,7 +634,7 @@ __global__ void __launch_bounds__(XS_THREADS) xs_write_kernel(const int *__restr
 // ctas_per_sm > 0 caps the persistent grid below what fits (used when the queries stream in over PCIe: a fraction of the
 // resident warps already keeps the link full, and the rest of each SM stays free for other streams)
 static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d_s, const void *d_e, const void *d_f,
-                     int mode, u32 *d_bits, const ThPeerOut &po, cudaStream_t st, int ctas_per_sm = 0) {
+                     int mode, u32 *d_bits, const ThPeerOut &po, cudaStream_t st, int ctas_per_sm = 0, bool packed = false) {
     const i64 n_tiles = ((m + 31) / 32 + BM_WARPS - 1) / BM_WARPS;   // blocks needed to give every warp at least one tile
     // persistent grid: exactly as many CTAs as can be resident at once (148 SMs x occupancy)
     // (per device and mode; the query is a pure function of both, so racing first uses write the same value)
@@ -634,16 +660,12 @@ static int k2_launch(const th_snapshot *h, i64 m, const void *d_u, const void *d
     const unsigned blocks = (unsigned)(n_tiles < resident ? (n_tiles > 0 ? n_tiles : 1) : resident);
     int al16 = ((((uintptr_t)d_u | (uintptr_t)d_s | (uintptr_t)d_e | (uintptr_t)d_f) & 15) == 0) ? 1 : 0;
     if (getenv("TH_K2_DIRECT")) al16 = 0;
-    if (mode == TH_MODE_STRICT)
-        k2_bitmap_kernel<TH_MODE_STRICT><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m,
-                                                                        (const i64 *)d_u, (const i64 *)d_s,
-                                                                        (const i64 *)d_e, (const i64 *)d_f, al16, d_bits,
-                                                                        po);
-    else
-        k2_bitmap_kernel<TH_MODE_INCLUSIVE><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids,
-                                                                           m, (const i64 *)d_u, (const i64 *)d_s,
-                                                                           (const i64 *)d_e, (const i64 *)d_f, al16,
-                                                                           d_bits, po);
+#define K2_GO(MODE_, PACKED_)                                                                                              \
+    k2_bitmap_kernel<MODE_, PACKED_><<<blocks, BM_THREADS, 0, st>>>(th_grid_of(h), h->p1, h->p2, h->p4, h->n_uuids, m, d_u, \
+                                                                    (const i64 *)d_s, (const i64 *)d_e, d_f, al16, d_bits, po)
+    if (mode == TH_MODE_STRICT) { if (packed) K2_GO(TH_MODE_STRICT, true); else K2_GO(TH_MODE_STRICT, false); }
+    else { if (packed) K2_GO(TH_MODE_INCLUSIVE, true); else K2_GO(TH_MODE_INCLUSIVE, false); }
+#undef K2_GO
     TH_CUDA(cudaGetLastError());
     return TH_OK;
 }
@@ -731,6 +753,58 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
     // one CTA per SM keeps the link full (1 / 2 / 4 per SM: 0.659 / 0.660 / 0.660 ms per 1 M-query batch, staged 0.78)
     TH_TRY(k2_launch(h, m, d_u, d_s, d_e, d_f, mode, (u32 *)d_bits, none, st, zero_copy ? 1 : 0));
     TH_CUDA(cudaGetLastError());
+    if (!out_direct) TH_TRY(th_copy_back(out_bits_u32, d_bits, 4 * words, mem, st));
+    if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
+    return TH_OK;
+}
+
+// The same verdicts from a narrower wire format (the host path is bound by PCIe bytes, nothing else): uuid codes and
+// self ids travel as uint32 columns -- q_self_id_u32[i] = 0xFFFFFFFF means "not saved yet", and the whole column may
+// be NULL when no candidate is a self-update -- so a query is 24 or 20 bytes instead of 32.  Ids must be below 2^32 - 1.
+extern "C" int th_conflict_bitmap_packed(const th_snapshot *h, int64_t m, const uint32_t *q_uuid_u32, const int64_t *q_start,
+                                         const int64_t *q_end, const uint32_t *q_self_id_u32, int mode,
+                                         uint32_t *out_bits_u32, int mem, void *stream) {
+    TH_REQUIRE(h != nullptr && h->loaded, "th_conflict_bitmap_packed: snapshot not loaded");
+    TH_REQUIRE(m >= 0, "th_conflict_bitmap_packed: negative m");
+    TH_REQUIRE(mode == TH_MODE_STRICT || mode == TH_MODE_INCLUSIVE, "th_conflict_bitmap_packed: mode %d not supported", mode);
+    TH_REQUIRE(mem == TH_MEM_HOST || mem == TH_MEM_DEVICE, "th_conflict_bitmap_packed: bad mem flag %d", mem);
+    if (m == 0) return TH_OK;
+    TH_REQUIRE(q_uuid_u32 && q_start && q_end && out_bits_u32, "th_conflict_bitmap_packed: NULL array");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) { th_set_error("th_conflict_bitmap_packed: cannot select device %d", h->device); return TH_ECUDA; }
+    cudaStream_t st = th_call_stream(stream, mem, h->device);
+    ThScratch sc(st);
+    const size_t zm = (size_t)m, words = (zm + 31) / 32;
+    const void *d_u, *d_s, *d_e, *d_f = nullptr;
+    void *d_bits;
+    bool zero_copy = false;
+    if (mem == TH_MEM_HOST && !getenv("TH_NO_ZERO_COPY")) {
+        const void *cols[4] = {q_uuid_u32, q_start, q_end, q_self_id_u32};
+        const void *mapped[4];
+        zero_copy = k2_map_pinned(cols, 4, mapped) == 1;
+        if (zero_copy) { d_u = mapped[0]; d_s = mapped[1]; d_e = mapped[2]; d_f = mapped[3]; }
+    }
+    if (!zero_copy) {
+        TH_TRY(sc.in(q_uuid_u32, 4 * zm, mem, &d_u));
+        TH_TRY(sc.in(q_start, 8 * zm, mem, &d_s));
+        TH_TRY(sc.in(q_end, 8 * zm, mem, &d_e));
+        if (q_self_id_u32) TH_TRY(sc.in(q_self_id_u32, 4 * zm, mem, &d_f));
+    }
+    bool out_direct = false;
+    if (zero_copy) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, out_bits_u32) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer) {
+            d_bits = a.devicePointer;
+            out_direct = true;
+        } else {
+            cudaGetLastError();
+        }
+    }
+    if (!out_direct) TH_TRY(sc.out(out_bits_u32, 4 * words, mem, &d_bits));
+    ThPeerOut none;
+    none.n = 0;
+    none.unpack = 0;
+    TH_TRY(k2_launch(h, m, d_u, d_s, d_e, d_f, mode, (u32 *)d_bits, none, st, zero_copy ? 1 : 0, true));
     if (!out_direct) TH_TRY(th_copy_back(out_bits_u32, d_bits, 4 * words, mem, st));
     if (mem == TH_MEM_HOST) TH_CUDA(cudaStreamSynchronize(st));
     return TH_OK;

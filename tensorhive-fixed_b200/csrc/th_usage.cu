@@ -64,7 +64,7 @@ __device__ __forceinline__ i64 us_ld8_if(const i64 *p, bool pred, i64 dflt) {
         "{\n"
         ".reg .pred p;\n"
         "setp.ne.s32 p, %1, 0;\n"
-        "@p ld.global.nc.s64 %0, [%2];\n"
+        "@p ld.global.nc" TH_L2H ".s64 %0, [%2];\n"
         "}\n"
         : "+l"(v)
         : "r"((int)pred), "l"(p));
@@ -90,7 +90,7 @@ __device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64
     // The guess missed.  Irregular logs (gaps, restarts) put the answer tens of samples away, rarely thousands: gallop
     // from the window in doubling steps until the predicate flips, then bisect that bracket -- about 2 log2(distance)
     // dependent loads instead of log2(n).
-    auto holds = [&](i64 p) { const i64 x = __ldg(&seg[p]); return GE ? (x >= key) : (x > key); };
+    auto holds = [&](i64 p) { const i64 x = th_ld8(&seg[p]); return GE ? (x >= key) : (x > key); };
     i64 l, r;   // the answer lies in [l, r]; the predicate holds at r (r == n counts as "holds")
     if (nfalse == 0) {
         if (w0 == 0) return 0;
@@ -115,7 +115,7 @@ __device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64
     }
     while (l < r) {
         const i64 mid = l + ((r - l) >> 1);
-        const i64 x = __ldg(&seg[mid]);
+        const i64 x = th_ld8(&seg[mid]);
         if (GE ? (x >= key) : (x > key)) r = mid; else l = mid + 1;
     }
     return l;
@@ -215,8 +215,8 @@ __device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *
         const int lo = (int)(a > i0 ? a - i0 : 0);
         const int hi = (int)(b < i0 + 16 ? b - i0 : 16);
         if (i0 + 16 <= s_total) {
-            uint4 g4 = __ldg(reinterpret_cast<const uint4 *>(gpu + i0));
-            uint4 m4 = __ldg(reinterpret_cast<const uint4 *>(mem + i0));
+            uint4 g4 = th_ld16u(gpu + i0);
+            uint4 m4 = th_ld16u(mem + i0);
             if (lo > 0 || hi < 16) { g4 = us_mask16(g4, lo, hi); m4 = us_mask16(m4, lo, hi); }   // edge chunks only
             sg += us_sum16(g4);
             sm += us_sum16(m4);

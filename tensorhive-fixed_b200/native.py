@@ -32,6 +32,7 @@ SIGNATURES = {
     'th_snapshot_info': (_int, [_vp, _i64p, _i64p, _i64p, _i64p]),
     'th_snapshot_export': (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _vp]),
     'th_conflict_bitmap': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, _vp]),
+    'th_conflict_bitmap_packed': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, _vp]),
     'th_conflict_sets': (_int, [_vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _i64, _i64p, _int, _vp]),
     'th_current_owner': (_int, [_vp, _i64, _vp, _vp, _int, _vp]),
     'th_upcoming': (_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _int, _vp]),

@@ -617,3 +617,31 @@ def test_usage_reduce_u8_unaligned_columns(th, brute):
                                             base_m[shift:shift + n].astype(np.int64), wu, ws, we)
         assert np.array_equal(outs[0].cpu().numpy(), esg) and np.array_equal(outs[1].cpu().numpy(), esm)
         assert np.array_equal(outs[2].cpu().numpy(), ecnt)
+
+
+@pytest.mark.parametrize('m', [1, 31, 32, 33, 4097, 100_003])
+def test_packed_queries_give_identical_bitmaps(th, synth, brute, m):
+    """th_conflict_bitmap_packed (uint32 uuid / self columns, 20-24 B per query) against th_conflict_bitmap and the oracle:
+    host arrays (pageable and pinned, read in place), device arrays, misaligned columns, no self column, both modes."""
+    import torch
+    cal = synth.make_calendar(30_000, 96, seed=4242)
+    q = synth.make_queries(cal, m, seed=4243)
+    snap = _load(th, cal)
+    want = snap.conflict_words(q['uuid_id'], q['start'], q['end'], q['self_id'])
+    assert np.array_equal(th.api.unpack_bits(want, m), brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id']))
+    pu, pf = th.Snapshot.pack_queries(q['uuid_id'], q['self_id'])
+    assert np.array_equal(snap.conflict_words_packed(pu, q['start'], q['end'], pf), want)
+    # pinned host columns: the kernel reads them over PCIe itself
+    pin = [torch.from_numpy(x.copy()).pin_memory() for x in (pu.view(np.int32), q['start'], q['end'], pf.view(np.int32))]
+    got = snap.conflict_words_packed(pin[0].numpy().view(np.uint32), pin[1].numpy(), pin[2].numpy(), pin[3].numpy().view(np.uint32))
+    assert np.array_equal(got, want)
+    # device columns, and the same shifted by one element (4-byte aligned only: the direct-load path)
+    dev = [torch.from_numpy(np.concatenate([x[:1], x])).cuda() for x in (pu.view(np.int32), q['start'], q['end'], pf.view(np.int32))]
+    got = snap.conflict_words_packed(*[t[1:] for t in dev])
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), want)
+    # no self column at all = every candidate is new
+    no_self = snap.conflict_words(q['uuid_id'], q['start'], q['end'], np.full(m, -1, np.int64))
+    assert np.array_equal(snap.conflict_words_packed(pu, q['start'], q['end'], None), no_self)
+    incl = snap.conflict_words(q['uuid_id'], q['start'], q['end'], None, th.MODE_INCLUSIVE)
+    assert np.array_equal(snap.conflict_words_packed(pu, q['start'], q['end'], None, th.MODE_INCLUSIVE), incl)
+    snap.close()
