@@ -406,17 +406,42 @@ def run_ours(args):
 
     out_all = torch.empty(world * ((N_QUERIES + 31) // 32), dtype=torch.int32).pin_memory() if px is not None else None
 
-    def e2e_step():
+    # the packed wire format (uint32 uuid / self columns: 24 B per query instead of 32) in pinned buffers as well
+    pu, pf = th.Snapshot.pack_queries(q['uuid_id'], q['self_id'])
+    pin_u32 = torch.from_numpy(pu.view(np.int32)).pin_memory()
+    pin_f32 = torch.from_numpy(pf.view(np.int32)).pin_memory()
+    out_pin_p = torch.empty((N_QUERIES + 31) // 32, dtype=torch.int32).pin_memory()
+
+    def e2e_step(packed=True):
         if px is None:
-            native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, pin_np[0].ctypes.data, pin_np[1].ctypes.data,
-                                                pin_np[2].ctypes.data, pin_np[3].ctypes.data, 0, out_pin.data_ptr(), 0,
-                                                sp))
+            if packed:
+                native.check(lib.th_conflict_bitmap_packed(snap._h, N_QUERIES, pin_u32.data_ptr(), pin[1].data_ptr(),
+                                                           pin[2].data_ptr(), pin_f32.data_ptr(), 0, out_pin_p.data_ptr(), 0, sp))
+            else:
+                native.check(lib.th_conflict_bitmap(snap._h, N_QUERIES, pin_np[0].ctypes.data, pin_np[1].ctypes.data,
+                                                    pin_np[2].ctypes.data, pin_np[3].ctypes.data, 0, out_pin.data_ptr(), 0,
+                                                    sp))
             return
         # the fused kernel reads the pinned columns in place over PCIe (no staging copies); everybody's verdicts
         # come back to the host
-        g = px.conflict_words(snap, pin[0], pin[1], pin[2], pin[3], check=False)
+        if packed:
+            g = px.conflict_words(snap, pin_u32, pin[1], pin[2], pin_f32, check=False, packed=True)
+        else:
+            g = px.conflict_words(snap, pin[0], pin[1], pin[2], pin[3], check=False)
         out_all.copy_(g.reshape(-1), non_blocking=True)
         torch.cuda.synchronize()
+
+    def e2e_timed(packed):
+        for _ in range(3):
+            e2e_step(packed)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step(packed)
+        torch.cuda.synchronize()
+        dt_ = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        return dt_
 
     # for context: the same 32 MB as bare pinned-host -> device copies on this box (what the e2e step cannot beat)
     bare = [torch.empty_like(t) for t in qd]
@@ -429,21 +454,16 @@ def run_ours(args):
         torch.cuda.synchronize()
         copy_ms.append(1e3 * (time.perf_counter() - t0))
     del bare
-    for _ in range(3):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
+    e2e_wide_s = e2e_timed(False)           # int64 columns, 32 B per query
+    out_wide = out_all.clone() if px is not None else None
+    e2e_s = e2e_timed(True)                 # packed columns, 24 B per query: the headline
     e2e_value = world * N_QUERIES * steps / e2e_s
     # check the last e2e result against the device-resident run (same queries)
     k2_only(); torch.cuda.synchronize()
     exchange_check = None
     if px is None:
         assert np.array_equal(out_pin.numpy(), words.cpu().numpy()), 'host-path and device-path bitmaps differ'
+        assert np.array_equal(out_pin_p.numpy(), words.cpu().numpy()), 'packed host path and device path bitmaps differ'
     else:
         # EVERY rank's words as delivered by the fused exchange (device-resident step and e2e step) against the same
         # words moved by NCCL: all_gather of each rank's plain-kernel bitmap
@@ -455,10 +475,11 @@ def run_ours(args):
         px.check()
         want_all = nccl_all.view(world, -1).cpu().numpy()
         bad = int((fused.cpu().numpy()[:, :words.numel()] != want_all).sum())
-        bad += int((out_all.numpy().reshape(world, -1) != want_all).sum())
+        bad += int((out_all.numpy().reshape(world, -1) != want_all).sum())          # e2e, packed columns
+        bad += int((out_wide.numpy().reshape(world, -1) != want_all).sum())         # e2e, int64 columns
         t_bad = torch.tensor([bad], dtype=torch.int64, device=dev)
         dist.all_reduce(t_bad)
-        exchange_check = {'words_compared_per_rank': 2 * int(want_all.size), 'ranks': world,
+        exchange_check = {'words_compared_per_rank': 3 * int(want_all.size), 'ranks': world,
                           'mismatching_words_all_ranks': int(t_bad.item()),
                           'what': 'fused-exchange words of ALL ranks (device step and e2e step) vs an NCCL all_gather of the '
                                   'plain-kernel words, on every rank'}
@@ -468,14 +489,18 @@ def run_ours(args):
             'warmup': warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'int64', 'data': 'synthetic', 'config': _config(world),
             'clocks': clocks.summary(),
-            'e2e': {'value': e2e_value, 'unit': 'queries/s', 'h2d_bytes_per_step': 32 * N_QUERIES,
+            'e2e': {'value': e2e_value, 'unit': 'queries/s', 'h2d_bytes_per_step': 24 * N_QUERIES,
+                    'int64_columns': {'value': world * N_QUERIES * steps / e2e_wide_s, 'ms_per_step': 1e3 * e2e_wide_s / steps,
+                                      'h2d_bytes_per_step': 32 * N_QUERIES,
+                                      'api': 'th_conflict_bitmap / th_conflict_bitmap_exchange on four int64 columns'},
                     'd2h_bytes_per_step': 4 * ((N_QUERIES + 31) // 32) * (world if px is not None else 1),
                     'ms_per_step': 1e3 * e2e_s / steps, 'host_affinity': affinity,
                     'bare_h2d_copy_ms': min(copy_ms), 'bare_h2d_GBs': 32 * N_QUERIES / (min(copy_ms) * 1e-3) / 1e9,
-                    'api': ('th_conflict_bitmap(TH_MEM_HOST) on pinned buffers: the kernel reads the 32 MB of query columns in place over '
-                            'PCIe and writes the bitmap into the pinned output, no staging copies' if px is None else
-                            'th_conflict_bitmap_exchange on pinned buffers (fused K2 + peer all-gather; the kernel reads the query '
-                            'columns in place over PCIe) + D2H of all ranks\' words')},
+                    'api': ('th_conflict_bitmap_packed(TH_MEM_HOST) on pinned buffers (uuid / self id as uint32, start / end int64: '
+                            '24 B per query): the kernel reads the columns in place over PCIe and writes the bitmap into the '
+                            'pinned output, no staging copies' if px is None else
+                            'th_conflict_bitmap_exchange_packed on pinned buffers (fused K2 + peer all-gather; the kernel reads '
+                            'the packed query columns in place over PCIe) + D2H of all ranks\' words')},
             'gpu_launches': steps,      # one K2 launch per step (send and receive halves of the exchange are inside it)
             'roofline': {'kernel': 'k2_bitmap_kernel', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': _traffic('k2_bitmap_kernel') if N_ROWS == 1_000_000 else None,

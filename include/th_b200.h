@@ -240,6 +240,11 @@ int th_peer_check(th_peer *p, void *stream);
 int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
                                 const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id, int mode,
                                 const int64_t *m_per_rank, int wait, uint32_t **out_gathered, void *stream);
+/* th_conflict_bitmap_exchange from the packed wire format of th_conflict_bitmap_packed. */
+int th_conflict_bitmap_exchange_packed(const th_snapshot *h, th_peer *peer, int64_t m, const uint32_t *q_uuid_u32,
+                                       const int64_t *q_start, const int64_t *q_end, const uint32_t *q_self_id_u32,
+                                       int mode, const int64_t *m_per_rank, int wait, uint32_t **out_gathered,
+                                       void *stream);
 int th_peer_wait(th_peer *p, void *stream);
 /* Device-side rendezvous of all ranks on `stream` (no host synchronisation). */
 int th_peer_barrier(th_peer *p, void *stream);

@@ -942,10 +942,9 @@ static int k2_launch_unpack(th_peer *peer, cudaStream_t st) {
     return TH_OK;
 }
 
-extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
-                                           const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id,
-                                           int mode, const int64_t *m_per_rank, int wait, uint32_t **out_gathered,
-                                           void *stream) {
+static int k2_exchange_impl(const th_snapshot *h, th_peer *peer, int64_t m, const void *q_uuid, const int64_t *q_start,
+                            const int64_t *q_end, const void *q_self_id, bool packed, int mode,
+                            const int64_t *m_per_rank, int wait, uint32_t **out_gathered, void *stream) {
     TH_REQUIRE(h != nullptr && h->loaded, "th_conflict_bitmap_exchange: snapshot not loaded");
     TH_REQUIRE(peer != nullptr && peer->connected, "th_conflict_bitmap_exchange: peer group not connected");
     TH_REQUIRE(peer->device == h->device, "th_conflict_bitmap_exchange: peer group and snapshot are on different devices");
@@ -954,7 +953,7 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
                (long long)m, (long long)((m + 31) / 32), (long long)peer->words_per_rank);
     TH_REQUIRE(mode == TH_MODE_STRICT || mode == TH_MODE_INCLUSIVE, "th_conflict_bitmap_exchange: mode %d not supported", mode);
     TH_REQUIRE(m == 0 || (q_uuid && q_start && q_end), "th_conflict_bitmap_exchange: NULL array");
-    TH_REQUIRE(mode != TH_MODE_STRICT || m == 0 || q_self_id, "th_conflict_bitmap_exchange: q_self_id is NULL");
+    TH_REQUIRE(packed || mode != TH_MODE_STRICT || m == 0 || q_self_id, "th_conflict_bitmap_exchange: q_self_id is NULL");
     const int world = peer->world;
     const i64 wpr = peer->words_per_rank;
     for (int r = 0; r < world; ++r) {
@@ -995,10 +994,26 @@ extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, 
     const void *mapped[4];
     const int pinned = m > 0 ? k2_map_pinned(cols, 4, mapped) : 0;
     TH_REQUIRE(pinned >= 0, "th_conflict_bitmap_exchange: query columns mix page-locked host memory with other memory");
-    if (m > 0) TH_TRY(k2_launch(h, m, mapped[0], mapped[1], mapped[2], mapped[3], mode, nullptr, po, st, pinned == 1 ? 1 : 0));
+    if (m > 0) TH_TRY(k2_launch(h, m, mapped[0], mapped[1], mapped[2], mapped[3], mode, nullptr, po, st, pinned == 1 ? 1 : 0, packed));
     if (wait && m == 0) TH_TRY(k2_launch_unpack(peer, st));
     if (out_gathered) *out_gathered = th_peer_out(peer, parity);
     return TH_OK;
+}
+
+extern "C" int th_conflict_bitmap_exchange(const th_snapshot *h, th_peer *peer, int64_t m, const int64_t *q_uuid,
+                                           const int64_t *q_start, const int64_t *q_end, const int64_t *q_self_id,
+                                           int mode, const int64_t *m_per_rank, int wait, uint32_t **out_gathered,
+                                           void *stream) {
+    return k2_exchange_impl(h, peer, m, q_uuid, q_start, q_end, q_self_id, false, mode, m_per_rank, wait, out_gathered, stream);
+}
+
+// the same step from the packed wire format of th_conflict_bitmap_packed (uint32 uuid / self columns, self may be NULL)
+extern "C" int th_conflict_bitmap_exchange_packed(const th_snapshot *h, th_peer *peer, int64_t m, const uint32_t *q_uuid_u32,
+                                                  const int64_t *q_start, const int64_t *q_end,
+                                                  const uint32_t *q_self_id_u32, int mode, const int64_t *m_per_rank,
+                                                  int wait, uint32_t **out_gathered, void *stream) {
+    return k2_exchange_impl(h, peer, m, q_uuid_u32, q_start, q_end, q_self_id_u32, true, mode, m_per_rank, wait, out_gathered,
+                            stream);
 }
 
 // device-side rendezvous of all ranks: raise my barrier flag on every peer, then wait for everybody's

@@ -47,6 +47,7 @@ SIGNATURES = {
     'th_peer_destroy': (_int, [_vp]),
     'th_peer_check': (_int, [_vp, _vp]),
     'th_conflict_bitmap_exchange': (_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, C.POINTER(_vp), _vp]),
+    'th_conflict_bitmap_exchange_packed': (_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _int, _vp, _int, C.POINTER(_vp), _vp]),
     'th_peer_wait': (_int, [_vp, _vp]),
     'th_peer_barrier': (_int, [_vp, _vp]),
     'th_usage_reduce_u8': (_int, [_int, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,

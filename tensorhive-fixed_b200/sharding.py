@@ -253,7 +253,7 @@ class PeerExchange:
         self._native.check(self._lib.th_peer_connect(self._h, None, arr))
 
     def conflict_words(self, snapshot, q_uuid, q_start, q_end, q_self, mode: int = 0, wait: bool = True, counts=None,
-                       check: bool = True):
+                       check: bool = True, packed: bool = False):
         """int64 tensors in -- CUDA tensors, or page-locked host tensors (``.pin_memory()``), which the kernel streams
         over PCIe itself; returns an int32 CUDA tensor view [world, words_per_rank] of the gathered words (rank r's
         words for its own queries sit in row r).  ``counts[r]`` = number of queries rank r contributes this step
@@ -261,7 +261,8 @@ class PeerExchange:
 
         ``check=True`` (default) synchronises the stream and raises ``NativeError(TH_EINTERNAL)`` when a peer's words
         did not arrive in time (the words of such a step read as 0 and must not be used).  A caller that pipelines
-        steps passes ``check=False`` and calls :meth:`check` before it consumes the words."""
+        steps passes ``check=False`` and calls :meth:`check` before it consumes the words.  ``packed=True``: ``q_uuid`` and
+        ``q_self`` are int32 tensors holding the uint32 columns of ``Snapshot.pack_queries`` (``q_self`` may be None)."""
         import torch
         C = self._C
         m = int(q_uuid.numel())
@@ -270,7 +271,8 @@ class PeerExchange:
         cnt = None
         if counts is not None:
             cnt = (C.c_int64 * self.world)(*[int(c) for c in counts])
-        self._native.check(self._lib.th_conflict_bitmap_exchange(
+        fn = self._lib.th_conflict_bitmap_exchange_packed if packed else self._lib.th_conflict_bitmap_exchange
+        self._native.check(fn(
             snapshot._h, self._h, m, C.c_void_p(q_uuid.data_ptr()), C.c_void_p(q_start.data_ptr()),
             C.c_void_p(q_end.data_ptr()), C.c_void_p(q_self.data_ptr()) if q_self is not None else None, int(mode),
             cnt, 1 if wait else 0, C.byref(out), stream))
