@@ -139,9 +139,10 @@ static void th_snapshot_release(th_snapshot *h) {
     if (h->p4) cudaFree(h->p4);
     if (h->uuid) cudaFree(h->uuid);
     if (h->grid) cudaFree(h->grid);
-    h->seg = nullptr; h->p1 = nullptr; h->p2 = nullptr; h->p3 = nullptr; h->p4 = nullptr; h->uuid = nullptr; h->grid = nullptr;
+    if (h->ugrid) cudaFree(h->ugrid);
+    h->seg = nullptr; h->p1 = nullptr; h->p2 = nullptr; h->p3 = nullptr; h->p4 = nullptr; h->uuid = nullptr; h->grid = nullptr; h->ugrid = nullptr;
     h->loaded = 0; h->n = 0; h->nt = 0; h->n_uuids = 0; h->device_bytes = 0;
-    h->cap_nt = 0; h->cap_uuids = 0; h->cap_cells = 0;
+    h->cap_nt = 0; h->cap_uuids = 0; h->cap_cells = 0; h->cap_ugrid = 0;
 }
 
 extern "C" int th_snapshot_create(int device, th_snapshot **out) {

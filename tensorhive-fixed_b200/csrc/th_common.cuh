@@ -64,19 +64,22 @@ struct __align__(16) ThP4 { i64 owner; i64 mall; }; // mall = max end over ALL r
 // the hot kernel needs no per-uuid bounds: position seg[u] is the sentinel, real rows are
 // (seg[u], seg[u + 1]).  nt = n + n_uuids positions in total.
 //
-// Time grid: cell (u, b) covers starts in [t0 + (b << shift), t0 + ((b + 1) << shift)) of uuid u (the sentinel
-// counts as bucket 0).  A cell is 32 bytes = ONE probe (a single 256-bit load, LDG.E.256 -- new with sm_100): the
+// Time grid, ONE PER UUID: cell (u, b) covers starts in [t0_u + (b << shift_u), t0_u + ((b + 1) << shift_u)) of uuid u
+// (the sentinel counts as bucket 0); uuid u owns cells [base_u, base_u + nb_u) with nb_u proportional to ITS row count
+// and spread over ITS OWN span of starts, so a hot GPU with a hundred times the rows gets a hundred times the cells
+// (round 1 cut every uuid's axis by one global span and the average row count: with skewed popularity most rows sat
+// in buckets of hundreds, finished by bisection).  The per-uuid entry {t0, base, shift, nb} is 32 bytes, L2-resident
+// (2 MB for 65 536 uuids).  A cell is 32 bytes = ONE probe (a single 256-bit load, LDG.E.256 -- new with sm_100): the
 // first position of the bucket, how many rows it holds, the running maximum m1 of everything before it, and the
 // bucket's FIRST row {start, m1}.  At ~1.5 cells per row half of the buckets are empty and a third hold one row, so
 // most lower bounds are settled by the cell's own 32-byte sector without touching the row arrays at all (at
 // config-5 size every scattered probe costs a 64-byte HBM atom: one atom per query instead of two or three).
 struct __align__(32) ThCell { int pos; int cnt; i64 m1_before; i64 start0; i64 m1_0; };
 struct ThCellV { i64 pc, m1_before, start0, m1_0; };   // as loaded: pc = pos | cnt << 32
+struct __align__(32) ThUGrid { i64 t0; i64 base; int shift; int nb; i64 pad; };   // read as ThCellV: {t0, base, shift | nb << 32, -}
 struct ThGrid {
-    const ThCell *cells;   // [n_uuids * nb]
-    i64 t0;
-    int shift;
-    int nb;
+    const ThCell *cells;   // [sum of nb_u]
+    const ThUGrid *ug;     // [n_uuids]
 };
 
 struct th_snapshot {
@@ -91,14 +94,14 @@ struct th_snapshot {
     ThP3 *p3;      // [nt]
     ThP4 *p4;      // [nt]
     u32 *uuid;     // [nt] uuid of each position (export / rebuild)
-    ThCell *grid;  // [n_uuids * nb]
-    i64 grid_t0;
-    int grid_shift, grid_nb;
+    ThCell *grid;  // [n_cells]
+    ThUGrid *ugrid;  // [n_uuids]
+    i64 n_cells;
     i64 max_id;                         // largest reservation id (bounds the digit plan when lists are id-sorted)
-    i64 cap_nt, cap_uuids, cap_cells;   // allocated capacities: a reload that fits reuses the buffers
+    i64 cap_nt, cap_uuids, cap_cells, cap_ugrid;   // allocated capacities: a reload that fits reuses the buffers
 };
 static inline ThGrid th_grid_of(const th_snapshot *h) {
-    ThGrid g; g.cells = h->grid; g.t0 = h->grid_t0; g.shift = h->grid_shift; g.nb = h->grid_nb; return g;
+    ThGrid g; g.cells = h->grid; g.ug = h->ugrid; return g;
 }
 
 // ---- peer exchange (multi-GPU): where a fused kernel deposits its bitmap words on every rank --------------
@@ -249,18 +252,25 @@ __device__ __forceinline__ void th_cp_async_wait() { asm volatile("cp.async.wait
 __device__ __forceinline__ i64 th_idc_id(i64 idc) { return idc & TH_I64_MAX; }
 __device__ __forceinline__ bool th_idc_cancelled(i64 idc) { return idc < 0; }
 
+// the grid cell of (u, key); u must be a valid uuid.  One L2-resident 32-byte read of the uuid's entry, then arithmetic.
+__device__ __forceinline__ const ThCell *th_cell_of(const ThGrid &g, i64 u, i64 key) {
+    const ThCellV e = th_ld32(&g.ug[u]);          // {t0, base, shift | nb << 32, -}
+    const int shift = (int)(e.start0 & 0xffffffffll), nb = (int)(e.start0 >> 32);
+    i64 b = 0;
+    if (key > e.pc) {
+        const u64 d = ((u64)key - (u64)e.pc) >> shift;
+        b = d < (u64)(nb - 1) ? (i64)d : (i64)(nb - 1);
+    }
+    return g.cells + (e.m1_before + b);
+}
+
 // End of the prefix "rows of uuid u that start before `key`" (STRICT: start < key, else start <= key) as an absolute
 // position, found through the time grid: one 16-byte cell, then a search over that bucket's rows only (rows of
 // earlier buckets start before the bucket and hence before key, rows of later buckets after it).  The result is
 // at least seg[u] + 1 because the sentinel (start = -inf) sits in bucket 0.  u must be a valid uuid.
 template <bool STRICT>
 __device__ __forceinline__ int th_grid_prefix_end(const ThGrid &g, const ThP1 *__restrict__ p1, i64 u, i64 key) {
-    i64 b = 0;
-    if (key > g.t0) {
-        const u64 d = ((u64)key - (u64)g.t0) >> g.shift;
-        b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
-    }
-    const ThCellV c = th_ld32(&g.cells[u * g.nb + b]);
+    const ThCellV c = th_ld32(th_cell_of(g, u, key));
     int lo = (int)(c.pc & 0xffffffffll);
     const int cnt = (int)(c.pc >> 32);
     int hi = lo + cnt;

@@ -53,13 +53,7 @@ constexpr int BM_PROBE = 4;
 
 // level 2: the grid cell of (u, qe); a query for an unknown uuid reads cell 0 and is masked later
 __device__ __forceinline__ const ThCell *k2_cell_of(const ThGrid &g, i64 n_uuids, i64 u, i64 qe) {
-    if (u < 0 || u >= n_uuids) return g.cells;
-    i64 b = 0;
-    if (qe > g.t0) {
-        const u64 d = ((u64)qe - (u64)g.t0) >> g.shift;
-        b = d < (u64)(g.nb - 1) ? (i64)d : (i64)(g.nb - 1);
-    }
-    return g.cells + (u * g.nb + b);
+    return th_cell_of(g, (u < 0 || u >= n_uuids) ? 0 : u, qe);
 }
 
 // level 3: verdict from the cell and (if needed) the bucket's rows.  The cell carries the bucket's first row, so the
@@ -230,10 +224,10 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         }
         stage_in(tile_of(it + BM_STAGES), st);
 #if BM_CELL_LD == 0
-        cell = th_ld32_if(k2_cell_of(g, n_uuids, u, qe), n_uuids > 0, ThCellV{0, 0, 0, 0});   // no uuids: no grid
+        cell = n_uuids > 0 ? th_ld32(k2_cell_of(g, n_uuids, u, qe)) : ThCellV{0, 0, 0, 0};   // no uuids: no grid
 #else
         {
-            const ThCell *cp = k2_cell_of(g, n_uuids, u, qe);
+            const ThCell *cp = n_uuids > 0 ? k2_cell_of(g, n_uuids, u, qe) : g.cells;
             const longlong2 a = th_ld16_if_off<0>(cp, n_uuids > 0, make_longlong2(0, 0));
 #if BM_CELL_LD == 1
             const longlong2 b = th_ld16_if_off<16>(cp, n_uuids > 0, make_longlong2(0, 0));

@@ -163,19 +163,52 @@ __global__ void __launch_bounds__(256) ld_sentinel_kernel(i64 n_uuids, const int
     }
 }
 
-// time grid: cells[c] = first position whose (uuid, bucket) cell is >= c.  The sentinel sits in bucket 0 of its
-// uuid, so cells[u * nb] = seg[u] and the last bucket of uuid u ends at seg[u + 1].
-__device__ __forceinline__ i64 ld_cell_of(const ThP1 *__restrict__ p1, const u32 *__restrict__ uuid, i64 pos, i64 t0,
-                                          int shift, int nb) {
+// Per-uuid grid plan: uuid u gets nb_u = about x4 / 4 cells per row of ITS rows, of power-of-two width, over ITS span of
+// starts [first real row, last real row] (rows are start-sorted, so those are positions seg[u] + 1 and seg[u + 1] - 1).
+__global__ void __launch_bounds__(256) ld_ugrid_kernel(i64 n_uuids, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
+                                                       i64 x4, ThUGrid *ug, int *nb_out) {
+    for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u < n_uuids; u += (i64)gridDim.x * blockDim.x) {
+        const int a = seg[u] + 1, b = seg[u + 1];
+        ThUGrid e;
+        e.t0 = 0; e.base = 0; e.shift = 0; e.nb = 1; e.pad = 0;
+        if (b > a) {
+            const i64 rows = b - a;
+            e.t0 = p1[a].start;
+            const u64 span = (u64)p1[b - 1].start - (u64)e.t0;
+            i64 target = (x4 * rows + 3) / 4;
+            if (target < 1) target = 1;
+            int shift = 0;
+            while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
+            e.shift = shift;
+            e.nb = (int)((span >> shift) + 1);
+        }
+        ug[u] = e;
+        nb_out[u] = e.nb;
+    }
+}
+__global__ void __launch_bounds__(256) ld_ugrid_base_kernel(i64 n_uuids, const i64 *__restrict__ base, ThUGrid *ug) {
+    for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u < n_uuids; u += (i64)gridDim.x * blockDim.x)
+        ug[u].base = base[u];
+}
+
+// time grid: first[c] = first position whose cell is >= c.  The sentinel sits in bucket 0 of its uuid, so
+// first[base_u] = seg[u] and the last bucket of uuid u ends at seg[u + 1].
+__device__ __forceinline__ i64 ld_cell_of(const ThP1 *__restrict__ p1, const u32 *__restrict__ uuid,
+                                          const ThUGrid *__restrict__ ug, i64 pos) {
     const i64 s = p1[pos].start;
-    const i64 b = s == TH_I64_MIN ? 0 : (i64)(((u64)s - (u64)t0) >> shift);
-    return (i64)uuid[pos] * nb + b;
+    const ThUGrid e = ug[uuid[pos]];
+    i64 b = 0;
+    if (s != TH_I64_MIN && s > e.t0) {
+        const u64 d = ((u64)s - (u64)e.t0) >> e.shift;
+        b = d < (u64)(e.nb - 1) ? (i64)d : (i64)(e.nb - 1);
+    }
+    return e.base + b;
 }
 __global__ void __launch_bounds__(256) ld_grid_kernel(const ThP1 *__restrict__ p1, const u32 *__restrict__ uuid, i64 nt,
-                                                      i64 n_cells, i64 t0, int shift, int nb, int *first) {
+                                                      i64 n_cells, const ThUGrid *__restrict__ ug, int *first) {
     for (i64 pos = (i64)blockIdx.x * blockDim.x + threadIdx.x; pos < nt; pos += (i64)gridDim.x * blockDim.x) {
-        const i64 cur = ld_cell_of(p1, uuid, pos, t0, shift, nb);
-        const i64 prev = pos > 0 ? ld_cell_of(p1, uuid, pos - 1, t0, shift, nb) : -1;
+        const i64 cur = ld_cell_of(p1, uuid, ug, pos);
+        const i64 prev = pos > 0 ? ld_cell_of(p1, uuid, ug, pos - 1) : -1;
         for (i64 c = prev + 1; c <= cur; ++c) first[c] = (int)pos;
         if (pos == nt - 1)
             for (i64 c = cur + 1; c <= n_cells; ++c) first[c] = (int)nt;
@@ -183,15 +216,19 @@ __global__ void __launch_bounds__(256) ld_grid_kernel(const ThP1 *__restrict__ p
 }
 // first[] -> 32-byte cells {pos, cnt, m1 of the row before the bucket (same uuid) or INT64_MIN, first row {start, m1}}
 __global__ void __launch_bounds__(256) ld_cells_kernel(const int *__restrict__ first, const ThP1 *__restrict__ p1,
-                                                       i64 n_cells, int nb, ThCell *cells) {
+                                                       i64 n_cells, ThCell *cells) {
     for (i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x; c < n_cells; c += (i64)gridDim.x * blockDim.x) {
         ThCell x;
         x.pos = first[c];
         x.cnt = first[c + 1] - x.pos;
-        x.m1_before = (c % nb == 0) ? TH_I64_MIN : p1[x.pos - 1].m1;   // bucket 0 starts at the sentinel
         x.start0 = TH_I64_MAX;                                          // empty bucket: no row before any key
+        ThP1 r; r.start = TH_I64_MAX; r.m1 = 0;
+        if (x.cnt > 0) r = p1[x.pos];
+        // bucket 0 of a uuid starts at its sentinel (start = INT64_MIN, reserved): nothing of this uuid lies before it;
+        // every other bucket -- empty ones included -- is preceded by a position of the same uuid
+        x.m1_before = (x.cnt > 0 && r.start == TH_I64_MIN) ? TH_I64_MIN : p1[x.pos - 1].m1;
         x.m1_0 = x.m1_before;
-        if (x.cnt > 0) { const ThP1 r = p1[x.pos]; x.start0 = r.start; x.m1_0 = r.m1; }
+        if (x.cnt > 0) { x.start0 = r.start; x.m1_0 = r.m1; }
         cells[c] = x;
     }
 }
@@ -416,18 +453,6 @@ __global__ void __launch_bounds__(256) dl_append_kernel(i64 n_up, i64 base, cons
 
 }  // namespace
 
-// time grid: power-of-two bucket width chosen for ~1.5 cells per row (TH_GRID_CELLS_PER_ROW_X4 / 4)
-static void ld_grid_plan(i64 n, i64 n_uuids, u64 span, int *shift_out, i64 *nb_out) {
-    i64 x4 = 6;
-    if (const char *env = getenv("TH_GRID_CELLS_PER_ROW_X4")) { x4 = atoll(env); if (x4 < 1) x4 = 1; if (x4 > 64) x4 = 64; }
-    i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
-    if (target < 1) target = 1;
-    int shift = 0;
-    while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
-    *shift_out = shift;
-    *nb_out = (i64)(span >> shift) + 1;
-}
-
 // `presorted` >= 0: rows [0, presorted) are already in (uuid, start, id) order (th_snapshot_apply_delta hands over
 // the survivors of the source snapshot that way); only the rows behind them are sorted, then the two runs are merged.
 static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_t *id, const int64_t *uuid_id,
@@ -507,15 +532,6 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         TH_REQUIRE(stats.min_start > TH_I64_MIN, "th_snapshot_load: start_us == INT64_MIN is reserved");
         min_start = stats.min_start;
         max_start = stats.max_start;
-        {   // the time grid must fit too, and that is known now: refuse before the handle is touched
-            int gs = 0;
-            i64 gnb = 1;
-            ld_grid_plan(n, n_uuids, (u64)max_start - (u64)min_start, &gs, &gnb);
-            TH_REQUIRE(n_uuids * gnb < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)",
-                       (long long)(n_uuids * gnb));
-        }
-        new_max_id = stats.max_id;
-
         ThRec *ra = nullptr, *rb = nullptr;
         TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));
         TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * zn));
@@ -603,11 +619,27 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             sc_fix_kernel<<<grid_nt, SC_THREADS, 0, st>>>(h->uuid, h->seg, nt, agg, h->p1, h->p2, h->p4);
             TH_CUDA(cudaGetLastError());
         }
-        // 5. time grid
-        int shift = 0;
-        i64 nb = 1;
-        ld_grid_plan(n, n_uuids, (u64)max_start - (u64)min_start, &shift, &nb);
-        const i64 n_cells = n_uuids * nb;
+        // 5. time grid, one per uuid: plan -> scan of the cell counts -> cells
+        i64 x4 = 6;
+        if (const char *env = getenv("TH_GRID_CELLS_PER_ROW_X4")) { x4 = atoll(env); if (x4 < 1) x4 = 1; if (x4 > 5) x4 = x4 > 64 ? 64 : x4; }
+        if (h->ugrid == nullptr || n_uuids > h->cap_ugrid) {
+            if (h->ugrid) { TH_CUDA(cudaFree(h->ugrid)); h->ugrid = nullptr; }
+            TH_CUDA(cudaMalloc((void **)&h->ugrid, sizeof(ThUGrid) * (size_t)(n_uuids > 0 ? n_uuids : 1)));
+            h->cap_ugrid = n_uuids > 0 ? n_uuids : 1;
+        }
+        int *nb_u = nullptr;
+        i64 *base = nullptr, *totals = nullptr;
+        TH_TRY(sc.alloc((void **)&nb_u, sizeof(int) * (size_t)(n_uuids > 0 ? n_uuids : 1)));
+        TH_TRY(sc.alloc((void **)&base, 8 * (size_t)(n_uuids + 1)));
+        TH_TRY(sc.alloc((void **)&totals, 16));
+        ld_ugrid_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, x4, h->ugrid, nb_u);
+        TH_CUDA(cudaGetLastError());
+        TH_TRY(th_exclusive_scan_i32(nb_u, n_uuids, base, totals, sc, st));
+        ld_ugrid_base_kernel<<<ugrid, 256, 0, st>>>(n_uuids, base, h->ugrid);
+        i64 tot[2] = {0, 0};
+        TH_CUDA(cudaMemcpyAsync(tot, totals, 16, cudaMemcpyDeviceToHost, st));
+        TH_CUDA(cudaStreamSynchronize(st));
+        const i64 n_cells = tot[0];
         TH_REQUIRE(n_cells < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)", (long long)n_cells);
         int *first = nullptr;
         TH_TRY(sc.alloc((void **)&first, sizeof(int) * (size_t)(n_cells + 1)));
@@ -616,13 +648,13 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             TH_CUDA(cudaMalloc((void **)&h->grid, sizeof(ThCell) * (size_t)(n_cells > 0 ? n_cells : 1)));
             h->cap_cells = n_cells > 0 ? n_cells : 1;
         }
-        bytes += sizeof(ThCell) * (size_t)h->cap_cells;
-        h->grid_t0 = min_start; h->grid_shift = shift; h->grid_nb = (int)nb;
-        ld_grid_kernel<<<grid_nt, 256, 0, st>>>(h->p1, h->uuid, nt, n_cells, min_start, shift, (int)nb, first);
-        ld_cells_kernel<<<th_grid_for(n_cells, 256 * 4, 8), 256, 0, st>>>(first, h->p1, n_cells, (int)nb, h->grid);
+        bytes += sizeof(ThCell) * (size_t)h->cap_cells + sizeof(ThUGrid) * (size_t)h->cap_ugrid;
+        h->n_cells = n_cells;
+        ld_grid_kernel<<<grid_nt, 256, 0, st>>>(h->p1, h->uuid, nt, n_cells, h->ugrid, first);
+        ld_cells_kernel<<<th_grid_for(n_cells, 256 * 4, 8), 256, 0, st>>>(first, h->p1, n_cells, h->grid);
         TH_CUDA(cudaGetLastError());
     } else {
-        h->grid_t0 = 0; h->grid_shift = 0; h->grid_nb = 1;
+        h->n_cells = 0;
     }
     TH_CUDA(cudaStreamSynchronize(st));
     h->radix_passes = passes_total;

@@ -17,7 +17,8 @@ lib = native.load()
 N = int(os.environ.get('TH_SWEEP_N', '1000000'))
 U = int(os.environ.get('TH_SWEEP_U', '4096'))
 M = int(os.environ.get('TH_SWEEP_M', '1000000'))
-cal = synth.make_calendar(N, U, seed=20260102)
+SKEW = float(os.environ.get('TH_SWEEP_SKEW', '0'))      # > 0: Zipf-like uuid popularity (hot GPUs hold most rows)
+cal = synth.make_calendar(N, U, seed=20260102, skew=SKEW)
 q = synth.make_queries(cal, M, seed=20260103)
 if os.environ.get('TH_SWEEP_NOSELF'):
     q['self_id'][:] = -1
