@@ -395,6 +395,23 @@ def run_ours(args):
             reps.append(a.elapsed_time(b) / 8.0)
         k_ms_stream = float(np.median(reps))
         del batches, outs_b
+    # K2 on a calendar with Zipf-skewed uuid popularity (a quarter of all rows on the hottest GPU): the load gives every
+    # uuid its own time grid there, so hot uuids do not fall back to long bisections
+    k_ms_skew = None
+    if dist is None and N_ROWS == 1_000_000:
+        cal_s = synth.make_calendar(N_ROWS, N_UUIDS, seed=SEED + 11, skew=1.2)
+        q_s = synth.make_queries(cal_s, N_QUERIES, seed=SEED + 12)
+        snap_s = th.Snapshot(local)
+        snap_s.load(cal_s['id'], cal_s['uuid_id'], cal_s['start'], cal_s['end'], cal_s['owner'], cal_s['cancelled'],
+                    n_uuids=N_UUIDS)
+        qs_d = [tdev(q_s[k]) for k in ('uuid_id', 'start', 'end', 'self_id')]
+
+        def k2_skew():
+            native.check(lib.th_conflict_bitmap(snap_s._h, N_QUERIES, qs_d[0].data_ptr(), qs_d[1].data_ptr(),
+                                                qs_d[2].data_ptr(), qs_d[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+        k_ms_skew = float(np.mean(timed(k2_skew, 10)))
+        snap_s.close()
+        del qs_d, cal_s, q_s
     peak, peak_src = _peaks()
     alg_bytes = N_QUERIES * 32 + N_ROWS * 25 + 8 * (N_UUIDS + 1) + N_QUERIES // 8
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
@@ -507,6 +524,7 @@ def run_ours(args):
                          'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes, 'kernel_ms': k_ms, 'kernel_ms_warm_l2': k_ms_warm,
                          'kernel_ms_streaming_8_batches_no_flush': k_ms_stream,
+                         'kernel_ms_zipf_skewed_calendar': k_ms_skew,
                          'frac_of_nominal_8TBs': achieved / 8000.0},
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
                               'ms_apply_delta_1000_rows_host_arrays': float(np.median(dl[1:])),
@@ -742,6 +760,81 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
         cpu = {'value': n_samples / dt, 'unit': 'samples/s', 'cores': 1, 'kind': 'port',
                'sample': '%d windows (%d samples) of in-memory Python lists; the reference additionally re-reads and '
                          're-writes each JSON log on every tick' % (len(lists), n_samples)}
+    # ---- the device-resident sample ring (th_ring_*) at 1/8 of config 3: ticks appended as a monitor would, then the
+    # same windows reduced from a ring whose stamps lie on an exact grid (run-length timestamps: the ts column is never
+    # read) and from one with jittered stamps (probed), against th_usage_reduce_u8 over plain columns
+    ring = None
+    if world == 1:
+        import ctypes as C
+        RU, RSPU, RW, BATCH = 8192, S_PER_UUID, S_WINDOWS // 8, 1024
+        rng = np.random.default_rng(SEED + 5)
+        rw = [i64(RW) for _ in range(3)]
+        native.check(lib.th_synth_windows(local, RU, RSPU, synth.T0_US, SEED + 6, RW, rw[0].data_ptr(), rw[1].data_ptr(),
+                                          rw[2].data_ptr(), sp))
+        rings, tick_ms, cols = {}, [], {}
+        for kind in ('regular', 'jittered'):
+            h = C.c_void_p(0)
+            native.check(lib.th_ring_create(local, RSPU, C.byref(h)))
+            parts = {'ts': [], 'g': [], 'm': []}
+            for t0_ in range(0, RSPU, BATCH):
+                nt_ = min(BATCH, RSPU - t0_)
+                uu = np.tile(np.arange(RU, dtype=np.int64), nt_)                      # tick-major, as a monitor reports
+                ts_ = np.repeat(synth.T0_US + (t0_ + np.arange(nt_, dtype=np.int64)) * 1_000_000, RU)
+                if kind == 'jittered':
+                    ts_ = ts_ + rng.integers(0, 900_000, size=ts_.size)
+                g_ = rng.integers(0, 101, size=ts_.size).astype(np.uint8)
+                m_ = rng.integers(0, 101, size=ts_.size).astype(np.uint8)
+                a0 = time.perf_counter()
+                native.check(lib.th_ring_append(h, uu.size, uu.ctypes.data, ts_.ctypes.data, g_.ctypes.data, m_.ctypes.data, None))
+                tick_ms.append(1e3 * (time.perf_counter() - a0) / nt_)
+                for k_, v_ in (('ts', ts_), ('g', g_), ('m', m_)):
+                    parts[k_].append(v_.reshape(nt_, RU))
+            rings[kind] = h
+            cols[kind] = [torch.from_numpy(np.ascontiguousarray(np.concatenate(parts[k_]).T).reshape(-1)).to(dev)
+                          for k_ in ('ts', 'g', 'm')]                               # uuid-major CSR columns of the same log
+            del parts
+        r_off = torch.arange(RU + 1, dtype=torch.int64, device=dev) * RSPU
+        r_out = {k_: [i64(RW) for _ in range(5)] for k_ in ('regular', 'jittered', 'plain')}
+
+        def ring_step(kind):
+            native.check(lib.th_ring_reduce(rings[kind], RW, rw[0].data_ptr(), rw[1].data_ptr(), rw[2].data_ptr(),
+                                            *[o.data_ptr() for o in r_out[kind]], 1, sp))
+
+        def plain_step(kind):
+            c_ = cols[kind]
+            native.check(lib.th_usage_reduce_u8(local, RU * RSPU, RU, r_off.data_ptr(), c_[0].data_ptr(), c_[1].data_ptr(),
+                                                c_[2].data_ptr(), RW, rw[0].data_ptr(), rw[1].data_ptr(), rw[2].data_ptr(),
+                                                *[o.data_ptr() for o in r_out['plain']], 1, sp))
+
+        def med_ms(fn):
+            for _ in range(3):
+                fn()
+            ev = []
+            for _ in range(10):
+                flush.sum()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream); fn(); b.record(stream)
+                ev.append((a, b))
+            torch.cuda.synchronize()
+            return float(np.median([a.elapsed_time(b) for a, b in ev]))
+
+        res = {}
+        for kind in ('regular', 'jittered'):
+            res[kind] = {'ring_ms': med_ms(lambda: ring_step(kind)), 'plain_columns_ms': med_ms(lambda: plain_step(kind))}
+            torch.cuda.synchronize()
+            res[kind]['identical_to_th_usage_reduce_u8'] = all(bool(torch.equal(x, y)) for x, y in
+                                                               zip(r_out[kind], r_out['plain']))
+        info = [C.c_int64(0) for _ in range(6)]
+        native.check(lib.th_ring_info(rings['regular'], *[C.byref(x) for x in info]))
+        ring = {'samples': RU * RSPU, 'uuids': RU, 'windows': RW, 'append_ms_per_tick_of_8192_samples': float(np.median(tick_ms)),
+                'relayouts': info[5].value, 'regular_uuids': info[4].value, 'device_bytes': info[3].value,
+                'regular_stamps': res['regular'], 'jittered_stamps': res['jittered'],
+                'note': '1/8 of config 3, appended through th_ring_append in batches of 1024 ticks; th_ring_reduce reads the ring in '
+                        'place (device window arrays in, device results out); with stamps on an exact grid both window ends '
+                        'come from divisions and the ts column is not read'}
+        for h in rings.values():
+            lib.th_ring_destroy(h)
+        del cols, r_out
     traffic = _traffic('k4_usage_kernel')
     return {'metric': 'usage_reduce_GB_per_s', 'value': world * gbs_survey, 'unit': 'GB/s', 'ms_per_step': ms,
             'value_note': 'SURVEY 8d definition: 24 B per logged sample (ts, gpu_util, mem_util) / time; above the HBM peak '
@@ -763,6 +856,7 @@ def bench_usage(torch, lib, native, dev, local, sp, stream, flush, steps, warmup
                                  'slowdown_vs_sorted_windows': ms_shuffled / ms, 'results_identical': shuffled_same,
                                  'note': 'the same 10M windows in random order (as a reservation table in id order would '
                                          'present them) instead of grouped by uuid with increasing starts'},
+            'sample_ring': ring,
             'narrow_u8': {'ms_per_step': ms8, 'samples_per_s': world * s_total / (ms8 * 1e-3),
                           'speedup_vs_int64_columns': ms / ms8, 'results_identical_to_int64_path': same,
                           'roofline': {'kernel': 'k4_usage_u8_kernel', 'bound': 'hbm', 'achieved': gbs8, 'peak': peak,

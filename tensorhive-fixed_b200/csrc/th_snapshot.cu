@@ -165,8 +165,11 @@ __global__ void __launch_bounds__(256) ld_sentinel_kernel(i64 n_uuids, const int
 
 // Per-uuid grid plan: uuid u gets nb_u = about x4 / 4 cells per row of ITS rows, of power-of-two width, over ITS span of
 // starts [first real row, last real row] (rows are start-sorted, so those are positions seg[u] + 1 and seg[u + 1] - 1).
+// Also accumulates, in *crowd, sum over uuids of rows_u^2 / (buckets uuid u would occupy under the SHARED plan): divided by
+// n that is the number of rows a random row shares its bucket with -- ~1 on a balanced calendar, hundreds when a few hot
+// uuids hold most rows or one uuid's span dwarfs the others'.
 __global__ void __launch_bounds__(256) ld_ugrid_kernel(i64 n_uuids, const int *__restrict__ seg, const ThP1 *__restrict__ p1,
-                                                       i64 x4, ThUGrid *ug, int *nb_out) {
+                                                       i64 x4, int shared_shift, ThUGrid *ug, int *nb_out, double *crowd) {
     for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u < n_uuids; u += (i64)gridDim.x * blockDim.x) {
         const int a = seg[u] + 1, b = seg[u + 1];
         ThUGrid e;
@@ -181,9 +184,18 @@ __global__ void __launch_bounds__(256) ld_ugrid_kernel(i64 n_uuids, const int *_
             while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
             e.shift = shift;
             e.nb = (int)((span >> shift) + 1);
+            const double used = (double)(span >> shared_shift) + 1.0;
+            atomicAdd(crowd, (double)rows * (double)rows / used);
         }
         ug[u] = e;
         nb_out[u] = e.nb;
+    }
+}
+__global__ void __launch_bounds__(256) ld_ugrid_shared_kernel(i64 n_uuids, i64 t0, int shift, int nb, ThUGrid *ug) {
+    for (i64 u = (i64)blockIdx.x * blockDim.x + threadIdx.x; u < n_uuids; u += (i64)gridDim.x * blockDim.x) {
+        ThUGrid e;
+        e.t0 = t0; e.base = u * nb; e.shift = shift; e.nb = nb; e.pad = 0;
+        ug[u] = e;
     }
 }
 __global__ void __launch_bounds__(256) ld_ugrid_base_kernel(i64 n_uuids, const i64 *__restrict__ base, ThUGrid *ug) {
@@ -532,6 +544,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         TH_REQUIRE(stats.min_start > TH_I64_MIN, "th_snapshot_load: start_us == INT64_MIN is reserved");
         min_start = stats.min_start;
         max_start = stats.max_start;
+        new_max_id = stats.max_id;
         ThRec *ra = nullptr, *rb = nullptr;
         TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * zn));
         TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * zn));
@@ -629,17 +642,44 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         }
         int *nb_u = nullptr;
         i64 *base = nullptr, *totals = nullptr;
+        double *crowd = nullptr;
         TH_TRY(sc.alloc((void **)&nb_u, sizeof(int) * (size_t)(n_uuids > 0 ? n_uuids : 1)));
         TH_TRY(sc.alloc((void **)&base, 8 * (size_t)(n_uuids + 1)));
         TH_TRY(sc.alloc((void **)&totals, 16));
-        ld_ugrid_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, x4, h->ugrid, nb_u);
+        TH_TRY(sc.alloc((void **)&crowd, sizeof(double)));
+        TH_CUDA(cudaMemsetAsync(crowd, 0, sizeof(double), st));
+        // the shared plan: one power-of-two width for all uuids over the global span, ~x4 / 4 cells per average row count
+        int s_shift = 0;
+        i64 s_nb = 1;
+        {
+            const u64 span = (u64)max_start - (u64)min_start;
+            i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
+            if (target < 1) target = 1;
+            while (s_shift < 63 && (i64)(span >> s_shift) + 1 > target) ++s_shift;
+            s_nb = (i64)(span >> s_shift) + 1;
+        }
+        ld_ugrid_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, x4, s_shift, h->ugrid, nb_u, crowd);
         TH_CUDA(cudaGetLastError());
         TH_TRY(th_exclusive_scan_i32(nb_u, n_uuids, base, totals, sc, st));
         ld_ugrid_base_kernel<<<ugrid, 256, 0, st>>>(n_uuids, base, h->ugrid);
         i64 tot[2] = {0, 0};
+        double crowd_h = 0.0;
         TH_CUDA(cudaMemcpyAsync(tot, totals, 16, cudaMemcpyDeviceToHost, st));
+        TH_CUDA(cudaMemcpyAsync(&crowd_h, crowd, sizeof(double), cudaMemcpyDeviceToHost, st));
         TH_CUDA(cudaStreamSynchronize(st));
-        const i64 n_cells = tot[0];
+        i64 n_cells = tot[0];
+        // balanced calendar (a random row shares its bucket with < 3 rows under the shared plan): keep the shared plan
+        const char *force = getenv("TH_GRID_PLAN");           // diagnostics: "shared" / "per_uuid"
+        bool shared = n > 0 && crowd_h / (double)n < 3.0 && n_uuids * s_nb < (1ll << 31) - 1;
+        if (force && force[0] == 's' && n_uuids * s_nb < (1ll << 31) - 1) shared = true;
+        if (force && force[0] == 'p') shared = false;
+        h->grid_t0 = 0; h->grid_shift = 0; h->grid_nb = 0;
+        if (shared) {
+            ld_ugrid_shared_kernel<<<ugrid, 256, 0, st>>>(n_uuids, min_start, s_shift, (int)s_nb, h->ugrid);
+            TH_CUDA(cudaGetLastError());
+            n_cells = n_uuids * s_nb;
+            h->grid_t0 = min_start; h->grid_shift = s_shift; h->grid_nb = (int)s_nb;
+        }
         TH_REQUIRE(n_cells < (1ll << 31) - 1, "th_snapshot_load: time grid too large (%lld cells)", (long long)n_cells);
         int *first = nullptr;
         TH_TRY(sc.alloc((void **)&first, sizeof(int) * (size_t)(n_cells + 1)));
@@ -655,6 +695,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         TH_CUDA(cudaGetLastError());
     } else {
         h->n_cells = 0;
+        h->grid_t0 = 0; h->grid_shift = 0; h->grid_nb = 0;
     }
     TH_CUDA(cudaStreamSynchronize(st));
     h->radix_passes = passes_total;

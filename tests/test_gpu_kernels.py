@@ -645,3 +645,32 @@ def test_packed_queries_give_identical_bitmaps(th, synth, brute, m):
     incl = snap.conflict_words(q['uuid_id'], q['start'], q['end'], None, th.MODE_INCLUSIVE)
     assert np.array_equal(snap.conflict_words_packed(pu, q['start'], q['end'], None, th.MODE_INCLUSIVE), incl)
     snap.close()
+
+
+@pytest.mark.parametrize('plan', ['shared', 'per_uuid'])
+@pytest.mark.parametrize('skew', [0.0, 1.5])
+def test_both_grid_plans_give_the_same_answers(th, synth, brute, monkeypatch, plan, skew):
+    """The time grid has two plans -- one bucket width for all uuids (balanced calendars) or one per uuid (hot GPUs, uuids
+    with very different spans); the load picks by itself, TH_GRID_PLAN forces one.  Every search goes through it."""
+    monkeypatch.setenv('TH_GRID_PLAN', plan)
+    cal = synth.make_calendar(60_000, 48, seed=77, skew=skew)
+    cal['start'][:50] -= 400 * synth.DAY_US            # a few outliers stretch one uuid's span far into the past
+    cal['end'][:50] -= 400 * synth.DAY_US
+    q = synth.make_queries(cal, 40_000, seed=78)
+    snap = _load(th, cal)
+    assert np.array_equal(snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], q['self_id']),
+                          brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id']))
+    assert np.array_equal(snap.conflict_bitmap(q['uuid_id'], q['start'], q['end'], None, th.MODE_INCLUSIVE),
+                          brute.conflict_bits(cal, q['uuid_id'], q['start'], q['end'], q['self_id'], brute.INCLUSIVE))
+    some = slice(0, 3000)
+    off, ids, _c = snap.conflict_sets(q['uuid_id'][some], q['start'][some], q['end'][some], q['self_id'][some])
+    assert csr_to_lists(off, ids) == brute.conflict_sets(cal, q['uuid_id'][some], q['start'][some], q['end'][some],
+                                                         q['self_id'][some], brute.STRICT)
+    now = int(np.median(cal['start']))
+    res, own = snap.current_owner(now)
+    want_res, want_own = brute.current_owner(cal, 48, now)
+    assert np.array_equal(res, want_res) and np.array_equal(own, want_own)
+    got = snap.upcoming(now, 30 * synth.MIN_US, np.arange(48, dtype=np.int64))
+    want = brute.upcoming_summary(cal, np.arange(48, dtype=np.int64), now, 30 * synth.MIN_US)
+    assert all(np.array_equal(a, b) for a, b in zip(got, want))
+    snap.close()
