@@ -525,7 +525,10 @@ def run_ours(args):
                          'algorithmic_bytes_per_launch': alg_bytes, 'kernel_ms': k_ms, 'kernel_ms_warm_l2': k_ms_warm,
                          'kernel_ms_streaming_8_batches_no_flush': k_ms_stream,
                          'kernel_ms_zipf_skewed_calendar': k_ms_skew,
-                         'frac_of_nominal_8TBs': achieved / 8000.0},
+                         'frac_of_nominal_8TBs': achieved / 8000.0,
+                         'what_bounds_it': 'the number of scattered L2 fills, not their bytes: 1.215 probe fills + 0.25 stream line '
+                                           'fills per query against ~46 G fills/s out of HBM on B200 (profiles/r2_random_access_rate.md); '
+                                           'at one fill per query the byte fraction could reach 0.36 at most'},
             'snapshot_load': {'ms_device_columns': float(np.median(ld)), 'ms_first_from_host': load_ms_host,
                               'ms_apply_delta_1000_rows_host_arrays': float(np.median(dl[1:])),
                               'radix_passes': info['radix_passes'], 'device_bytes': info['device_bytes']}}

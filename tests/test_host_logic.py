@@ -196,3 +196,30 @@ def test_bulk_load_from_columns_equals_the_row_wise_load(dropin):
     with pytest.raises(KeyError):
         b.rows_for([5])
     assert b.rows_for([3])[0].resource_id == g1
+
+
+def test_global_calendar_is_defined_chunk_by_chunk():
+    """synth.GlobalCalendar (what bench.py's config-5 share and its all-ranks parity check are built on): any process can
+    materialise any chunk, chunks are deterministic, ids unique across chunks, uuid codes inside the chunk's range, and the
+    partition by estimated rows per uuid balances the ranks."""
+    from tensorhive_fixed_b200 import synth, sharding
+    g = synth.GlobalCalendar(200_000, 2048, seed=5, chunk_uuids=256)
+    assert g.n_chunks == 8 and g.n_rows == 200_000 and int(g.chunk_rows.sum()) == 200_000
+    assert g.chunk_rows.min() > 0.6 * 25_000 and g.chunk_rows.max() < 1.4 * 25_000
+    a, b = g.chunk(3), g.chunk(3)
+    assert all(np.array_equal(a[k], b[k]) for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled'))
+    ids = np.concatenate([g.chunk(c)['id'] for c in range(g.n_chunks)])
+    assert len(np.unique(ids)) == 200_000 and ids.min() == 1 and ids.max() == 200_000
+    for c in (0, 5, 7):
+        u = g.chunk(c)['uuid_id']
+        assert u.min() >= c * 256 and u.max() < (c + 1) * 256
+    bounds = sharding.partition_uuids(g.rows_per_uuid_estimate(), 4)
+    assert bounds[0] == 0 and bounds[-1] == 2048 and np.all(np.diff(bounds) > 0)
+    rows = [sum(int((sharding.owner_rank(g.chunk(c)['uuid_id'], bounds) == r).sum()) for c in range(g.n_chunks)) for r in range(4)]
+    assert sum(rows) == 200_000 and max(rows) < 1.05 * 50_000
+    assert list(g.chunks_overlapping(int(bounds[1]), int(bounds[2]))) == list(range(int(bounds[1]) // 256, (int(bounds[2]) - 1) // 256 + 1))
+    q = g.chunk_queries(2, 5000, seed=9, unknown_frac=0.02)
+    known = q['uuid_id'] < 2048
+    assert (~known).any() and q['uuid_id'][known].min() >= 512 and q['uuid_id'][known].max() < 768
+    # queries of a chunk are routed to the ranks that own its uuids, unknown resources to rank 0
+    assert set(np.unique(sharding.owner_rank(q['uuid_id'][~known], bounds))) == {0}
