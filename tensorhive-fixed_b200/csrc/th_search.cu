@@ -465,7 +465,11 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64
                                                                  const int *__restrict__ beg_arr,
                                                                  const int *__restrict__ end_arr,
                                                                  const i64 *__restrict__ offsets,
-                                                                 i64 *__restrict__ out_ids, u8 *__restrict__ out_canc) {
+                                                                 i64 *__restrict__ out_ids, u8 *__restrict__ out_canc,
+                                                                 const i64 *__restrict__ totals = nullptr, i64 capacity = 0) {
+    // launched before the host has seen the totals (one synchronisation per call instead of two): nothing is written
+    // when the result does not fit the caller's buffers
+    if (totals != nullptr && totals[0] > capacity) return;
     const int lane = threadIdx.x & 31, gl = lane & (G - 1);
     const u32 gmask = cs_gmask<G>(lane);
     const i64 gstride = (i64)gridDim.x * (CS_THREADS / G);
@@ -502,7 +506,10 @@ template <int G>
 __global__ void __launch_bounds__(CS_THREADS) k2_sets_order_kernel(i64 m, const i64 *__restrict__ offsets,
                                                                   const i64 *__restrict__ tmp_ids,
                                                                   const u8 *__restrict__ tmp_canc,
-                                                                  i64 *__restrict__ out_ids, u8 *__restrict__ out_canc) {
+                                                                  i64 *__restrict__ out_ids, u8 *__restrict__ out_canc,
+                                                                  const i64 *__restrict__ totals = nullptr, i64 capacity = 0) {
+    // (speculative launch: skipped when the result does not fit or a list is long enough to want the radix sort)
+    if (totals != nullptr && (totals[0] > capacity || totals[1] > 64)) return;
     const int gl = threadIdx.x & (G - 1);
     const i64 gstride = (i64)gridDim.x * (CS_THREADS / G);
     for (i64 q = (i64)blockIdx.x * (CS_THREADS / G) + (threadIdx.x / G); q < m; q += gstride) {
@@ -855,6 +862,37 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     i64 *d_total;
     TH_TRY(sc.alloc((void **)&d_total, 16));       // [0] = total rows, [1] = longest list
     TH_TRY(th_exclusive_scan_i32(d_cnt, m, (i64 *)d_off, d_total, sc, st));
+    // Device arrays: fill (and rank short lists) speculatively, guarded on the device by the totals, so that the call has
+    // ONE host synchronisation in the common case; the radix path for long lists and the host-array path (whose copies
+    // need the total) keep the second one.
+    const bool spec = mem == TH_MEM_DEVICE && capacity > 0 && m < (1ll << 32) && capacity < (1ll << 30);
+    i64 *sp_ids = nullptr;
+    u8 *sp_canc = nullptr;
+    if (spec) {
+        if (mode == TH_MODE_UPCOMING) {
+            if (narrow)
+                k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                     (const i64 *)d_off, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
+            else
+                k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                      (const i64 *)d_off, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
+        } else {
+            TH_TRY(sc.alloc((void **)&sp_ids, 8 * (size_t)capacity));
+            TH_TRY(sc.alloc((void **)&sp_canc, (size_t)capacity));
+            if (narrow) {
+                k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                     (const i64 *)d_off, sp_ids, sp_canc, (const i64 *)d_total, (i64)capacity);
+                k2_sets_order_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, sp_ids, sp_canc, (i64 *)out_ids,
+                                                                      (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
+            } else {
+                k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
+                                                                      (const i64 *)d_off, sp_ids, sp_canc, (const i64 *)d_total, (i64)capacity);
+                k2_sets_order_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, sp_ids, sp_canc, (i64 *)out_ids,
+                                                                      (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
+            }
+        }
+        TH_CUDA(cudaGetLastError());
+    }
     i64 tot2[2] = {0, 0};
     TH_CUDA(cudaMemcpyAsync(tot2, d_total, 16, cudaMemcpyDeviceToHost, st));
     TH_TRY(th_copy_back(out_offsets, d_off, 8 * (zm + 1), mem, st));
@@ -866,6 +904,21 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
         return TH_ECAPACITY;
     }
     if (total == 0) return TH_OK;
+    if (spec) {
+        if (mode == TH_MODE_UPCOMING || longest <= 64) return TH_OK;          // everything was written before the synchronisation
+        // long lists: the speculative fill has left (start, id)-ordered rows in sp_ids / sp_canc; sort them by (query, id)
+        ThRec *ra, *rb, *sorted;
+        TH_TRY(sc.alloc((void **)&ra, sizeof(ThRec) * (size_t)total));
+        TH_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * (size_t)total));
+        k2_sets_rec_kernel<<<wgrid, 256, 0, st>>>(m, (const i64 *)d_off, sp_ids, ra);
+        TH_CUDA(cudaGetLastError());
+        int passes = 0;
+        TH_TRY(th_radix_sort(ra, rb, total, th_bits_for((u64)h->max_id), th_bits_for((u64)(m - 1)), &sorted, &passes, st));
+        k2_sets_unrec_kernel<<<th_grid_for(total, 256 * 4, 8), 256, 0, st>>>(total, sorted, sp_canc, (i64 *)out_ids, (u8 *)out_cancelled_u8);
+        TH_CUDA(cudaGetLastError());
+        TH_CUDA(cudaStreamSynchronize(st));
+        return TH_OK;
+    }
     void *d_ids, *d_canc;
     TH_TRY(sc.out(out_ids, 8 * (size_t)total, mem, &d_ids));
     TH_TRY(sc.out(out_cancelled_u8, (size_t)total, mem, &d_canc));
