@@ -131,7 +131,8 @@ int th_conflict_bitmap_packed(const th_snapshot *h, int64_t m, const uint32_t *q
  *   TH_MODE_UPCOMING   upcoming_events_for_resource :109-118 (cancelled EXCLUDED, ORDER BY start, id)
  * If the total exceeds `capacity`, nothing is written to out_ids/out_cancelled_u8, *out_needed is the
  * required capacity and TH_ECAPACITY is returned (out_offsets is valid).  out_needed is a HOST pointer
- * in both mem modes; the call synchronises `stream`. */
+ * in both mem modes; the call synchronises `stream` (once for device arrays whose lists are short -- the fill is
+ * launched under a device-side guard before the host has seen the total --, twice otherwise). */
 int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *q_uuid, const int64_t *q_start,
                      const int64_t *q_end, const int64_t *q_self_id, int mode, int64_t *out_offsets,
                      int64_t *out_ids, uint8_t *out_cancelled_u8, int64_t capacity, int64_t *out_needed, int mem,

@@ -90,6 +90,7 @@ class Snapshot:
         self.device = int(device)
         self.n = 0
         self.n_uuids = 0
+        self._cap_hints = {}
 
     # -- lifecycle ---------------------------------------------------------------------------------
     def close(self) -> None:
@@ -199,7 +200,10 @@ class Snapshot:
         """CSR (offsets[m+1], ids, cancelled).  Retries once with the exact capacity if the guess was short."""
         a = _Args(q_uuid, q_start, q_end, q_self)
         m = int(len(q_uuid))
-        cap = int(capacity) if capacity is not None else max(64, 2 * m)
+        # first guess: two rows per query, or what a batch of this size and mode needed last time (a calendar view polls
+        # the same ranges again and again: without the memory every poll ran the count pass twice)
+        hint = self._cap_hints.get((m, int(mode)), 0)
+        cap = int(capacity) if capacity is not None else max(64, 2 * m, hint + hint // 8)
         needed = C.c_int64(0)
         for _attempt in range(2):
             offsets, op = a.out(m + 1, np.int64)
@@ -212,6 +216,8 @@ class Snapshot:
                 continue
             native.check(rc)
             total = int(needed.value)
+            if total > 2 * m:
+                self._cap_hints[(m, int(mode))] = total
             return offsets, ids[:total], canc[:total]
         raise NativeError(TH_ECAPACITY, native.last_error())
 

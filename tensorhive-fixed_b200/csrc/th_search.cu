@@ -333,9 +333,11 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         const i64 per_r = (po.recv_words + gridDim.x - 1) / gridDim.x;
         const i64 r_begin = (i64)blockIdx.x * per_r;
         const i64 r_cnt = r_begin < po.recv_words ? (r_begin + per_r < po.recv_words ? per_r : po.recv_words - r_begin) : 0;
-        for (i64 k = threadIdx.x; k < (i64)po.n * r_cnt; k += BM_THREADS) {
-            const int r = (int)(k / r_cnt);
-            const i64 j = r_begin + (k - (i64)r * r_cnt);
+        // (32-bit index arithmetic: a 64-bit division per slot cost more than the poll itself on small batches)
+        const u32 rc32 = (u32)r_cnt, total32 = (u32)po.n * rc32;
+        for (u32 k = threadIdx.x; k < total32; k += BM_THREADS) {
+            const u32 r = k / rc32;
+            const i64 j = r_begin + (k - r * rc32);
             const i64 idx = (i64)r * po.wpr + j;
             u32 w = 0;
             if (j < po.expect[r]) {
@@ -356,10 +358,9 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         }
         // slots beyond what any rank contributes this step read as 0
         const i64 tail = po.wpr - po.recv_words;
-        for (i64 k = (i64)blockIdx.x * BM_THREADS + threadIdx.x; k < (i64)po.n * tail; k += (i64)gridDim.x * BM_THREADS) {
-            const int r = (int)(k / tail);
-            po.my_out[(i64)r * po.wpr + po.recv_words + (k - (i64)r * tail)] = 0;
-        }
+        for (int r = 0; r < po.n; ++r)
+            for (i64 k = (i64)blockIdx.x * BM_THREADS + threadIdx.x; k < tail; k += (i64)gridDim.x * BM_THREADS)
+                po.my_out[(i64)r * po.wpr + po.recv_words + k] = 0;
     }
 }
 

@@ -145,6 +145,9 @@ __device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSe
 }
 
 __device__ __forceinline__ i64 us_floor_div(i64 a, i64 b) {   // b > 0; Python's //
+    // utilisation sums of a window fit 32 bits unless it holds tens of millions of samples: a 32-bit division is ~20
+    // instructions, the 64-bit one a subroutine of ~150, and every window pays two of them
+    if ((((u64)a | (u64)b) >> 32) == 0) return (i64)((u32)a / (u32)b);
     i64 q = a / b;
     if ((a % b != 0) && (a < 0)) --q;
     return q;
