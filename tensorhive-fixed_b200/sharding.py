@@ -40,9 +40,13 @@ def owner_rank(uuid_codes, bounds: np.ndarray) -> np.ndarray:
     """Rank that owns each uuid code; codes outside [0, n_uuids) (unknown resources) go to rank 0, which
     answers "no reservations" for them like any other rank would."""
     u = np.asarray(uuid_codes, np.int64)
-    r = np.searchsorted(bounds, u, side='right') - 1
     world = bounds.size - 1
-    return np.where((u < 0) | (u >= bounds[-1]), 0, np.clip(r, 0, world - 1)).astype(np.int64)
+    # a handful of comparisons against the inner boundaries (world <= 16) beats a binary search per element
+    r = np.zeros(u.shape, np.int64)
+    for b in bounds[1:world]:
+        r += u >= b
+    r[(u < 0) | (u >= bounds[-1])] = 0
+    return r
 
 
 class Router:
@@ -54,7 +58,9 @@ class Router:
         self.world = self.bounds.size - 1
         self.m = int(len(q_uuid))
         self.owner = owner_rank(q_uuid, self.bounds)
-        self.perm = np.argsort(self.owner, kind='stable')            # queries grouped by rank, input order kept
+        # queries grouped by rank, input order kept (= a stable argsort of `owner`, three times faster for a few ranks)
+        self.perm = (np.concatenate([np.flatnonzero(self.owner == r) for r in range(self.world)])
+                     if self.m else np.zeros(0, np.int64))
         self.counts = np.bincount(self.owner, minlength=self.world).astype(np.int64)
         self.offsets = np.concatenate([[0], np.cumsum(self.counts)])
         self.words_per_rank = int((self.counts.max() + 31) // 32) if self.m else 0
