@@ -91,6 +91,32 @@ cudaStream_t th_call_stream(void *stream, int mem, int device) {
     return s;
 }
 
+// ---- per-thread page-locked slab for controller-sized host calls ---------------------------------------------------
+// One would_interfere from a REST controller is 32 bytes in and 4 bytes out: staging that through five stream-ordered
+// allocations and five copies costs more than the search.  Small host-array batches are instead copied (by the CPU) into
+// a page-locked, device-mapped slab of the calling thread, which the kernel reads and writes in place: no cudaMemcpy,
+// no allocation, one launch and one synchronisation.
+namespace {
+struct ThreadSlab {
+    void *host[64];
+    ThreadSlab() { for (auto &x : host) x = nullptr; }
+    ~ThreadSlab() { for (auto x : host) if (x) cudaFreeHost(x); }
+};
+thread_local ThreadSlab g_thread_slab;
+}  // namespace
+
+void *th_thread_slab(int device, void **dev_alias) {
+    if (device < 0 || device >= 64) return nullptr;
+    void *&h = g_thread_slab.host[device];
+    if (h == nullptr && cudaHostAlloc(&h, TH_SLAB_BYTES, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        h = nullptr;
+        return nullptr;
+    }
+    if (cudaHostGetDevicePointer(dev_alias, h, 0) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return h;
+}
+
 // ---- ThScratch ---------------------------------------------------------------------------------------
 int ThScratch::alloc(void **out, size_t bytes) {
     if (count >= (int)(sizeof(ptrs) / sizeof(ptrs[0]))) {

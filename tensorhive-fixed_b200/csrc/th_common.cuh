@@ -346,6 +346,11 @@ struct DeviceGuard {
 // every other stream of the process.
 cudaStream_t th_call_stream(void *stream, int mem, int device);
 
+// page-locked, device-mapped slab of the calling thread on `device` (current), TH_SLAB_BYTES long; NULL if unavailable
+#define TH_SLAB_BYTES (64 << 10)
+#define TH_SLAB_MAX_QUERIES 1024
+void *th_thread_slab(int device, void **dev_alias);
+
 // ---- host-side scratch: stream-ordered device buffers used to stage TH_MEM_HOST calls -----------------
 struct ThScratch {
     cudaStream_t st;

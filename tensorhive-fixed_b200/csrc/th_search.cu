@@ -16,6 +16,7 @@
 // can match; a second pass re-walks the examined range forwards and compacts matches with ballots.
 #include "th_common.cuh"
 #include <stdlib.h>
+#include <string.h>
 #include <atomic>
 
 namespace {
@@ -730,6 +731,27 @@ extern "C" int th_conflict_bitmap(const th_snapshot *h, int64_t m, const int64_t
         const void *mapped[4];
         zero_copy = k2_map_pinned(cols, 4, mapped) == 1;
         if (zero_copy) { d_u = mapped[0]; d_s = mapped[1]; d_e = mapped[2]; d_f = mapped[3]; }
+    }
+    // Controller-sized batches in pageable memory: through the calling thread's page-locked slab (th_api.cu), which the
+    // kernel reads and writes in place -- no allocation, no cudaMemcpy.
+    if (!zero_copy && mem == TH_MEM_HOST && m <= TH_SLAB_MAX_QUERIES && !getenv("TH_NO_ZERO_COPY")) {
+        void *dev = nullptr;
+        char *slab = (char *)th_thread_slab(h->device, &dev);
+        if (slab != nullptr) {
+            const size_t col = (8 * zm + 15) & ~(size_t)15;
+            memcpy(slab, q_uuid, 8 * zm);
+            memcpy(slab + col, q_start, 8 * zm);
+            memcpy(slab + 2 * col, q_end, 8 * zm);
+            if (q_self_id) memcpy(slab + 3 * col, q_self_id, 8 * zm);
+            ThPeerOut none;
+            none.n = 0;
+            none.unpack = 0;
+            const char *d = (const char *)dev;
+            TH_TRY(k2_launch(h, m, d, d + col, d + 2 * col, q_self_id ? d + 3 * col : nullptr, mode, (u32 *)(d + 4 * col), none, st));
+            TH_CUDA(cudaStreamSynchronize(st));
+            memcpy(out_bits_u32, slab + 4 * col, 4 * words);
+            return TH_OK;
+        }
     }
     if (!zero_copy) {
         TH_TRY(sc.in(q_uuid, 8 * zm, mem, &d_u));
