@@ -280,25 +280,65 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     };
 #if BM_PIPE
     // Two tiles in flight per warp: the cell of tile k + 1 is requested before the rows of tile k are probed, so an
-    // iteration exposes one round trip to L2 / HBM instead of two.  The loads are volatile asm, which keeps their order.
+    // iteration exposes one round trip to L2 / HBM instead of two.  Only the next tile's CELL lives in registers across
+    // the iteration: its query is read again from the shared-memory stage when its turn comes (a stage is refilled only
+    // after its tile has been answered).  The loads are volatile asm, which keeps their order.
     {
+        auto landed = [&](i64 tile) {                   // tile's stage is complete and visible to the whole warp
+            if (tile < full_tiles) { th_cp_async_wait<BM_STAGES - 2>(); __syncwarp(); }
+        };
+        auto read_q = [&](i64 tile, int st, i64 &u, i64 &qs, i64 &qe, i64 &self) {
+            if (tile < full_tiles) {
+                qe = sq[warp][st][1][lane];
+                qs = sq[warp][st][2][lane];
+                if (!PACKED) {
+                    u = sq[warp][st][0][lane];
+                    self = MODE == TH_MODE_STRICT ? sq[warp][st][3][lane] : -1;
+                } else {
+                    u = (i64)reinterpret_cast<const u32 *>(&sq[warp][st][0][0])[lane];
+                    const u32 f = with_self ? reinterpret_cast<const u32 *>(&sq[warp][st][3][0])[lane] : 0xffffffffu;
+                    self = f == 0xffffffffu ? -1 : (i64)f;
+                }
+            } else {
+                const i64 i = tile * 32 + lane;
+                const i64 ic = i < m ? i : m - 1;
+                qe = th_ld_stream(&q_end[ic]);
+                qs = th_ld_stream(&q_start[ic]);
+                if (!PACKED) {
+                    u = th_ld_stream(&q_uuid[ic]);
+                    self = MODE == TH_MODE_STRICT ? th_ld_stream(&q_self[ic]) : -1;
+                } else {
+                    u = (i64)__ldg(&q_uuid32[ic]);
+                    const u32 f = with_self ? __ldg(&q_self32[ic]) : 0xffffffffu;
+                    self = f == 0xffffffffu ? -1 : (i64)f;
+                }
+            }
+        };
+        auto cell_for = [&](i64 tile, int st) -> ThCellV {
+            i64 u, qs, qe, self;
+            read_q(tile, st, u, qs, qe, self);
+            return n_uuids > 0 ? th_ld32(k2_cell_of(g, n_uuids, u, qe)) : ThCellV{0, 0, 0, 0};
+        };
         u32 it = 0;
         i64 tile = tile_of(0);
-        i64 u = 0, qs = 0, qe = 0, self = -1;
-        ThCellV cell = {0, 0, 0, 0};
         bool have = tile < t_end;
-        if (have) fetch(tile, it, u, qs, qe, self, cell);
+        ThCellV cell = {0, 0, 0, 0};
+        if (have) { landed(tile); cell = cell_for(tile, 0); }
         while (have) {
+            const int st = it % BM_STAGES;
             const i64 ntile = tile_of(it + 1);
             const bool nhave = ntile < t_end;
-            i64 nu = 0, nqs = 0, nqe = 0, nself = -1;
             ThCellV ncell = {0, 0, 0, 0};
-            if (nhave) fetch(ntile, it + 1, nu, nqs, nqe, nself, ncell);
+            if (nhave) { landed(ntile); ncell = cell_for(ntile, (it + 1) % BM_STAGES); }
+            i64 u, qs, qe, self;
+            read_q(tile, st, u, qs, qe, self);
             const i64 i = tile * 32 + lane;
             const bool hit = (i < m) && (u >= 0 && u < n_uuids) && qe > TH_I64_MIN &&
                              k2_resolve<MODE>(cell, p1, p2, p4, qs, qe, self);
             emit(tile, hit);
-            tile = ntile; u = nu; qs = nqs; qe = nqe; self = nself; cell = ncell; have = nhave; ++it;
+            __syncwarp();                               // every lane has read this stage for the last time: refill it
+            stage_in(tile_of(it + BM_STAGES), st);
+            cell = ncell; tile = ntile; have = nhave; ++it;
         }
     }
 #else
