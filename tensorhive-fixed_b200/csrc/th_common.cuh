@@ -131,6 +131,7 @@ struct ThPeerOut {
     u32 *my_out;
     int *err;
     i64 expect[TH_MAX_PEERS];    // bitmap words each rank contributes this step
+    u64 *trace;                  // diagnostics (TH_PEER_TRACE): 4 globaltimer stamps per CTA, or NULL
     i64 recv_words;              // max over expect[]: the word range the CTAs split between them for the receive half
     u64 timeout_ns;              // how long a receiver waits for a peer's word before it reports TH_EINTERNAL
 };
@@ -146,9 +147,9 @@ struct th_peer {
     ThPeerCounts counts;         // of the latest step
     int connected;
 };
-static inline size_t th_peer_bytes(int world, i64 wpr) { return (size_t)2 * world * wpr * 8 + (size_t)(world + 8) * 4; }
+static inline size_t th_peer_bytes(int world, i64 wpr) { return (size_t)2 * world * wpr * 8 + (size_t)(2 * TH_MAX_PEERS + 8) * 4; }
 static inline u64 *th_peer_slots(void *base, int world, i64 wpr, int parity) { return (u64 *)base + (size_t)parity * world * wpr; }
-// after the slots: err | 7 spare | barrier_flags[world]
+// after the slots: err | 7 spare | barrier flags round 1 [TH_MAX_PEERS] | round 2 [TH_MAX_PEERS]
 static inline u32 *th_peer_misc(void *base, int world, i64 wpr) { return (u32 *)((u64 *)base + (size_t)2 * world * wpr); }
 static inline u32 *th_peer_bflags(void *base, int world, i64 wpr) { return th_peer_misc(base, world, wpr) + 8; }
 static inline u32 *th_peer_out(const th_peer *p, int parity) { return p->out + (size_t)parity * p->world * p->words_per_rank; }

@@ -28,6 +28,9 @@ constexpr int BM_THREADS = 256;
 #ifndef BM_PIPE
 #define BM_PIPE 0
 #endif
+#ifndef BM_SEND_FENCE
+#define BM_SEND_FENCE 0
+#endif
 #ifndef BM_CELL_LD      // how the 32-byte cell is read: 0 = one LDG.256, 1 = two LDG.128, 2 = LDG.128 + second half on demand
 #define BM_CELL_LD 0
 #endif
@@ -167,6 +170,8 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
     __shared__ u32 swords[BM_MAXW];
     const bool buffered = po.n > 0 && per_cta <= BM_MAXW;
     auto tile_of = [&](u32 it) -> i64 { return t_begin + warp + (i64)BM_WARPS * it; };
+    u64 *const trace = po.n > 0 ? po.trace : nullptr;
+    if (trace && threadIdx.x == 0) trace[4 * blockIdx.x + 0] = th_globaltimer_ns();
 
     // level 1: a warp tile (32 queries x 4 columns = 1 KB = 64 chunks of 16 bytes) is staged with two cp.async per
     // lane -- coalesced, 16 bytes each, no registers -- into a per-warp 4-stage ring; one commit group per tile, and
@@ -359,13 +364,19 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
         // 8-byte {word, epoch} stores (256-byte packets; a 4-byte store per word and tile was measured at +3 us per
         // extra peer on the whole kernel).  Nothing else is needed: the receiver sees each slot turn to this epoch.
         __syncthreads();
+        if (trace && threadIdx.x == 0) trace[4 * blockIdx.x + 1] = th_globaltimer_ns();
         const int cnt = (int)(t_end > t_begin ? t_end - t_begin : 0);
         const u64 tag = (u64)po.epoch << 32;
         for (int p = 0; p < po.n; ++p) {
             u64 *dst = po.dst[p] + po.word_off + t_begin;
             for (int j = threadIdx.x; j < cnt; j += BM_THREADS) dst[j] = (u64)swords[j] | tag;
         }
+#if BM_SEND_FENCE
+        // not needed for correctness (a slot is one atomic 8-byte store); pushes the posted peer writes out at once
+        if (threadIdx.x < cnt) __threadfence_system();
+#endif
     }
+    if (trace && threadIdx.x == 0) trace[4 * blockIdx.x + 2] = th_globaltimer_ns();
     if (po.n > 0 && po.unpack) {
         // Receive half, fused: a CTA that has sent its own words turns to the SAME word range of every rank.  The ranks
         // run the same grid over the same tile ranges, so the peer CTA that owns this range finished at about the same
@@ -397,6 +408,8 @@ __global__ void __launch_bounds__(BM_THREADS, BM_MIN_BLOCKS) k2_bitmap_kernel(
             }
             po.my_out[idx] = w;
         }
+        __syncthreads();
+        if (trace && threadIdx.x == 0) trace[4 * blockIdx.x + 3] = th_globaltimer_ns();
         // slots beyond what any rank contributes this step read as 0
         const i64 tail = po.wpr - po.recv_words;
         for (int r = 0; r < po.n; ++r)
@@ -1091,6 +1104,8 @@ static int k2_exchange_impl(const th_snapshot *h, th_peer *peer, int64_t m, cons
         if (po.expect[p] > po.recv_words) po.recv_words = po.expect[p];
     }
     po.timeout_ns = th_peer_timeout_ns();
+    po.trace = nullptr;
+    if (const char *tr = getenv("TH_PEER_TRACE")) po.trace = (u64 *)strtoull(tr, nullptr, 0);      // diagnostics: a device buffer
     // wait = 1: the receive half runs inside the K2 kernel (needs every rank's kernel to be running at the same time,
     // i.e. one rank per GPU); wait = 0: only the send half is enqueued and th_peer_wait adds the unpack kernel later
     // (ranks emulated on one GPU, where a kernel must never wait for one that is queued behind it).
@@ -1127,15 +1142,25 @@ extern "C" int th_conflict_bitmap_exchange_packed(const th_snapshot *h, th_peer 
 }
 
 // device-side rendezvous of all ranks: raise my barrier flag on every peer, then wait for everybody's
+// Two rounds.  After one round the LAST rank to arrive leaves at once (it has seen everybody's flag) while the others
+// leave one NVLink flight later, when its flag reaches them: the ranks start the step a flight apart, and the early one
+// then waits that flight for its peers' words (measured: the fused step cost ~6 us more than the plain kernel whatever
+// the batch).  In the second round everybody needs a flag that was sent a flight after the last arrival, so with three
+// or more ranks all of them leave together.
 __global__ void k2_peer_barrier_kernel(ThPeerOut po, volatile u32 *my_bflags, int *err) {
     const int r = threadIdx.x;
-    if (r >= po.n) return;
-    volatile u32 *f = po.flags[r] + po.rank;
-    *f = po.epoch;
-    __threadfence_system();
-    for (u64 spins = 0; (int)(my_bflags[r] - po.epoch) < 0; ++spins) {
-        if (spins > (1ull << 24)) { *err = 1; return; }
-        __nanosleep(100);
+    for (int round = 0; round < 2; ++round) {
+        if (r < po.n) {
+            volatile u32 *f = po.flags[r] + round * TH_MAX_PEERS + po.rank;
+            *f = po.epoch;
+            __threadfence_system();
+            volatile u32 *mine = my_bflags + round * TH_MAX_PEERS;
+            for (u64 spins = 0; (int)(mine[r] - po.epoch) < 0; ++spins) {
+                if (spins > (1ull << 24)) { *err = 1; break; }
+                __nanosleep(100);
+            }
+        }
+        __syncwarp();
     }
 }
 
