@@ -21,7 +21,8 @@
 // the bounds arithmetic.  Measured and dropped: prefetching the next windows' columns / entries one or two
 // iterations ahead through registers (4.5-5.1 ms against 3.6 ms: the prefetches share scoreboards with the loads the
 // warp is waiting for and cost 15-40 registers) or through a cp.async shared-memory ring (4.0 ms), four or eight pairs
-// per lane and iteration (3.65 / 4.5 ms), and 48 resident warps at 40 registers (3.8 ms).
+// per lane and iteration (3.65 / 4.5 ms).  Round 2: the kernel is held at 40 registers (__launch_bounds__(256, 6), 48
+// resident warps, no spills) -- with the converged-warp form below 48 warps win over 40 by 3-6 % on every variant.
 #include "th_common.cuh"
 
 
@@ -123,12 +124,15 @@ __device__ __forceinline__ i64 us_finish(const i64 *__restrict__ seg, i64 n, i64
 
 // [a, b) = samples of the segment with ws <= ts <= we, as indices relative to the segment.  Both ends are probed
 // together: four independent loads per lane, then four ballots.  All arguments are uniform within the 8-lane group.
+// The ballots are FULL-WARP (every lane of the warp calls this together; a group with nothing to search passes n = 0):
+// a ballot over a partial mask that differs from group to group compiles into a loop over the groups -- 8 rounds of ~12
+// instructions per ballot and shuffle, a fifth of the uint8 kernel's instructions.
 template <int G, int W>
-__device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSeg &e, i64 ws, i64 we, int gl, u32 gmask,
-                                         i64 &a, i64 &b) {
+__device__ __forceinline__ void us_range(const i64 *__restrict__ seg, i64 n, i64 t_lo, double inv, i64 ws, i64 we, int gl,
+                                         int gbase, i64 &a, i64 &b) {
     constexpr int R = W / G;                      // probe loads per lane and end
-    const i64 n = e.n;
-    const i64 wa = us_window<W>(n, ws, e.t_lo, e.inv), wb = us_window<W>(n, we, e.t_lo, e.inv);
+    const i64 wa = us_window<W>(n, ws, t_lo, inv), wb = us_window<W>(n, we, t_lo, inv);
+    constexpr u32 GM = G == 32 ? 0xffffffffu : ((1u << (G & 31)) - 1u);
     i64 va[R], vb[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) va[r] = us_ld8_if(seg + wa + r * G + gl, wa + r * G + gl < n, TH_I64_MAX);
@@ -136,9 +140,9 @@ __device__ __forceinline__ void us_range(const i64 *__restrict__ seg, const UsSe
     for (int r = 0; r < R; ++r) vb[r] = us_ld8_if(seg + wb + r * G + gl, wb + r * G + gl < n, TH_I64_MAX);
     int fa = 0, fb = 0;                           // beyond the segment counts as "holds"
 #pragma unroll
-    for (int r = 0; r < R; ++r) fa += __popc(__ballot_sync(gmask, wa + r * G + gl < n && va[r] < ws));
+    for (int r = 0; r < R; ++r) fa += __popc((__ballot_sync(0xffffffffu, wa + r * G + gl < n && va[r] < ws) >> gbase) & GM);
 #pragma unroll
-    for (int r = 0; r < R; ++r) fb += __popc(__ballot_sync(gmask, wb + r * G + gl < n && vb[r] <= we));
+    for (int r = 0; r < R; ++r) fb += __popc((__ballot_sync(0xffffffffu, wb + r * G + gl < n && vb[r] <= we) >> gbase) & GM);
     a = us_finish<true, W>(seg, n, ws, wa, fa);   // first ts >= ws
     b = us_finish<false, W>(seg, n, we, wb, fb);  // first ts >  we
     if (b < a) b = a;                             // end before start: empty window
@@ -238,7 +242,7 @@ __device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *
 // (the sample ring establishes that while it appends, th_ring.cu): both range ends follow from two divisions and the ts
 // column is not touched at all.
 template <int ELEM, bool VEC, bool TAB, int G, int W, bool REG = false>
-__global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
+__global__ void __launch_bounds__(US_THREADS, 6) k4_usage_kernel(i64 s_total, i64 n_uuids, const i64 *__restrict__ off,
                                                               const UsSeg *__restrict__ tab, const i64 *__restrict__ ts,
                                                               const void *__restrict__ gpu_v, const void *__restrict__ mem_v,
                                                               i64 w, const i64 *__restrict__ win_uuid,
@@ -249,14 +253,22 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
     const int lane = threadIdx.x & 31;
     constexpr int GROUPS_PER_BLOCK = US_THREADS / G;
     const int gl = lane & (G - 1);
-    const u32 gmask = ((1u << G) - 1u) << (lane & ~(G - 1));
+    const int gbase = lane & ~(G - 1);
+    constexpr int GPW = 32 / G;                               // windows per warp and iteration
     const i64 gstride = (i64)gridDim.x * GROUPS_PER_BLOCK;
-    for (i64 q = (i64)blockIdx.x * GROUPS_PER_BLOCK + (threadIdx.x / G); q < w; q += gstride) {
-        const i64 u = win_uuid[q];
-        const i64 ws = win_start[q], we = win_end[q];
+    // The warp stays converged: a warp-uniform loop (a warp's last iteration may have idle groups) and full-warp ballots
+    // and shuffles.  A/B on one B200 against per-group masks and a per-group loop, both at 40 registers (6 blocks per
+    // SM; at 48 registers every variant loses 3-6 %): uint8 columns 1.27 -> 1.08 ms, int64 columns 2.77 -> 2.74 ms,
+    // shuffled windows 3.70 -> 3.65 ms, ring with jittered stamps 0.168 -> 0.146 ms, ring on an exact cadence 0.141 -> 0.143 ms.
+    for (i64 qb = (i64)blockIdx.x * GROUPS_PER_BLOCK + (i64)(threadIdx.x >> 5) * GPW; qb < w; qb += gstride) {
+        const i64 q = qb + (lane / G);
+        const bool live = q < w;
+        const i64 u = live ? win_uuid[q] : -1;
+        const i64 ws = live ? win_start[q] : 0, we = live ? win_end[q] : 0;
         i64 a = 0, b = 0;
+        UsSeg e;
+        e.lo = 0; e.n = 0; e.t_lo = 0; e.inv = 0.0;
         if (u >= 0 && u < n_uuids) {
-            UsSeg e;
             if (TAB) {
                 const longlong2 x = th_ld16(&tab[u]);
                 const longlong2 y = th_ld16(reinterpret_cast<const char *>(&tab[u]) + 16);
@@ -264,21 +276,22 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
             } else {
                 e = us_make_seg(off, ts, u);
             }
-            if (REG && e.inv < 0.0) {
-                const i64 c = (i64)(-e.inv);
-                a = ws <= e.t_lo ? 0 : (ws - e.t_lo + c - 1) / c;        // first k with t_lo + k c >= ws
-                b = we < e.t_lo ? 0 : (we - e.t_lo) / c + 1;              // one past the last k with t_lo + k c <= we
-                a = a < e.n ? a : e.n;
-                b = b < e.n ? b : e.n;
-                if (b < a) b = a;
-                a += e.lo;
-                b += e.lo;
-            } else if (e.n > 0) {
-                us_range<G, W>(ts + e.lo, e, ws, we, gl, gmask, a, b);
-                a += e.lo;
-                b += e.lo;
-            }
         }
+        const bool reg = REG && e.inv < 0.0;                  // an exact arithmetic run: no search at all
+        // a warp-uniform branch: a warp whose windows are all empty or arithmetic runs skips the search
+        const bool need = !reg && e.n > 0;
+        if (__any_sync(0xffffffffu, need))
+            us_range<G, W>(ts + e.lo, need ? e.n : 0, e.t_lo, need ? e.inv : 0.0, ws, we, gl, gbase, a, b);
+        if (reg) {
+            const i64 c = (i64)(-e.inv);
+            a = ws <= e.t_lo ? 0 : (ws - e.t_lo + c - 1) / c;            // first k with t_lo + k c >= ws
+            b = we < e.t_lo ? 0 : (we - e.t_lo) / c + 1;                  // one past the last k with t_lo + k c <= we
+            a = a < e.n ? a : e.n;
+            b = b < e.n ? b : e.n;
+            if (b < a) b = a;
+        }
+        a += e.lo;
+        b += e.lo;
         i64 sg = 0, sm = 0;
         if (ELEM == 8) {
             const i64 *gpu = static_cast<const i64 *>(gpu_v), *mem = static_cast<const i64 *>(mem_v);
@@ -291,10 +304,10 @@ __global__ void __launch_bounds__(US_THREADS) k4_usage_kernel(i64 s_total, i64 n
         }
 #pragma unroll
         for (int o = G / 2; o > 0; o >>= 1) {
-            sg += __shfl_xor_sync(gmask, sg, o);
-            sm += __shfl_xor_sync(gmask, sm, o);
+            sg += __shfl_xor_sync(0xffffffffu, sg, o);        // o < G: partners stay inside the group
+            sm += __shfl_xor_sync(0xffffffffu, sm, o);
         }
-        if (gl == 0) {
+        if (gl == 0 && live) {
             const i64 c = b - a;
             if (o_sg) o_sg[q] = sg;
             if (o_sm) o_sm[q] = sm;

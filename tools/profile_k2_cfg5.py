@@ -40,3 +40,30 @@ for _ in range(4):
 torch.cuda.synchronize()
 print('k2 us per launch:', ['%.1f' % (1e3 * a.elapsed_time(b)) for a, b in ev], 'conflicts:',
       int(th.api.unpack_bits(words, M).sum()), 'lib:', native.LIB_PATH)
+
+# TH_PROF_ORDERS=group8,group32,group128,sorted: the same candidates presented in another order (reordered outside the
+# timed region).  groupG = bucketed into G uuid ranges, random inside a bucket: what K2 would see AFTER a partition pass
+# that blocks the index for L2 -- the upper bound of that lever, without the pass.  sorted = by (uuid, start): the
+# order a whole-calendar revalidation presents.
+for order in [o for o in os.environ.get('TH_PROF_ORDERS', '').split(',') if o]:
+    if order == 'sorted':
+        key = qd[0] * (1 << 42) + (qd[1] - qd[1].min())
+    else:
+        g = int(order[5:])
+        key = qd[0] // ((U + g - 1) // g)
+    perm = torch.sort(key, stable=True).indices
+    qo = [c[perm].contiguous() for c in qd]
+    del key, perm
+    ev = []
+    for _ in range(4):
+        flush.sum()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        native.check(lib.th_conflict_bitmap(snap._h, M, qo[0].data_ptr(), qo[1].data_ptr(), qo[2].data_ptr(),
+                                            qo[3].data_ptr(), 0, words.data_ptr(), 1, sp))
+        b.record(stream)
+        ev.append((a, b))
+    torch.cuda.synchronize()
+    print('order', order, 'k2 us per launch:', ['%.1f' % (1e3 * a.elapsed_time(b)) for a, b in ev], 'conflicts:',
+          int(th.api.unpack_bits(words, M).sum()))
+    del qo
