@@ -215,23 +215,41 @@ __device__ __forceinline__ uint4 us_mask16(uint4 v, int lo, int hi) {
     v.x &= (u32)m0; v.y &= (u32)(m0 >> 32); v.z &= (u32)m1; v.w &= (u32)(m1 >> 32);
     return v;
 }
+// Only the first and the last chunk of a range can be partial.  They go to lanes 0 and 1 of the group, once, with masks;
+// the chunks between them are whole and are summed by all lanes without a mask.  (Round 2, from the ncu source page: with
+// the masks inside the chunk loop 99 % of the WARP's iterations took the mask branch, because some lane of the warp's 32
+// always held an edge chunk -- 75 of the loop's 123 instructions, three times per warp iteration.)
 template <int G>
 __device__ __forceinline__ void us_sum_u8(const u8 *__restrict__ gpu, const u8 *__restrict__ mem, i64 s_total, i64 a,
                                           i64 b, int gl, i64 &sg, i64 &sm) {
-    const i64 c1 = (b + 15) >> 4;                       // 16-sample chunks
-    for (i64 c = (a >> 4) + gl; c < c1; c += G) {
-        const i64 i0 = c << 4;
-        const int lo = (int)(a > i0 ? a - i0 : 0);
-        const int hi = (int)(b < i0 + 16 ? b - i0 : 16);
-        if (i0 + 16 <= s_total) {
-            uint4 g4 = th_ld16u(gpu + i0);
-            uint4 m4 = th_ld16u(mem + i0);
-            if (lo > 0 || hi < 16) { g4 = us_mask16(g4, lo, hi); m4 = us_mask16(m4, lo, hi); }   // edge chunks only
-            sg += us_sum16(g4);
-            sm += us_sum16(m4);
-        } else {
-            for (int t = lo; t < hi; ++t) { sg += gpu[i0 + t]; sm += mem[i0 + t]; }
-        }
+    static_assert(G >= 2, "the two edge chunks go to two lanes");
+    if (b <= a) return;
+    const i64 c0 = a >> 4, cl = (b - 1) >> 4;           // first and last 16-sample chunk
+    // the edge chunk of this lane, if any: loaded before the interior loop, consumed after it
+    const bool edge = gl == 0 || (gl == 1 && cl != c0);
+    const i64 e0 = (gl == 0 ? c0 : cl) << 4;
+    const int lo = gl == 0 ? (int)(a - e0) : 0;
+    const int hi = b - e0 < 16 ? (int)(b - e0) : 16;
+    const bool wide = edge && e0 + 16 <= s_total;       // the whole 16 bytes exist
+    const longlong2 zero2 = make_longlong2(0, 0);
+    const longlong2 eg = th_ld16_if(reinterpret_cast<const longlong2 *>(gpu + e0), wide, zero2);
+    const longlong2 em = th_ld16_if(reinterpret_cast<const longlong2 *>(mem + e0), wide, zero2);
+#pragma unroll 1
+    for (i64 c = c0 + 1 + gl; c < cl; c += G) {         // interior chunks end before b <= s_total
+        const uint4 g4 = th_ld16u(gpu + (c << 4));
+        const uint4 m4 = th_ld16u(mem + (c << 4));
+        sg += us_sum16(g4);
+        sm += us_sum16(m4);
+    }
+    if (wide) {
+        uint4 g4 = make_uint4((u32)eg.x, (u32)((u64)eg.x >> 32), (u32)eg.y, (u32)((u64)eg.y >> 32));
+        uint4 m4 = make_uint4((u32)em.x, (u32)((u64)em.x >> 32), (u32)em.y, (u32)((u64)em.y >> 32));
+        g4 = us_mask16(g4, lo, hi);
+        m4 = us_mask16(m4, lo, hi);
+        sg += us_sum16(g4);
+        sm += us_sum16(m4);
+    } else if (edge) {                                  // the column ends inside this chunk
+        for (int t = lo; t < hi; ++t) { sg += gpu[e0 + t]; sm += mem[e0 + t]; }
     }
 }
 
