@@ -456,3 +456,36 @@ def test_usage_ring_stays_on_the_device_and_knows_regular_runs(dropin):
     assert all(np.array_equal(a.cpu().numpy(), b) for a, b in zip(dgot, got))
     ring.close()
     cal.close()
+
+
+@pytest.mark.parametrize('n', [1, 17, 48, 83])
+def test_usage_ring_every_range_of_a_short_log(dropin, n):
+    """Every index range of an n-sample ring log as a window, for a uuid on an exact cadence (both ends from divisions,
+    ts never read) and one stamped off the grid (probed): the edge-chunk split of the uint8 sums in every position."""
+    cal, _ = _calendar(dropin, [])
+    rng = np.random.default_rng(300 + n)
+    ring = dropin.UsageRing(initial_capacity=16)
+    t0 = 1_800_000_000_000_000
+    g = rng.integers(0, 256, size=(2, n)).astype(np.uint8)
+    m = rng.integers(0, 256, size=(2, n)).astype(np.uint8)
+    ts = np.zeros((2, n), np.int64)
+    for k in range(n):
+        ts[0, k] = t0 + k * 1_000_000
+        ts[1, k] = t0 + k * 1_000_000 + int(rng.integers(0, 900_000))
+        ring.append_tick([('GPU-regular', int(ts[0, k]), int(g[0, k]), int(m[0, k])),
+                          ('GPU-jitter', int(ts[1, k]), int(g[1, k]), int(m[1, k]))])
+    assert ring.info()['regular_uuids'] == (1 if n > 1 else ring.info()['regular_uuids'])
+    ab = np.array([(u, a, b) for u in range(2) for a in range(n) for b in range(a, n)], np.int64)
+    wu = np.array([ring.code('GPU-regular'), ring.code('GPU-jitter')], np.int64)[ab[:, 0]]
+    ws = ts[ab[:, 0], ab[:, 1]]
+    we = ts[ab[:, 0], ab[:, 2]]
+    sg, sm, cnt = ring.reduce(wu, ws, we)[:3]
+    for u in range(2):
+        sel = ab[:, 0] == u
+        cg = np.concatenate([[0], np.cumsum(g[u].astype(np.int64))])
+        cm = np.concatenate([[0], np.cumsum(m[u].astype(np.int64))])
+        a, b = ab[sel, 1], ab[sel, 2]
+        assert np.array_equal(cnt[sel], b - a + 1)
+        assert np.array_equal(sg[sel], cg[b + 1] - cg[a]) and np.array_equal(sm[sel], cm[b + 1] - cm[a])
+    ring.close()
+    cal.close()

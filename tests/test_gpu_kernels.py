@@ -595,6 +595,28 @@ def test_usage_reduce_u8_matches_oracle(th, synth, brute, kw):
         assert np.array_equal(a, b)
 
 
+@pytest.mark.parametrize('n', [1, 15, 16, 17, 47, 48, 83])
+def test_usage_reduce_u8_every_range_of_a_short_log(th, brute, n):
+    """Every index range [a, b] of an n-sample log as a window: first and last 16-sample chunk the same, adjacent, or apart;
+    ranges that start / end on every byte of a chunk; the column ending inside its last chunk (n not a multiple of 16)."""
+    rng = np.random.default_rng(n)
+    ts = (np.arange(n, dtype=np.int64) * 1_000_000 + 1_700_000_000_000_000)
+    off = np.array([0, 0, n], np.int64)                               # uuid 0 has no samples
+    g8 = rng.integers(0, 256, size=n, dtype=np.uint8)
+    m8 = rng.integers(0, 256, size=n, dtype=np.uint8)
+    ab = np.array([(a, b) for a in range(n) for b in range(a, n)], np.int64)
+    wu = np.ones(len(ab), np.int64)
+    ws, we = ts[ab[:, 0]], ts[ab[:, 1]] + 999_999                     # ends between two samples
+    outs = th.usage_reduce_u8(off, ts, g8, m8, wu, ws, we)
+    cs_g = np.concatenate([[0], np.cumsum(g8.astype(np.int64))])
+    cs_m = np.concatenate([[0], np.cumsum(m8.astype(np.int64))])
+    assert np.array_equal(outs[2], ab[:, 1] - ab[:, 0] + 1)
+    assert np.array_equal(outs[0], cs_g[ab[:, 1] + 1] - cs_g[ab[:, 0]])
+    assert np.array_equal(outs[1], cs_m[ab[:, 1] + 1] - cs_m[ab[:, 0]])
+    esg, esm, ecnt = brute.usage_reduce(off, ts, g8.astype(np.int64), m8.astype(np.int64), wu, ws, we)
+    assert np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm) and np.array_equal(outs[2], ecnt)
+
+
 def test_usage_reduce_u8_unaligned_columns(th, brute):
     import torch
     rng = np.random.default_rng(18)
