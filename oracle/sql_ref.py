@@ -26,8 +26,10 @@ R4     ``upcoming_events_for_resource``    :106-118     :func:`SqlCalendar.upcom
 Parity pinning: the reference's own tests for this path
 (``tests/unit/models/test_reservation_model.py:10-64,113-125``) are transcribed as known-answer
 vectors in ``tests/golden/reference_kat.json`` and checked against this oracle by
-``tests/test_oracle_kat.py``.  R2, R4 have no reference test: for them **parity is unpinned by
-reference tests** and the SQL text above is the anchor.
+``tests/test_oracle_kat.py``.  R2, R4 have no reference test; all four rows are additionally held to
+``tests/golden/reference_model_vectors.json`` -- answers of the reference's own model methods,
+executed under an expression-evaluating stand-in for SQLAlchemy
+(``tests/golden/make_reference_model_vectors.py``) -- by ``tests/test_oracle_model_vectors.py``.
 """
 from __future__ import annotations
 

@@ -21,8 +21,8 @@ is 30 (tensorhive/config.py:259), `datetime.utcnow()` is frozen per world, and U
 way one SQLAlchemy session maps them (JobSchedulingService.py:127 compares with `is not`).  Everything the service
 functions compute -- loops, comparisons, dictionary layout, the float minutes -- is the reference's code.
 
-R2 / R4 stay unpinned: their arithmetic is SQL text that SQLAlchemy 1.3.0 generates, and SQLAlchemy cannot be
-installed here.  The GPU box has no /root/reference: the vectors (inputs AND outputs) are committed, and
+The model's own queries (R1-R4) are executed separately, under a stand-in for SQLAlchemy's operators:
+tests/golden/make_reference_model_vectors.py.  The GPU box has no /root/reference: the vectors (inputs AND outputs) are committed, and
 tests/test_oracle_exec_vectors.py (CPU, oracle restatement) and tests/test_gpu_exec_vectors.py (dropin on the GPU) are
 held to them.
 """

@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 import test_gpu_dropin as G
+import test_gpu_model_vectors as M
 from oracle import brute
 
 
@@ -103,6 +104,9 @@ test_usage_log = G.test_usage_log_averages
 test_save_destroy = G.test_save_move_save_and_destroy
 # (the sample ring lives on the device: its tests are GPU tests)
 test_calendar_view = G.test_calendar_view_controller
+# the host logic of the drop-in against the executed reference's model vectors (queries and the write path)
+test_model_methods = M.test_model_methods_match_the_executed_reference
+test_write_path = M.test_write_path_matches_the_executed_reference
 
 
 def test_calendar_delta_bookkeeping(dropin):
