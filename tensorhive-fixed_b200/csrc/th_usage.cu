@@ -157,6 +157,27 @@ __device__ __forceinline__ i64 us_floor_div(i64 a, i64 b) {   // b > 0; Python's
     return q;
 }
 
+__device__ __forceinline__ i64 us_sat_sub(i64 a, i64 b) {      // a - b for a >= b, clamped to INT64_MAX
+    const u64 d = (u64)a - (u64)b;
+    return d > (u64)TH_I64_MAX ? TH_I64_MAX : (i64)d;
+}
+__device__ __forceinline__ i64 us_sat_add(i64 a, i64 b) {      // a + b for a, b >= 0, clamped to INT64_MAX
+    return a > TH_I64_MAX - b ? TH_I64_MAX : a + b;
+}
+
+// x / c for x >= 0, c > 0 through the double-precision reciprocal, corrected to the exact quotient: ~15 instructions
+// against ~80 for the 64-bit integer division (two per window on an exact-cadence log: a fifth of that kernel's
+// instructions).  (double)x is exact below 2^53 and the product is then off by at most a few units, which the remainder
+// test repairs; larger x take the integer division.
+__device__ __forceinline__ i64 us_div_nonneg(i64 x, i64 c, double rc) {
+    if (x >= (1ll << 52)) return x / c;
+    i64 q = (i64)((double)x * rc);
+    i64 r = x - q * c;
+    while (r < 0) { --q; r += c; }
+    while (r >= c) { ++q; r -= c; }
+    return q;
+}
+
 // ---- range sums --------------------------------------------------------------------------------------------------
 // int64 columns, 16-byte aligned: element pairs, two pairs per lane and iteration, every load issued before any is
 // consumed.  Positions are int32 offsets from the (even) first pair, so the bounds checks are single compares.
@@ -302,8 +323,10 @@ __global__ void __launch_bounds__(US_THREADS, 6) k4_usage_kernel(i64 s_total, i6
             us_range<G, W>(ts + e.lo, need ? e.n : 0, e.t_lo, need ? e.inv : 0.0, ws, we, gl, gbase, a, b);
         if (reg) {
             const i64 c = (i64)(-e.inv);
-            a = ws <= e.t_lo ? 0 : (ws - e.t_lo + c - 1) / c;            // first k with t_lo + k c >= ws
-            b = we < e.t_lo ? 0 : (we - e.t_lo) / c + 1;                  // one past the last k with t_lo + k c <= we
+            const double rc = 1.0 / (double)c;
+            // (saturating: a window end at the int64 extremes must not wrap; anything beyond the run is clamped below)
+            a = ws <= e.t_lo ? 0 : us_div_nonneg(us_sat_add(us_sat_sub(ws, e.t_lo), c - 1), c, rc);   // first k with t_lo + k c >= ws
+            b = we < e.t_lo ? 0 : us_sat_add(us_div_nonneg(us_sat_sub(we, e.t_lo), c, rc), 1);         // one past the last k with t_lo + k c <= we
             a = a < e.n ? a : e.n;
             b = b < e.n ? b : e.n;
             if (b < a) b = a;

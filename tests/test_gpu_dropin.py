@@ -479,6 +479,16 @@ def test_usage_ring_every_range_of_a_short_log(dropin, n):
     wu = np.array([ring.code('GPU-regular'), ring.code('GPU-jitter')], np.int64)[ab[:, 0]]
     ws = ts[ab[:, 0], ab[:, 1]]
     we = ts[ab[:, 0], ab[:, 2]]
+    # windows at the int64 extremes, for both uuids: everything, nothing after the log, nothing before it
+    I = np.iinfo(np.int64)
+    xs = np.array([I.min, I.max - 5, I.min, t0 + 1, I.min], np.int64)
+    xe = np.array([I.max, I.max, I.min + 5, I.max, t0 - 1], np.int64)
+    for u in range(2):
+        code = ring.code(['GPU-regular', 'GPU-jitter'][u])
+        xg, xm, xc = ring.reduce(np.full(5, code, np.int64), xs, xe)[:3]
+        first = int(ts[u, 0] >= t0 + 1)
+        assert list(xc) == [n, 0, 0, n - 1 + first, 0]
+        assert xg[0] == g[u].astype(np.int64).sum() and xm[3] == m[u, 1 - first:].astype(np.int64).sum()
     sg, sm, cnt = ring.reduce(wu, ws, we)[:3]
     for u in range(2):
         sel = ab[:, 0] == u
