@@ -112,6 +112,17 @@ __device__ __forceinline__ bool k2_resolve(const ThCellV c, const ThP1 *__restri
     } else {   // TH_MODE_INCLUSIVE: any row, cancelled or not, with start <= qe and qs <= end
         // mall (running maximum of `end` over ALL rows, P4) is at least m1 (non-cancelled rows only), so the cell's
         // m1_before settles "yes" early; otherwise speculative probes on {start} (row 0 from the cell) and {mall}.
+        if (qs == TH_I64_MIN) {
+            // Every `end` qualifies, so the question is "does a row start at or before qe" -- and the sentinel's end of
+            // -inf, which the comparisons below would accept, must not count as one.  Rare: a plain search of the bucket.
+            int lo = pos, hi = pos + cnt;
+            while (lo < hi) {
+                const int mid = (int)(((unsigned)lo + (unsigned)hi) >> 1);
+                if (th_ld8(&p1[mid].start) <= qe) lo = mid + 1; else hi = mid;
+            }
+            // row lo - 1 is the last one with start <= qe: a real row, or the uuid's sentinel (start = -inf)
+            return lo > 0 && th_ld8(&p1[lo - 1].start) != TH_I64_MIN;
+        }
         if (c.m1_before >= qs) return true;
         const bool in0 = cnt > 0 && c.start0 <= qe;
         const bool more = in0 && cnt > 1;

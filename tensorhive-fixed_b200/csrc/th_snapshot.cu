@@ -181,7 +181,8 @@ __global__ void __launch_bounds__(256) ld_ugrid_kernel(i64 n_uuids, const int *_
             i64 target = (x4 * rows + 3) / 4;
             if (target < 1) target = 1;
             int shift = 0;
-            while (shift < 63 && (i64)(span >> shift) + 1 > target) ++shift;
+            // (unsigned: a span of 2^63 us or more -- starts near both int64 extremes -- must not read as negative)
+            while (shift < 63 && (span >> shift) >= (u64)target) ++shift;
             e.shift = shift;
             e.nb = (int)((span >> shift) + 1);
             const double used = (double)(span >> shared_shift) + 1.0;
@@ -655,7 +656,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             const u64 span = (u64)max_start - (u64)min_start;
             i64 target = n_uuids > 0 ? (x4 * ((n + n_uuids - 1) / n_uuids) + 3) / 4 : 1;
             if (target < 1) target = 1;
-            while (s_shift < 63 && (i64)(span >> s_shift) + 1 > target) ++s_shift;
+            while (s_shift < 63 && (span >> s_shift) >= (u64)target) ++s_shift;      // unsigned, see ld_ugrid_kernel
             s_nb = (i64)(span >> s_shift) + 1;
         }
         ld_ugrid_kernel<<<ugrid, 256, 0, st>>>(n_uuids, h->seg, h->p1, x4, s_shift, h->ugrid, nb_u, crowd);

@@ -49,6 +49,9 @@ def make_calendar(n: int, n_uuids: int, seed: int, skew: float = 0.0, shuffle_id
     dur = rng.integers(MIN_DURATION_US, MAX_DURATION_US + 1, size=n, dtype=np.int64)
     # live rows advance the walk; cancelled rows are placed afterwards
     step = np.where(is_canc, 0, gap + dur)
+    if float(step.sum(dtype=np.float64)) > 9.0e18:
+        raise ValueError('make_calendar(%d rows): the walk would overflow int64 microseconds -- build calendars of this '
+                         'size chunk by chunk (GlobalCalendar)' % n)
     csum = np.cumsum(step)
     first = np.ones(n, bool)
     first[1:] = uuid[1:] != uuid[:-1]

@@ -138,3 +138,46 @@ def test_long_lists_take_the_radix_path(lib_built):
         flag = {int(i): int(c) for i, c in zip(cal['id'], cal['cancelled'])}
         assert [flag[int(i)] for i in ids] == [int(c) for c in canc]
     snap.close()
+
+
+@pytest.mark.parametrize('plan', ['shared', 'per_uuid'])
+def test_calendar_spanning_the_whole_int64_range(lib_built, monkeypatch, plan):
+    """Starts near both ends of int64: the span of the calendar (and of one uuid) exceeds 2^63 us, which the grid sizing
+    must not read as a negative number (found with a synthetic 100 M-row calendar whose generator had overflowed)."""
+    import tensorhive_fixed_b200 as th
+    from oracle import brute
+    monkeypatch.setenv('TH_GRID_PLAN', plan)
+    I = np.iinfo(np.int64)
+    rng = np.random.default_rng(3)
+    lo = I.min + 1 + np.sort(rng.integers(0, 10_000, size=40))
+    mid = np.sort(rng.integers(-5_000, 5_000, size=40))
+    hi = I.max - 20_000 + np.sort(rng.integers(0, 10_000, size=40))
+    start = np.concatenate([lo, mid, hi, mid + 7]).astype(np.int64)
+    end = start + rng.integers(0, 3_000, size=start.size)
+    n = start.size
+    cal = {'id': rng.permutation(np.arange(1, n + 1)).astype(np.int64),
+           'uuid_id': np.concatenate([np.zeros(120, np.int64), np.ones(40, np.int64)]),        # uuid 0 spans everything
+           'start': start, 'end': end.astype(np.int64), 'owner': rng.integers(1, 5, size=n).astype(np.int64),
+           'cancelled': (rng.random(n) < 0.2).astype(np.uint8), 'n_uuids': 3}
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=3)
+    m = 600
+    qu = rng.integers(-1, 4, size=m).astype(np.int64)
+    anchor = rng.choice(np.concatenate([start, end]), size=m)
+    clip = lambda x: min(max(x, int(I.min)), int(I.max))                              # Python ints: no wrap-around
+    qs = np.array([clip(int(a) + int(d)) for a, d in zip(anchor, rng.integers(-2_000, 2_000, size=m))], np.int64)
+    qe = np.array([clip(int(a) + int(d)) for a, d in zip(qs, rng.integers(0, 4_000, size=m))], np.int64)
+    qs[:4], qe[:4] = [I.min, I.min, I.max - 5, 0], [I.max, I.min + 5, I.max, I.max]
+    qf = np.where(rng.random(m) < 0.5, -1, rng.choice(cal['id'], size=m)).astype(np.int64)
+    for mode, bmode in ((th.MODE_STRICT, brute.STRICT), (th.MODE_INCLUSIVE, brute.INCLUSIVE)):
+        f = qf if mode == th.MODE_STRICT else None
+        bits = snap.conflict_bitmap(qu, qs, qe, f, mode)
+        want = brute.conflict_bits(cal, qu, qs, qe, qf if mode == th.MODE_STRICT else np.full(m, -1, np.int64), bmode)
+        assert np.array_equal(np.asarray(bits, bool), np.asarray(want, bool)), mode
+        off, ids, _c = snap.conflict_sets(qu, qs, qe, f, mode)
+        assert csr_to_lists(off, ids) == brute.conflict_sets(cal, qu, qs, qe, qf if mode == th.MODE_STRICT else np.full(m, -1, np.int64), bmode)
+    for now in (int(lo[3]), 0, int(hi[5]) + 1, int(I.min), int(I.min) + 1, int(I.max)):
+        res, own = snap.current_owner(now)
+        eres, eown = brute.current_owner(cal, 3, now)
+        assert np.array_equal(res, eres) and np.array_equal(own, eown)
+    snap.close()

@@ -18,8 +18,23 @@ U = int(os.environ.get('TH_PROF_U', '8192'))
 M = int(os.environ.get('TH_PROF_M', '12500000'))
 dev = torch.device('cuda:0')
 lib = native.load()
-cal = synth.make_calendar(N, U, seed=20260102)
-q = synth.make_queries(cal, M, seed=20260103)
+KEYS = ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')
+if N <= 16_000_000:
+    cal = synth.make_calendar(N, U, seed=20260102)
+    q = synth.make_queries(cal, M, seed=20260103)
+else:                                                   # too many rows for one walk in int64 us: chunk by chunk
+    g = synth.GlobalCalendar(N, U, seed=20260102)
+    cparts, qparts = [], []
+    for c in range(g.n_chunks):
+        cc = g.chunk(c)
+        cparts.append(cc)
+        qparts.append(g.chunk_queries(c, int(round(M * g.chunk_rows[c] / g.n_rows)), seed=20260103, cal=cc))
+    cal = synth.concat_columns(cparts, KEYS)
+    q = synth.concat_columns(qparts, ('uuid_id', 'start', 'end', 'self_id'))
+    perm = np.random.default_rng(1).permutation(len(q['uuid_id']))        # candidates arrive in no particular order
+    q = {k: v[perm] for k, v in q.items()}
+    N, M = len(cal['id']), len(q['uuid_id'])
+    del cparts, qparts
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 snap = th.Snapshot(0)
 snap.load(*[t(cal[k]) for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')], n_uuids=U)
@@ -40,6 +55,24 @@ for _ in range(4):
 torch.cuda.synchronize()
 print('k2 us per launch:', ['%.1f' % (1e3 * a.elapsed_time(b)) for a, b in ev], 'conflicts:',
       int(th.api.unpack_bits(words, M).sum()), 'lib:', native.LIB_PATH)
+
+# TH_PROF_CHECK=1: the verdicts of every candidate of 24 sampled uuids against the brute-force oracle over those uuids' rows
+if os.environ.get('TH_PROF_CHECK'):
+    from oracle import brute
+    rng = np.random.default_rng(5)
+    pick = np.sort(rng.choice(U, size=min(24, U), replace=False))
+    rsel = np.isin(cal['uuid_id'], pick)
+    qsel = np.flatnonzero(np.isin(q['uuid_id'], pick))
+    sub = {k: cal[k][rsel] for k in ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')}
+    sub['n_uuids'] = U
+    want = brute.conflict_bits(sub, q['uuid_id'][qsel], q['start'][qsel], q['end'][qsel], q['self_id'][qsel])
+    got = th.api.unpack_bits(words, M)
+    got = got.cpu().numpy() if hasattr(got, 'cpu') else np.asarray(got)
+    bad = int((got[qsel].astype(bool) != np.asarray(want, bool)).sum())
+    print('parity on %d uuids: %d rows, %d candidates, %d conflicts expected, %d mismatches' % (
+        len(pick), int(rsel.sum()), len(qsel), int(np.asarray(want, bool).sum()), bad))
+    info = snap.info()
+    print('snapshot:', info)
 
 # TH_PROF_ORDERS=group8,group32,group128,sorted: the same candidates presented in another order (reordered outside the
 # timed region).  groupG = bucketed into G uuid ranges, random inside a bucket: what K2 would see AFTER a partition pass
