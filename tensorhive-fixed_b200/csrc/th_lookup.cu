@@ -229,6 +229,12 @@ extern "C" int th_current_owner(const th_snapshot *h, int64_t now_us, int64_t *o
     return TH_OK;
 }
 
+// now + period for period >= 0, clamped: a horizon beyond INT64_MAX means "no upper bound" (the reference's datetime
+// arithmetic cannot get there; through the C ABI it can, and must not wrap into the past)
+static inline int64_t th_later(int64_t now_us, int64_t period_us) {
+    return now_us > TH_I64_MAX - period_us ? TH_I64_MAX : now_us + period_us;
+}
+
 extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_us, int64_t k, const int64_t *uuids,
                            int64_t *out_first_id, int64_t *out_first_start, int64_t *out_first_owner,
                            int64_t *out_count, int mem, void *stream) {
@@ -250,7 +256,7 @@ extern "C" int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_
     TH_TRY(sc.out(out_first_owner, 8 * zk, mem, &d_o));
     TH_TRY(sc.out(out_count, 8 * zk, mem, &d_c));
     k3_upcoming_kernel<<<th_grid_for(k, LK_GROUPS_PER_BLOCK, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
-                                                                            now_us + period_us, k, (const i64 *)d_u,
+                                                                            th_later(now_us, period_us), k, (const i64 *)d_u,
                                                                             (i64 *)d_id, (i64 *)d_s, (i64 *)d_o, (i64 *)d_c);
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_first_id, d_id, 8 * zk, mem, st));
@@ -281,7 +287,7 @@ extern "C" int th_upcoming_owner_flags(const th_snapshot *h, int64_t now_us, int
     TH_TRY(sc.in(task_owner, 8 * zt, mem, &d_o));
     TH_TRY(sc.out(out_flag_u8, zt, mem, &d_f));
     k5_owner_flags_kernel<<<th_grid_for(t, LK_GROUPS_PER_BLOCK, 16), LK_THREADS, 0, st>>>(th_grid_of(h), h->seg, h->p1, h->p3, h->p4, h->n_uuids, now_us,
-                                                                               now_us + period_us, t, (const i64 *)d_u,
+                                                                               th_later(now_us, period_us), t, (const i64 *)d_u,
                                                                                (const i64 *)d_o, test, (u8 *)d_f);
     TH_CUDA(cudaGetLastError());
     TH_TRY(th_copy_back(out_flag_u8, d_f, zt, mem, st));

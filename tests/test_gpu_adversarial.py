@@ -181,3 +181,17 @@ def test_calendar_spanning_the_whole_int64_range(lib_built, monkeypatch, plan):
         eres, eown = brute.current_owner(cal, 3, now)
         assert np.array_equal(res, eres) and np.array_equal(own, eown)
     snap.close()
+
+
+def test_lookups_at_the_int64_extremes(lib_built, monkeypatch):
+    """current_owner, upcoming (head, count, owner flags, row lists) and the violation join on calendars whose starts lie at
+    both ends of int64, with `now` at the extremes and horizons `now + period` beyond INT64_MAX (= no upper bound; the sum
+    used to wrap into the past), against a truth computed with Python integers: tools/fuzz_extremes.py."""
+    import importlib.util
+    import os
+    monkeypatch.setenv('TH_GRID_PLAN', 'shared')           # run() sets the plan itself; restore the variable afterwards
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tools', 'fuzz_extremes.py')
+    spec = importlib.util.spec_from_file_location('fuzz_extremes', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run() == 0
