@@ -147,7 +147,8 @@ int th_current_owner(const th_snapshot *h, int64_t now_us, int64_t *out_res_id, 
 /* Per requested uuid, the head and length of upcoming_events_for_resource(uuid, period)
  * (Reservation.py:106-118) as JobSchedulingService.check_current_gpu_slots reads it
  * (tensorhive/core/services/JobSchedulingService.py:94-102): first row in (start, id) order and the
- * number of rows; -1/-1/-1/0 when empty or when the uuid is outside [0, n_uuids). */
+ * number of rows; -1/-1/-1/0 when empty or when the uuid is outside [0, n_uuids).  period_us >= 0; a horizon
+ * now_us + period_us beyond INT64_MAX is clamped there (no upper bound), here and in th_upcoming_owner_flags. */
 int th_upcoming(const th_snapshot *h, int64_t now_us, int64_t period_us, int64_t k, const int64_t *uuids,
                 int64_t *out_first_id, int64_t *out_first_start, int64_t *out_first_owner, int64_t *out_count,
                 int mem, void *stream);
