@@ -196,8 +196,13 @@ extern "C" int th_ring_append(th_ring *r, int64_t k, const int64_t *uuid, const 
         const i64 t = ts_us[i];
         TH_REQUIRE(s.len == 0 || t >= s.t_last, "th_ring_append: timestamps of uuid %lld go backwards", (long long)uuid[i]);
         if (s.len == 0) { s.t_first = t; s.cadence = 0; }
-        else if (s.len == 1) { s.cadence = t > s.t_last ? t - s.t_last : -1; }
-        else if (s.cadence > 0 && t - s.t_last != s.cadence) s.cadence = -1;       // the run is broken: back to probing
+        else {
+            // t >= t_last: the step as an unsigned difference (stamps at both ends of int64 must not overflow); a step of
+            // 2^62 us or more is never a cadence
+            const u64 step = (u64)t - (u64)s.t_last;
+            if (s.len == 1) s.cadence = (step > 0 && step < (1ull << 62)) ? (i64)step : -1;
+            else if (s.cadence > 0 && step != (u64)s.cadence) s.cadence = -1;      // the run is broken: back to probing
+        }
         s.t_last = t;
         pos[(size_t)i] = s.len;        // index inside the region; the region's begin is added below (it may still move)
         s.len += 1;

@@ -696,3 +696,47 @@ def test_both_grid_plans_give_the_same_answers(th, synth, brute, monkeypatch, pl
     want = brute.upcoming_summary(cal, np.arange(48, dtype=np.int64), now, 30 * synth.MIN_US)
     assert all(np.array_equal(a, b) for a, b in zip(got, want))
     snap.close()
+
+
+def test_usage_reduce_with_stamps_at_both_ends_of_int64(th, brute):
+    """Sample logs whose timestamps run from INT64_MIN + 1 to INT64_MAX (the interpolation guess works in doubles, the
+    answer must still be exact), windows anywhere including the extremes: int64 columns, uint8 columns and the ring."""
+    import ctypes as C
+    from tensorhive_fixed_b200 import native
+    I = np.iinfo(np.int64)
+    rng = np.random.default_rng(44)
+    segs = []
+    for kind in range(4):
+        lo = I.min + 1 + np.sort(rng.integers(0, 5_000, size=300))
+        mid = np.sort(rng.integers(-3_000, 3_000, size=300))
+        hi = I.max - 6_000 + np.sort(rng.integers(0, 5_000, size=300))
+        segs.append([np.concatenate([lo, mid, hi]), np.concatenate([lo, hi]), mid, np.concatenate([lo[:1], hi[-1:]])][kind])
+    off = np.concatenate([[0], np.cumsum([len(s) for s in segs])]).astype(np.int64)
+    ts = np.concatenate(segs).astype(np.int64)
+    s_total = int(off[-1])
+    g8 = rng.integers(0, 256, size=s_total, dtype=np.uint8)
+    m8 = rng.integers(0, 256, size=s_total, dtype=np.uint8)
+    w = 3000
+    wu = rng.integers(-1, 5, size=w).astype(np.int64)
+    a = rng.choice(ts, size=w).astype(object) + rng.integers(-3, 4, size=w)
+    b = rng.choice(ts, size=w).astype(object) + rng.integers(-3, 4, size=w)
+    clip = lambda x: min(max(int(x), int(I.min)), int(I.max))
+    ws = np.array([clip(min(x, y)) for x, y in zip(a, b)], np.int64)
+    we = np.array([clip(max(x, y)) for x, y in zip(a, b)], np.int64)
+    ws[:3], we[:3] = [I.min, I.max, I.min], [I.max, I.max, I.min]
+    esg, esm, ecnt = brute.usage_reduce(off, ts, g8.astype(np.int64), m8.astype(np.int64), wu, ws, we)
+    assert (ecnt > 300).any() and (ecnt == 0).any()
+    wide = th.usage_reduce(off, ts, g8.astype(np.int64), m8.astype(np.int64), wu, ws, we)
+    narrow = th.usage_reduce_u8(off, ts, g8, m8, wu, ws, we)
+    for outs in (wide, narrow):
+        assert np.array_equal(outs[2], ecnt) and np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm)
+    # the ring: appended sample by sample per uuid (stamps of a uuid must not decrease), reduced in place
+    lib = native.load()
+    h = C.c_void_p(0)
+    native.check(lib.th_ring_create(0, 16, C.byref(h)))
+    uu = np.repeat(np.arange(4, dtype=np.int64), np.diff(off))
+    native.check(lib.th_ring_append(h, s_total, uu.ctypes.data, ts.ctypes.data, g8.ctypes.data, m8.ctypes.data, None))
+    outs = [np.zeros(w, np.int64) for _ in range(5)]
+    native.check(lib.th_ring_reduce(h, w, wu.ctypes.data, ws.ctypes.data, we.ctypes.data, *[o.ctypes.data for o in outs], 0, None))
+    assert np.array_equal(outs[2], ecnt) and np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm)
+    lib.th_ring_destroy(h)
