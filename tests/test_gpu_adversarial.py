@@ -195,3 +195,49 @@ def test_lookups_at_the_int64_extremes(lib_built, monkeypatch):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     assert mod.run() == 0
+
+
+@pytest.mark.parametrize('plan', ['shared', 'per_uuid'])
+def test_thousands_of_rows_on_a_handful_of_instants(lib_built, monkeypatch, plan):
+    """20 000 rows whose starts take only five values (every grid bucket that is not empty holds thousands of rows with
+    EQUAL starts: the long-bucket bisection, the top-2 self-exclusion inside ties, the radix ordering of long lists)."""
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    monkeypatch.setenv('TH_GRID_PLAN', plan)
+    rng = np.random.default_rng(77)
+    n, u = 20_000, 3
+    instants = synth.T0_US + np.array([0, 1, 1000, 1001, 500_000], np.int64)
+    start = rng.choice(instants, size=n)
+    end = start + rng.choice([0, 1, 2, 999, 1000, 1001, 600_000], size=n)
+    cal = {'id': rng.permutation(np.arange(1, n + 1)).astype(np.int64), 'uuid_id': rng.integers(0, u, size=n).astype(np.int64),
+           'start': start.astype(np.int64), 'end': end.astype(np.int64), 'owner': rng.integers(1, 5, size=n).astype(np.int64),
+           'cancelled': (rng.random(n) < 0.5).astype(np.uint8), 'n_uuids': u}
+    # uuid 2: every row but one is cancelled, and that one is what a self-update must exclude
+    sel2 = np.flatnonzero(cal['uuid_id'] == 2)
+    cal['cancelled'][sel2] = 1
+    cal['cancelled'][sel2[7]] = 0
+    snap = th.Snapshot(0)
+    snap.load(cal['id'], cal['uuid_id'], cal['start'], cal['end'], cal['owner'], cal['cancelled'], n_uuids=u)
+    m = 400
+    qu = rng.integers(0, u, size=m).astype(np.int64)
+    qs = (rng.choice(instants, size=m) + rng.integers(-2, 3, size=m)).astype(np.int64)
+    qe = (qs + rng.choice([0, 1, 2, 998, 1000, 1003, 700_000], size=m)).astype(np.int64)
+    qf = np.where(rng.random(m) < 0.5, -1, rng.choice(cal['id'], size=m)).astype(np.int64)
+    qf[qu == 2] = np.where(rng.random(int((qu == 2).sum())) < 0.5, cal['id'][sel2[7]], qf[qu == 2])
+    for mode, bmode in ((th.MODE_STRICT, brute.STRICT), (th.MODE_INCLUSIVE, brute.INCLUSIVE)):
+        f = qf if mode == th.MODE_STRICT else None
+        fb = qf if mode == th.MODE_STRICT else np.full(m, -1, np.int64)
+        bits = snap.conflict_bitmap(qu, qs, qe, f, mode)
+        assert np.array_equal(np.asarray(bits, bool), np.asarray(brute.conflict_bits(cal, qu, qs, qe, fb, bmode), bool)), mode
+    off, ids, canc = snap.conflict_sets(qu[:60], qs[:60], qe[:60], qf[:60], th.MODE_STRICT)
+    got = csr_to_lists(off, ids)
+    assert got == brute.conflict_sets(cal, qu[:60], qs[:60], qe[:60], qf[:60], brute.STRICT)
+    assert max(len(x) for x in got) > 1000
+    off, ids, canc = snap.conflict_sets(qu[:60], qs[:60], qe[:60], None, th.MODE_UPCOMING)
+    assert csr_to_lists(off, ids) == brute.conflict_sets(cal, qu[:60], qs[:60], qe[:60], np.full(60, -1, np.int64), brute.UPCOMING)
+    for now in [int(x) for x in instants] + [int(instants[2]) + 1]:
+        res, own = snap.current_owner(now)
+        eres, eown = brute.current_owner(cal, u, now)
+        assert np.array_equal(res, eres) and np.array_equal(own, eown)
+    snap.close()
