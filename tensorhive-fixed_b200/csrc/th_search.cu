@@ -142,8 +142,8 @@ __device__ __forceinline__ bool k2_resolve(const ThCellV c, const ThP1 *__restri
         int k = in0 ? 1 : 0;
         i64 mall = in0 ? w[1].y : w[0].y;
 #pragma unroll
-        for (int j = 1; j < BM_PROBE; ++j)
-            if (e[j].x <= qe) { k = j + 1; mall = w[j + 1].y; }
+        for (int j = 1; j < BM_PROBE; ++j)      // (more && cnt > j: for qe = INT64_MAX the default of a row that was not probed is "before qe" too)
+            if (more && cnt > j && e[j].x <= qe) { k = j + 1; mall = w[j + 1].y; }
         if (k == BM_PROBE && cnt > BM_PROBE) {        // long bucket: finish with a binary search
             int lo = pos + BM_PROBE, hi = pos + cnt;
             while (lo < hi) {

@@ -154,6 +154,8 @@ def test_calendar_spanning_the_whole_int64_range(lib_built, monkeypatch, plan):
     hi = I.max - 20_000 + np.sort(rng.integers(0, 10_000, size=40))
     start = np.concatenate([lo, mid, hi, mid + 7]).astype(np.int64)
     end = start + rng.integers(0, 3_000, size=start.size)
+    start[118:120] = [I.max - 1, I.max]                # rows that start and end AT the upper extreme
+    end[118:120] = [I.max, I.max]
     n = start.size
     cal = {'id': rng.permutation(np.arange(1, n + 1)).astype(np.int64),
            'uuid_id': np.concatenate([np.zeros(120, np.int64), np.ones(40, np.int64)]),        # uuid 0 spans everything
@@ -168,6 +170,8 @@ def test_calendar_spanning_the_whole_int64_range(lib_built, monkeypatch, plan):
     qs = np.array([clip(int(a) + int(d)) for a, d in zip(anchor, rng.integers(-2_000, 2_000, size=m))], np.int64)
     qe = np.array([clip(int(a) + int(d)) for a, d in zip(qs, rng.integers(0, 4_000, size=m))], np.int64)
     qs[:4], qe[:4] = [I.min, I.min, I.max - 5, 0], [I.max, I.min + 5, I.max, I.max]
+    qe[4:60] = I.max                                   # many candidates that end at the upper extreme
+    qu[:12] = 0
     qf = np.where(rng.random(m) < 0.5, -1, rng.choice(cal['id'], size=m)).astype(np.int64)
     for mode, bmode in ((th.MODE_STRICT, brute.STRICT), (th.MODE_INCLUSIVE, brute.INCLUSIVE)):
         f = qf if mode == th.MODE_STRICT else None

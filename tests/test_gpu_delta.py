@@ -208,3 +208,40 @@ def test_duplicate_ids_are_refused_and_leave_the_snapshot_as_it_was(lib_built):
     with pytest.raises(ValueError):
         c.apply_delta(upserts=[dict(rows[0], id=-3)])
     c.close()
+
+
+def test_delta_that_stretches_the_calendar_to_both_ends_of_int64(lib_built):
+    """A delta whose rows start near INT64_MIN and INT64_MAX: the span of the calendar (and of two uuids) jumps past
+    2^63 us, the grid is re-planned, and the result equals a fresh load; a second delta removes them again."""
+    import tensorhive_fixed_b200 as th
+    from tensorhive_fixed_b200 import synth
+    from oracle import brute
+    I = np.iinfo(np.int64)
+    u = 12
+    cal = synth.make_calendar(5_000, u, seed=31)
+    table = {k: cal[k].copy() for k in COLS}
+    cur = _fresh(th, table, u)
+    base = int(table['id'].max()) + 1
+    ext = {'id': np.arange(base, base + 6, dtype=np.int64), 'uuid_id': np.array([0, 0, 3, 3, 11, 11], np.int64),
+           'start': np.array([I.min + 1, I.max - 5_000, I.min + 77, I.max - 1, I.min + 1, 0], np.int64),
+           'end': np.array([I.min + 900, I.max - 10, I.min + 78, I.max, I.min + 1, I.max], np.int64),
+           'owner': np.arange(1, 7, dtype=np.int64), 'cancelled': np.array([0, 0, 1, 0, 0, 0], np.uint8)}
+    cur.apply_delta(cur, u, *[ext[k] for k in COLS], np.zeros(0, np.int64))
+    table2 = {k: np.concatenate([table[k], ext[k]]) for k in COLS}
+    ref = _fresh(th, table2, u)
+    assert _same(cur, ref)
+    q = synth.make_queries(dict(table, n_uuids=u), 2000, seed=32)
+    qs, qe = q['start'].copy(), q['end'].copy()
+    qs[:6], qe[:6] = [I.min, I.min, I.max - 3, 0, I.min + 1, I.max], [I.max, I.min + 50, I.max, I.max, I.min + 2, I.max]
+    qu = q['uuid_id'].copy()
+    qu[:6] = [0, 3, 3, 11, 11, 0]
+    for mode, bmode in ((th.MODE_STRICT, brute.STRICT), (th.MODE_INCLUSIVE, brute.INCLUSIVE)):
+        f = q['self_id'] if mode == th.MODE_STRICT else None
+        fb = q['self_id'] if mode == th.MODE_STRICT else np.full(len(qu), -1, np.int64)
+        got = cur.conflict_bitmap(qu, qs, qe, f, mode)
+        assert np.array_equal(np.asarray(got, bool), np.asarray(brute.conflict_bits(dict(table2, n_uuids=u), qu, qs, qe, fb, bmode), bool))
+    cur.apply_delta(cur, u, *[np.zeros(0, np.int64) for _ in range(5)], np.zeros(0, np.uint8), ext['id'])
+    back = _fresh(th, table, u)
+    assert _same(cur, back)
+    for s in (cur, ref, back):
+        s.close()
