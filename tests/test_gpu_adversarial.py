@@ -245,3 +245,16 @@ def test_thousands_of_rows_on_a_handful_of_instants(lib_built, monkeypatch, plan
         eres, eown = brute.current_owner(cal, u, now)
         assert np.array_equal(res, eres) and np.array_equal(own, eown)
     snap.close()
+
+
+def test_odd_table_shapes(lib_built, monkeypatch):
+    """A million uuids and ten rows, no rows at all, one uuid holding every row, 65 536 uuids ...: bitmap, row lists (all
+    three modes), owner table and upcoming against brute force under every grid plan: tools/fuzz_shapes.py."""
+    import importlib.util
+    import os
+    monkeypatch.setenv('TH_GRID_PLAN', 'shared')           # run() sets / clears the plan itself; restored afterwards
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tools', 'fuzz_shapes.py')
+    spec = importlib.util.spec_from_file_location('fuzz_shapes', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run() == 0
