@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(256) sp_rec_kernel(const i64 *__restrict__ hi,
                                                      i64 min_lo, i64 min_hi, ThRec *rec) {
     for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
         ThRec r;
-        r.k0 = (u64)(lo[i] - min_lo); r.k1 = (u32)(hi[i] - min_hi); r.idx = (u32)i;
+        r.k0 = (u64)lo[i] - (u64)min_lo; r.k1 = (u32)((u64)hi[i] - (u64)min_hi); r.idx = (u32)i;
         rec[i] = r;
     }
 }
@@ -127,7 +127,7 @@ extern "C" int th_sort_pairs(int device, int64_t n, const int64_t *k_hi, const i
             PairStats stats;
             SP_CUDA(cudaMemcpyAsync(&stats, d_stats, sizeof(stats), cudaMemcpyDeviceToHost, st));
             SP_CUDA(cudaStreamSynchronize(st));
-            if ((u64)(stats.max_hi - stats.min_hi) >= (1ull << 32)) {
+            if (((u64)stats.max_hi - (u64)stats.min_hi) >= (1ull << 32)) {
                 th_set_error("th_sort_pairs: k_hi spread does not fit 32 bits");
                 rc = TH_EINVAL;
                 break;
@@ -137,8 +137,8 @@ extern "C" int th_sort_pairs(int device, int64_t n, const int64_t *k_hi, const i
             SP_TRY(sc.alloc((void **)&rb, sizeof(ThRec) * zn));
             sp_rec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_hi, (const i64 *)d_lo, n, stats.min_lo, stats.min_hi, ra);
             int passes = 0;
-            SP_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)(stats.max_lo - stats.min_lo)),
-                                 th_bits_for((u64)(stats.max_hi - stats.min_hi)), &sorted, &passes, st));
+            SP_TRY(th_radix_sort(ra, rb, n, th_bits_for(((u64)stats.max_lo - (u64)stats.min_lo)),
+                                 th_bits_for(((u64)stats.max_hi - (u64)stats.min_hi)), &sorted, &passes, st));
             sp_perm_kernel<<<grid, 256, 0, st>>>(sorted, n, (i64 *)d_perm);
             SP_CUDA(cudaGetLastError());
             SP_TRY(th_copy_back(out_perm, d_perm, 8 * zn, mem, st));

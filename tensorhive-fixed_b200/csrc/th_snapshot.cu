@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) ld_idrec_kernel(const i64 *__restrict__ i
                                                        i64 base = 0) {   // rows [base, base + n) of the columns
     for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
         ThRec r;
-        r.k0 = (u64)(id[base + i] - min_id); r.k1 = 0; r.idx = (u32)(base + i);
+        r.k0 = (u64)id[base + i] - (u64)min_id; r.k1 = 0; r.idx = (u32)(base + i);
         rec[i] = r;
     }
 }
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) ld_keyrec_kernel(const i64 *__restrict__ 
     for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (i64)gridDim.x * blockDim.x) {
         const u32 i = order ? order[j].idx : (u32)j;
         ThRec r;
-        r.k0 = (u64)(start[i] - min_start); r.k1 = (u32)uuid[i]; r.idx = i;
+        r.k0 = (u64)start[i] - (u64)min_start; r.k1 = (u32)uuid[i]; r.idx = i;
         rec[j] = r;
     }
 }
@@ -568,12 +568,12 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
                 const int bgrid = th_grid_for(nb, 256 * 4, 8);
                 ld_idrec_kernel<<<bgrid, 256, 0, st>>>((const i64 *)d_id, nb, stats.min_id, ba, presorted);
                 TH_CUDA(cudaGetLastError());
-                TH_TRY(th_radix_sort(ba, bb, nb, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &b_id, &passes, st));
+                TH_TRY(th_radix_sort(ba, bb, nb, th_bits_for((u64)stats.max_id - (u64)stats.min_id), 0, &b_id, &passes, st));
                 passes_total += passes;
                 ThRec *other = (b_id == ba) ? bb : ba;
                 ld_keyrec_kernel<<<bgrid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, b_id, nb, stats.min_start, bc);
                 TH_CUDA(cudaGetLastError());
-                TH_TRY(th_radix_sort(bc, other, nb, th_bits_for((u64)(stats.max_start - stats.min_start)),
+                TH_TRY(th_radix_sort(bc, other, nb, th_bits_for((u64)stats.max_start - (u64)stats.min_start),
                                      th_bits_for((u64)stats.max_uuid), &b_key, &passes, st));
                 passes_total += passes;
                 mg_merge_kernel<<<grid, 256, 0, st>>>(ra, presorted, b_key, nb, (const i64 *)d_id, rb);
@@ -586,7 +586,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
             // sort leaves equal keys in id order (SQLite's scan order for ties).
             ld_idrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_id, n, stats.min_id, ra);
             TH_CUDA(cudaGetLastError());
-            TH_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)(stats.max_id - stats.min_id)), 0, &sorted, &passes, st));
+            TH_TRY(th_radix_sort(ra, rb, n, th_bits_for((u64)stats.max_id - (u64)stats.min_id), 0, &sorted, &passes, st));
             passes_total += passes;
             int *d_dup = nullptr, dup = 0;
             TH_TRY(sc.alloc((void **)&d_dup, sizeof(int)));
@@ -605,7 +605,7 @@ static int th_load_impl(th_snapshot *h, int64_t n, int64_t n_uuids, const int64_
         ld_keyrec_kernel<<<grid, 256, 0, st>>>((const i64 *)d_uuid, (const i64 *)d_start, order, n, stats.min_start,
                                                key_a);
         TH_CUDA(cudaGetLastError());
-        TH_TRY(th_radix_sort(key_a, key_b, n, th_bits_for((u64)(stats.max_start - stats.min_start)),
+        TH_TRY(th_radix_sort(key_a, key_b, n, th_bits_for((u64)stats.max_start - (u64)stats.min_start),
                              th_bits_for((u64)stats.max_uuid), &sorted, &passes, st));
         passes_total += passes;
         }
