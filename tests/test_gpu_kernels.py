@@ -43,7 +43,7 @@ def test_sort_pairs_matches_stable_lexsort(th, n):
     assert np.array_equal(perm, want)
 
 
-@pytest.mark.parametrize('pattern', ['all_equal', 'sorted', 'reversed', 'few_values', 'wide_hi', 'one_bit'])
+@pytest.mark.parametrize('pattern', ['all_equal', 'sorted', 'reversed', 'few_values', 'wide_hi', 'one_bit', 'full_range'])
 def test_sort_pairs_patterns(th, pattern):
     n = 70_000
     rng = np.random.default_rng(11)
@@ -60,6 +60,11 @@ def test_sort_pairs_patterns(th, pattern):
     elif pattern == 'wide_hi':
         lo = rng.integers(0, 1 << 50, size=n, dtype=np.int64)
         hi = rng.integers(0, (1 << 32) - 1, size=n, dtype=np.int64)
+    elif pattern == 'full_range':       # the low key spans all of int64 (its extremes included), the high key is signed
+        I = np.iinfo(np.int64)
+        lo = rng.integers(I.min, I.max, size=n, dtype=np.int64, endpoint=True)
+        lo[:4] = [I.min, I.max, I.min, I.max]
+        hi = rng.integers(-3, 4, size=n, dtype=np.int64)
     else:
         lo = (rng.integers(0, 2, size=n, dtype=np.int64)) << 40
     perm = th.sort_pairs(hi, lo)
