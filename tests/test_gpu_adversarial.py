@@ -258,3 +258,16 @@ def test_odd_table_shapes(lib_built, monkeypatch):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     assert mod.run() == 0
+
+
+def test_random_worlds_of_four_styles(lib_built, monkeypatch):
+    """tools/fuzz_worlds.py on 48 seeds: tiny time grids, bursts (long buckets), nested intervals over 13 orders of
+    magnitude, synthetic walks; random grid plan; EVERY entry point (packed format included) against brute force."""
+    import importlib.util
+    import os
+    monkeypatch.setenv('TH_GRID_PLAN', 'shared')           # check_world sets / clears the plan; restored afterwards
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tools', 'fuzz_worlds.py')
+    spec = importlib.util.spec_from_file_location('fuzz_worlds', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run(48, 1000) == 0
