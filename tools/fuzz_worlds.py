@@ -133,8 +133,74 @@ def check_world(seed, verbose=True):
     return len(set(bad))
 
 
-def run(n_worlds=60, first=0, verbose=True):
-    return sum(check_world(s, verbose) for s in range(first, first + n_worlds))
+COLS = ('id', 'uuid_id', 'start', 'end', 'owner', 'cancelled')
+
+
+def check_delta(seed, verbose=True):
+    """Three random deltas (deletes, moved / re-flagged rows, inserts taken from another world, sometimes on new uuids) on
+    a world of the seed's style: after each one the snapshot must export exactly what a fresh load of the table exports."""
+    cal, rng = make_world(seed)
+    other, _ = make_world(seed + 7777)
+    u = cal['n_uuids']
+    table = {k: cal[k].copy() for k in COLS}
+    cur = th.Snapshot(0)
+    cur.load(*[table[k] for k in COLS], n_uuids=u)
+    spare = th.Snapshot(0)
+    next_id = int(table['id'].max()) + 1 if len(table['id']) else 1
+    bad = []
+    for step in range(3):
+        n = len(table['id'])
+        del_pos = rng.choice(n, size=int(rng.integers(0, n // 3 + 1)), replace=False) if n else np.zeros(0, np.int64)
+        rest = np.setdiff1d(np.arange(n), del_pos)
+        upd_pos = rng.choice(rest, size=int(rng.integers(0, len(rest) // 3 + 1)), replace=False) if len(rest) else np.zeros(0, np.int64)
+        n_ins = int(rng.integers(0, len(other['id']) + 1))
+        sel = rng.choice(len(other['id']), size=n_ins, replace=False) if n_ins else np.zeros(0, np.int64)
+        ins = {k: other[k][sel].copy() for k in COLS}
+        ins['id'] = np.arange(next_id, next_id + n_ins, dtype=np.int64)
+        next_id += n_ins
+        u = max(u, other['n_uuids']) if n_ins else u
+        upd = {k: table[k][upd_pos].copy() for k in COLS}
+        shift = rng.choice([0, 1, -1, 10**6, -10**9], size=len(upd_pos))
+        upd['start'] = upd['start'] + shift
+        upd['end'] = np.maximum(upd['end'] + rng.choice([0, 1, 10**6], size=len(upd_pos)) + shift, upd['start'])
+        upd['cancelled'] = (rng.random(len(upd_pos)) < 0.4).astype(np.uint8)
+        ups = {k: np.concatenate([upd[k], ins[k]]) for k in COLS}
+        order = rng.permutation(len(ups['id']))
+        ups = {k: v[order] for k, v in ups.items()}
+        del_ids = table['id'][del_pos].copy()
+        keep = np.ones(n, bool)
+        keep[del_pos] = False
+        keep[upd_pos] = False
+        table = {k: np.concatenate([table[k][keep], ups[k]]) for k in COLS}
+        in_place = bool((seed + step) & 1)
+        dst = cur if in_place else spare
+        dst.apply_delta(cur, u, *[ups[k] for k in COLS], del_ids)
+        if not in_place:
+            cur, spare = dst, cur
+        ref = th.Snapshot(0)
+        ref.load(*[table[k] for k in COLS], n_uuids=u)
+        ea, eb = cur.export(), ref.export()
+        if not all(np.array_equal(ea[k], eb[k]) for k in ea):
+            bad.append('export after delta %d' % step)
+        full = dict(table, n_uuids=u)
+        qu, qs, qe, qf = make_queries(full, rng, 800)
+        got = np.asarray(cur.conflict_bitmap(qu, qs, qe, qf), bool)
+        if not np.array_equal(got, np.asarray(brute.conflict_bits(full, qu, qs, qe, qf), bool)):
+            bad.append('bitmap after delta %d' % step)
+        ref.close()
+    cur.close()
+    spare.close()
+    if bad and verbose:
+        print('seed', seed, 'style', seed % 4, 'delta ->', bad)
+    return len(bad)
+
+
+def run(n_worlds=60, first=0, verbose=True, deltas=True):
+    bad = sum(check_world(s, verbose) for s in range(first, first + n_worlds))
+    if deltas:
+        os.environ.pop('TH_GRID_PLAN', None)
+        bad += sum(check_delta(s, verbose) for s in range(first, first + n_worlds))
+    return bad
 
 
 if __name__ == '__main__':
