@@ -745,3 +745,15 @@ def test_usage_reduce_with_stamps_at_both_ends_of_int64(th, brute):
     native.check(lib.th_ring_reduce(h, w, wu.ctypes.data, ws.ctypes.data, we.ctypes.data, *[o.ctypes.data for o in outs], 0, None))
     assert np.array_equal(outs[2], ecnt) and np.array_equal(outs[0], esg) and np.array_equal(outs[1], esm)
     lib.th_ring_destroy(h)
+
+
+def test_usage_random_logs_of_six_kinds(th):
+    """tools/fuzz_usage.py on 40 seeds: exact cadence, jitter, missing stretches, repeated stamps, bursts, one break in a
+    run; int64 columns (also negative values), uint8 columns and the ring appended in random batches, against brute force."""
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tools', 'fuzz_usage.py')
+    spec = importlib.util.spec_from_file_location('fuzz_usage', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.run(40, 2000) == 0
