@@ -50,6 +50,19 @@ def main():
         px.check()
         fused = router.decode(g.cpu().numpy())
         ok = ok and bool(np.array_equal(fused, want))
+    # ragged steps through the same peer group: odd batch sizes, ranks with very different shares, ranks with NO query at
+    # all (their kernel only receives), back to back
+    hot = np.flatnonzero((q['uuid_id'] >= bounds[0]) & (q['uuid_id'] < bounds[1]))          # candidates of rank 0 only
+    last = np.flatnonzero(q['uuid_id'] >= bounds[world - 1])
+    subsets = [np.arange(k) for k in (1, 31, 33, 1000, 4097, 77_777)] + [hot[:5000], last[:37], hot[:1], np.arange(0)]
+    for sub in subsets:
+        r2 = sharding.Router(q['uuid_id'][sub], bounds)
+        i2 = sub[r2.local_indices(rank)]
+        q2 = [t(r2.local_uuid(q['uuid_id'][sub], rank)), t(q['start'][i2]), t(q['end'][i2]), t(q['self_id'][i2])]
+        g = px.conflict_words(snap, *q2, counts=r2.counts)
+        torch.cuda.synchronize()
+        px.check()
+        ok = ok and bool(np.array_equal(r2.decode(g.cpu().numpy()), want[sub]))
     # the other two gathers of section 8e: per-uuid (cur_res_id, cur_owner) from K3 and window averages from K4
     now = int(np.median(cal['start']))
     gather64 = lambda v: sharding.torch_all_gather_i64(v, dev)
