@@ -937,14 +937,16 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     // large batches (would_interfere for a whole candidate list): 4 lanes per query, eight queries per warp (1 M
     // config-2 candidates, 1.25 M rows returned: 0.54 / 0.37 / 0.26 / 0.185 / 0.163 ms with 32 / 16 / 8 / 4 / 2 lanes; 4 keeps long ranges affordable -- the walk is
     // a chain of dependent probes, so queries in flight are what counts); a few calendar ranges: one warp per query
-    const bool narrow = m >= 32768;
-    const int wgrid = th_grid_for(m, narrow ? CS_THREADS / 4 : CS_WARPS, 16);
-    if (narrow)
-        k2_sets_count_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
-                                                              (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
-    else
-        k2_sets_count_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s,
-                                                               (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
+    // ... and two lanes for batches of 256 K candidates and more (1 M candidates: 0.170 -> 0.146 ms)
+    const int lanes = m >= (1 << 18) ? 2 : (m >= 32768 ? 4 : 32);
+    const int wgrid = th_grid_for(m, CS_THREADS / lanes, 16);
+#define CS_BY_LANES(KERNEL, ...)                                                           \
+    do {                                                                                   \
+        if (lanes == 2) KERNEL<2><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);              \
+        else if (lanes == 4) KERNEL<4><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);         \
+        else KERNEL<32><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);                        \
+    } while (0)
+    CS_BY_LANES(k2_sets_count_kernel, v, h->n_uuids, m, (const i64 *)d_u, (const i64 *)d_s, (const i64 *)d_e, (const i64 *)d_f, mode, d_cnt, d_beg, d_end);
     TH_CUDA(cudaGetLastError());
     i64 *d_total;
     TH_TRY(sc.alloc((void **)&d_total, 16));       // [0] = total rows, [1] = longest list
@@ -957,26 +959,12 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     u8 *sp_canc = nullptr;
     if (spec) {
         if (mode == TH_MODE_UPCOMING) {
-            if (narrow)
-                k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                     (const i64 *)d_off, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
-            else
-                k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                      (const i64 *)d_off, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
+            CS_BY_LANES(k2_sets_fill_kernel, v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end, (const i64 *)d_off, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
         } else {
             TH_TRY(sc.alloc((void **)&sp_ids, 8 * (size_t)capacity));
             TH_TRY(sc.alloc((void **)&sp_canc, (size_t)capacity));
-            if (narrow) {
-                k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                     (const i64 *)d_off, sp_ids, sp_canc, (const i64 *)d_total, (i64)capacity);
-                k2_sets_order_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, sp_ids, sp_canc, (i64 *)out_ids,
-                                                                      (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
-            } else {
-                k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                      (const i64 *)d_off, sp_ids, sp_canc, (const i64 *)d_total, (i64)capacity);
-                k2_sets_order_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, sp_ids, sp_canc, (i64 *)out_ids,
-                                                                      (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
-            }
+            CS_BY_LANES(k2_sets_fill_kernel, v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end, (const i64 *)d_off, sp_ids, sp_canc, (const i64 *)d_total, (i64)capacity);
+            CS_BY_LANES(k2_sets_order_kernel, m, (const i64 *)d_off, sp_ids, sp_canc, (i64 *)out_ids, (u8 *)out_cancelled_u8, (const i64 *)d_total, (i64)capacity);
         }
         TH_CUDA(cudaGetLastError());
     }
@@ -1010,30 +998,15 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     TH_TRY(sc.out(out_ids, 8 * (size_t)total, mem, &d_ids));
     TH_TRY(sc.out(out_cancelled_u8, (size_t)total, mem, &d_canc));
     if (mode == TH_MODE_UPCOMING) {
-        if (narrow)
-            k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                 (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
-        else
-            k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                  (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
+        CS_BY_LANES(k2_sets_fill_kernel, v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end, (const i64 *)d_off, (i64 *)d_ids, (u8 *)d_canc);
     } else {
         i64 *t_ids; u8 *t_canc;
         TH_TRY(sc.alloc((void **)&t_ids, 8 * (size_t)total));
         TH_TRY(sc.alloc((void **)&t_canc, (size_t)total));
-        if (narrow)
-            k2_sets_fill_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                 (const i64 *)d_off, t_ids, t_canc);
-        else
-            k2_sets_fill_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end,
-                                                                  (const i64 *)d_off, t_ids, t_canc);
+        CS_BY_LANES(k2_sets_fill_kernel, v, m, (const i64 *)d_s, (const i64 *)d_f, mode, d_beg, d_end, (const i64 *)d_off, t_ids, t_canc);
         if (longest <= 64 || total >= (1ll << 30) || m >= (1ll << 32)) {
             // short lists: rank by counting inside the warp (c^2 / 32 compares per list)
-            if (narrow)
-                k2_sets_order_kernel<4><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
-                                                                      (u8 *)d_canc);
-            else
-                k2_sets_order_kernel<32><<<wgrid, CS_THREADS, 0, st>>>(m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids,
-                                                                       (u8 *)d_canc);
+            CS_BY_LANES(k2_sets_order_kernel, m, (const i64 *)d_off, t_ids, t_canc, (i64 *)d_ids, (u8 *)d_canc);
         } else {
             // calendar views return thousands of rows per uuid: sort all of them by (query, id) with K1 instead
             ThRec *ra, *rb, *sorted;
@@ -1060,6 +1033,8 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
 // same stream polls the slots it expects and writes the compact [world][words_per_rank] words the caller reads.
 // No NCCL call, no fence, no host round trip.  Device pointers only.  m_per_rank (host, world entries, may be NULL =
 // "every rank has m") tells the receiver how many queries each rank contributes this step.
+#undef CS_BY_LANES
+
 static int k2_launch_unpack(th_peer *peer, cudaStream_t st) {
     const int parity = (int)(peer->epoch & 1u);
     const i64 total = (i64)peer->world * peer->words_per_rank;
