@@ -128,3 +128,22 @@ def test_router_round_trip_with_unknown_uuids():
     for k in range(3):
         stack[k, :] = _pack(np.concatenate([verdict[r.local_indices(k)], np.zeros(32 * r.words_per_rank, bool)])[:32 * r.words_per_rank])
     assert np.array_equal(r.decode(stack), verdict)
+
+
+@pytest.mark.parametrize('world', [1, 2, 8, 255, 300])
+def test_router_groups_stably_for_any_world_size(world):
+    """owner_rank counts ranks in one byte up to 255 ranks (numpy then groups with a counting sort) and in int64 beyond;
+    both must give the grouping of a stable sort by owner, and the owner a binary search of the bounds would give."""
+    from tensorhive_fixed_b200 import sharding
+    rng = np.random.default_rng(world)
+    n_uuids = 5000
+    cuts = np.sort(rng.choice(np.arange(1, n_uuids), size=world - 1, replace=False)) if world > 1 else np.zeros(0, np.int64)
+    bounds = np.concatenate([[0], cuts, [n_uuids]]).astype(np.int64)
+    q = rng.integers(-3, n_uuids + 3, size=20_000).astype(np.int64)
+    r = sharding.Router(q, bounds)
+    want = np.searchsorted(bounds[1:world], q, side='right')
+    want[(q < 0) | (q >= n_uuids)] = 0
+    assert np.array_equal(np.asarray(r.owner, np.int64), want)
+    assert np.array_equal(r.perm, np.argsort(want, kind='stable'))
+    assert np.array_equal(r.counts, np.bincount(want, minlength=world))
+    assert int(r.counts.sum()) == len(q)
