@@ -516,7 +516,8 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_count_kernel(RowView v, i6
                     const i64 s = (mode == TH_MODE_UPCOMING) ? th_ld8(&v.p1[j].start) : 0;
                     mt = cs_match(mode, s, e.x, e.y, qs, self);
                 }
-                cnt += __popc(__ballot_sync(gmask, mt) & gmask);
+                if (G == 1) cnt += mt ? 1 : 0;                  // one lane per query: nothing to vote on
+                else cnt += __popc(__ballot_sync(gmask, mt) & gmask);
                 beg = c0;
                 c1 = c0;
             }
@@ -554,6 +555,14 @@ __global__ void __launch_bounds__(CS_THREADS) k2_sets_fill_kernel(RowView v, i64
                 e = th_ld16(&v.p3[j]);
                 const i64 s = (mode == TH_MODE_UPCOMING) ? th_ld8(&v.p1[j].start) : 0;
                 mt = cs_match(mode, s, e.x, e.y, qs, self);
+            }
+            if (G == 1) {                                       // one lane per query: nothing to vote on
+                if (mt) {
+                    out_ids[o] = th_idc_id(e.y);
+                    out_canc[o] = th_idc_cancelled(e.y) ? 1 : 0;
+                    ++o;
+                }
+                continue;
             }
             const u32 bal = __ballot_sync(gmask, mt) & gmask;
             if (mt) {
@@ -937,12 +946,15 @@ extern "C" int th_conflict_sets(const th_snapshot *h, int64_t m, const int64_t *
     // large batches (would_interfere for a whole candidate list): 4 lanes per query, eight queries per warp (1 M
     // config-2 candidates, 1.25 M rows returned: 0.54 / 0.37 / 0.26 / 0.185 / 0.163 ms with 32 / 16 / 8 / 4 / 2 lanes; 4 keeps long ranges affordable -- the walk is
     // a chain of dependent probes, so queries in flight are what counts); a few calendar ranges: one warp per query
-    // ... and two lanes for batches of 256 K candidates and more (1 M candidates: 0.170 -> 0.146 ms)
-    const int lanes = m >= (1 << 18) ? 2 : (m >= 32768 ? 4 : 32);
+    // ... and ONE lane per query for batches of 256 K candidates and more, where a list is a row or two (1 M candidates:
+    // 0.170 ms with four lanes, 0.146 with two, 0.129 with one: no votes at all, 32 queries in flight per warp)
+    int lanes = m >= (1 << 18) ? 1 : (m >= 32768 ? 4 : 32);
+    if (const char *e = getenv("TH_SETS_LANES")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 32) lanes = v; }   // diagnostics
     const int wgrid = th_grid_for(m, CS_THREADS / lanes, 16);
 #define CS_BY_LANES(KERNEL, ...)                                                           \
     do {                                                                                   \
-        if (lanes == 2) KERNEL<2><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);              \
+        if (lanes == 1) KERNEL<1><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);              \
+        else if (lanes == 2) KERNEL<2><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);         \
         else if (lanes == 4) KERNEL<4><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);         \
         else KERNEL<32><<<wgrid, CS_THREADS, 0, st>>>(__VA_ARGS__);                        \
     } while (0)

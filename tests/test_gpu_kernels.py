@@ -197,7 +197,7 @@ def test_bad_arguments_are_reported_not_thrown_across_the_abi(th, synth):
 
 
 # ---- K2 row lists ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize('m', [5000, 40_000, 270_000])       # one warp / four lanes (>= 32 768) / two lanes (>= 262 144) per query
+@pytest.mark.parametrize('m', [5000, 40_000, 270_000])       # one warp / four lanes (>= 32 768) / one lane (>= 262 144) per query
 @pytest.mark.parametrize('mode_name', ['STRICT', 'INCLUSIVE', 'UPCOMING'])
 def test_conflict_sets_match_brute_force(th, synth, brute, mode_name, m):
     cal = synth.make_calendar(30_000, 40, seed=77, skew=0.8)
