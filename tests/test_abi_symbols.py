@@ -53,3 +53,28 @@ def test_header_is_plain_c(tmp_path):
                     os.path.join(ROOT, 'include', 'th_b200.h')], check=True)
     subprocess.run(['gcc', '-std=c99', '-Wall', '-Werror', '-I', os.path.join(ROOT, 'include'), '-c', str(src), '-o',
                     str(tmp_path / 'use.o')], check=True)
+
+
+def test_a_missing_library_fails_loudly_and_nothing_falls_back(tmp_path):
+    """No CPU path hides behind the product API: with the library absent every entry raises ImportError (and the package
+    itself never imports oracle/)."""
+    import subprocess
+    import sys
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import tensorhive_fixed_b200 as th\n"
+        "assert not any(m == 'oracle' or m.startswith('oracle.') for m in sys.modules)\n"
+        "z = np.zeros(1, np.int64)\n"
+        "for call in (lambda: th.Snapshot(0), lambda: th.usage_reduce(np.array([0, 1]), z, z, z, z, z, z)):\n"
+        "    try:\n"
+        "        call()\n"
+        "    except ImportError as e:\n"
+        "        assert 'no CPU' in str(e) or 'missing' in str(e)\n"
+        "    else:\n"
+        "        raise SystemExit('call succeeded without the library')\n"
+        "print('loud')\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TH_B200_LIB=str(tmp_path / 'nowhere' / 'libth_b200.so'))
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0 and 'loud' in out.stdout, out.stdout + out.stderr
