@@ -7,6 +7,7 @@ import pytest
 
 import test_gpu_dropin as G
 import test_gpu_model_vectors as M
+import test_gpu_exec_vectors as E
 from oracle import brute
 
 
@@ -85,8 +86,12 @@ def _fake_usage_reduce(off, ts, gpu, mem, wu, ws, we, device=0):
 
 @pytest.fixture()
 def dropin(monkeypatch):
+    import os
+    import time
     import tensorhive_fixed_b200.calendar as calmod
     from tensorhive_fixed_b200 import dropin as d
+    monkeypatch.setenv('TZ', 'UTC')          # the executed-reference vectors were made with TZ=UTC (utc2local)
+    time.tzset()
     monkeypatch.setattr(calmod, 'Snapshot', FakeSnapshot)
     monkeypatch.setattr(d.api, 'usage_reduce', _fake_usage_reduce)
     monkeypatch.setattr(d.api, 'usage_reduce_u8', _fake_usage_reduce)
@@ -107,6 +112,8 @@ test_calendar_view = G.test_calendar_view_controller
 # the host logic of the drop-in against the executed reference's model vectors (queries and the write path)
 test_model_methods = M.test_model_methods_match_the_executed_reference
 test_write_path = M.test_write_path_matches_the_executed_reference
+# ... and the service loops (V, J1-J3) against the vectors of the executed reference services
+test_services = E.test_services_match_the_executed_reference
 
 
 def test_calendar_delta_bookkeeping(dropin):
