@@ -86,7 +86,6 @@ def _fake_usage_reduce(off, ts, gpu, mem, wu, ws, we, device=0):
 
 @pytest.fixture()
 def dropin(monkeypatch):
-    import os
     import time
     import tensorhive_fixed_b200.calendar as calmod
     from tensorhive_fixed_b200 import dropin as d
