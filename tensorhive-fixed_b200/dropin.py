@@ -638,7 +638,8 @@ def utc2local(utc: _dt.datetime) -> _dt.datetime:
     # tensorhive/core/utils/time.py:5-9
     import time
     epoch = time.mktime(utc.timetuple())
-    offset = _dt.datetime.fromtimestamp(epoch) - _dt.datetime.utcfromtimestamp(epoch)
+    # (the reference calls datetime.utcfromtimestamp, deprecated since Python 3.12: the same naive UTC value)
+    offset = _dt.datetime.fromtimestamp(epoch) - _dt.datetime.fromtimestamp(epoch, _dt.timezone.utc).replace(tzinfo=None)
     return utc + offset
 
 
