@@ -10,6 +10,8 @@ What runs here is the unmodified text of (paths relative to /root/reference)
                                      check_assertions :42-55, the is_cancelled / start / end / duration hybrids :57-86
   tensorhive/models/CRUDModel.py     save :21-39, destroy :41-50, get :52-65
   tensorhive/utils/DateUtils.py      try_parse_string (the start / end setters go through it)
+  tensorhive/core/utils/ReservationVerifier.py   update_user_reservations_statuses :90-109, widening case (section 8f.2),
+                                     with is_reservation_allowed -- the restriction walk, out of scope -- replaced by a fixed predicate
 
 loaded as modules under their real dotted names with `importlib`.  SQLAlchemy 1.3.0 is not installable in this image,
 so `sys.modules['sqlalchemy']` is a stand-in for the handful of operators those methods use.  It evaluates the
@@ -58,6 +60,7 @@ from tensorhive_fixed_b200 import synth                             # noqa: E402
 EXECUTED = {
     'tensorhive/utils/DateUtils.py': ['DateUtils.try_parse_string :47-59', 'parse_string :13-26'],
     'tensorhive/models/CRUDModel.py': ['CRUDModel.save :21-39', 'destroy :41-50', 'get :52-65'],
+    'tensorhive/core/utils/ReservationVerifier.py': ['ReservationVerifier.update_user_reservations_statuses :90-109'],
     'tensorhive/models/Reservation.py': ['columns :14-37', 'check_assertions :42-55', 'duration / start / end hybrids :57-78',
                                          'is_cancelled :80-86', 'current_events :88-104',
                                          'upcoming_events_for_resource :106-118', 'would_interfere :120-130',
@@ -324,6 +327,11 @@ def load_reference():
     ref['dateutils'] = _load('tensorhive/utils/DateUtils.py')
     ref['crud'] = _load('tensorhive/models/CRUDModel.py')
     ref['model'] = _load('tensorhive/models/Reservation.py')
+    _package('tensorhive.core')
+    _package('tensorhive.core.utils')
+    _module('tensorhive.models.Resource', Resource=type('Resource', (), {}))
+    ref['verifier'] = _load('tensorhive/core/utils/ReservationVerifier.py')
+    ref['verifier'].datetime = _FrozenDateTime                     # `datetime.utcnow()` at ReservationVerifier.py:100
     # `datetime.datetime.utcnow()` at Reservation.py:93,108; the isinstance checks at :141-142 see the same class
     ref['model'].datetime = types.SimpleNamespace(datetime=_FrozenDateTime, timedelta=dt.timedelta)
     logging.getLogger('tensorhive').setLevel(logging.CRITICAL + 1)          # save() logs every refused row
@@ -545,6 +553,49 @@ def run_write_script(ref, script):
     return {'steps': log, 'final_table': table}
 
 
+def make_verifier_world(seed):
+    """Valid reservations (30 min slots, 30 min ... 3 h long, two GPUs, two users), many of them cancelled, built through
+    the reference's own save() so that live rows never overlap; then `now` somewhere inside the calendar."""
+    rng = np.random.default_rng(9000 + seed)
+    H = 1_800_000_000
+    rows = []
+    for _ in range(int(rng.integers(30, 90))):
+        start = synth.T0_US + int(rng.integers(0, 40)) * H
+        rows.append({'user_id': int(rng.integers(1, 3)), 'resource_id': synth.uuid_string(int(rng.integers(0, 2))),
+                     'start_us': start, 'end_us': start + int(rng.integers(1, 7)) * H,
+                     'is_cancelled': bool(rng.random() < 0.7)})
+    return {'seed': seed, 'candidates': rows, 'now_us': synth.T0_US + int(rng.integers(0, 12)) * H + int(rng.integers(0, 2)),
+            'user_id': int(rng.integers(1, 3)), 'denied_mod': int(rng.integers(2, 6))}
+
+
+def run_verifier(ref, w):
+    """Builds the table with save() (refused candidates are dropped), then runs the reference's
+    update_user_reservations_statuses for the widening case with `is_reservation_allowed` replaced by a deterministic
+    predicate (id % denied_mod != 0: the restriction walk itself is out of scope) and records what it restored, in order."""
+    R = ref['model'].Reservation
+    V = ref['verifier'].ReservationVerifier
+    Table.rows, Table.seq = [], 0
+    _FrozenDateTime.now_us = w['now_us']
+    for c in w['candidates']:
+        r = R(user_id=c['user_id'], title='T', description='D', resource_id=c['resource_id'], start=at(c['start_us']),
+              end=at(c['end_us']))
+        r.is_cancelled = c['is_cancelled']
+        try:
+            r.save()
+        except AssertionError:
+            pass
+    table = [[r.id, r.resource_id, us_of(r._start), us_of(r._end), r.user_id, None if r._is_cancelled is None else int(r._is_cancelled)]
+             for r in sorted(Table.rows, key=lambda r: r.id)]
+    user = types.SimpleNamespace(id=w['user_id'])
+    mine = [r for r in sorted(Table.rows, key=lambda r: r.id) if r.user_id == w['user_id']]    # the relationship loads by primary key
+    user.get_reservations = lambda include_cancelled=False: mine if include_cancelled else [r for r in mine if not r.is_cancelled]
+    before = {r.id: bool(r.is_cancelled) for r in mine}
+    V.is_reservation_allowed = classmethod(lambda cls, u, r: r.id % w['denied_mod'] != 0)
+    V.update_user_reservations_statuses(user, True)
+    restored = [r.id for r in mine if before[r.id] and not r.is_cancelled]
+    return {'table': table, 'restored': restored}
+
+
 def main():
     ref = load_reference()
     ran = selfcheck(ref)
@@ -558,6 +609,11 @@ def main():
         s = make_write_script(seed)
         s['expect'] = run_write_script(ref, s)
         scripts.append(s)
+    verifier_worlds = []
+    for seed in range(12):
+        w = make_verifier_world(seed)
+        w['expect'] = run_verifier(ref, w)
+        verifier_worlds.append(w)
     header = {
         'what': 'inputs and outputs of the reference\'s own Reservation model methods, executed under an expression-'
                 'evaluating stand-in for SQLAlchemy (see tests/golden/make_reference_model_vectors.py)',
@@ -572,11 +628,13 @@ def main():
     }
     path = os.path.join(HERE, 'reference_model_vectors.json')
     with open(path, 'w') as f:
-        json.dump({'header': header, 'worlds': worlds, 'write_scripts': scripts}, f, separators=(',', ':'))
+        json.dump({'header': header, 'worlds': worlds, 'write_scripts': scripts, 'verifier_worlds': verifier_worlds}, f,
+                  separators=(',', ':'))
     n_probe = sum(len(v) for w in worlds for v in w['probes'].values())
     n_true = sum(x['verdict'] for w in worlds for x in w['expect']['interfere'])
     print('wrote %s: %d worlds, %d probes (%d interfering), %d write scripts, %.0f KB' % (
         path, len(worlds), n_probe, n_true, len(scripts), os.path.getsize(path) / 1e3))
+    print(' verifier worlds:', [(len(w['expect']['table']), len(w['expect']['restored'])) for w in verifier_worlds])
     for s in scripts:
         res = [x['result'] + (':' + x.get('message', '')[:28] if 'message' in x else '') for x in s['expect']['steps']]
         print(' script %d:' % s['seed'], {k: res.count(k) for k in sorted(set(res))})

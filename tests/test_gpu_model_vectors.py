@@ -172,3 +172,15 @@ def test_write_path_matches_the_executed_reference(dropin, sc):
               r.user_id, None if r._is_cancelled is None else int(r._is_cancelled)] for r in (R.get(i) for i in sorted(live))]
     assert final == sc['expect']['final_table']
     cal.close()
+
+
+@pytest.mark.parametrize('w', VEC['verifier_worlds'], ids=['verifier%d' % w['seed'] for w in VEC['verifier_worlds']])
+def test_bulk_revalidation_matches_the_executed_reference(dropin, w):
+    """ReservationVerifier.update_user_reservations_statuses, widening case (ReservationVerifier.py:90-109), executed from
+    the reference's source with `is_reservation_allowed` replaced by a fixed predicate: the same reservations come back
+    from the drop-in's batched form, in the same order (one restored earlier is a live row for the ones after it)."""
+    cal, _clock = _bind(dropin, w['expect']['table'], w['now_us'])
+    mine = sorted((dropin.Reservation.get(r[0]) for r in w['expect']['table'] if r[4] == w['user_id']), key=lambda r: r.id)
+    back = dropin.reservations_that_may_be_restored(mine, is_allowed=lambda r: r.id % w['denied_mod'] != 0)
+    assert [r.id for r in back] == w['expect']['restored']
+    cal.close()
