@@ -12,6 +12,8 @@ What runs here is the unmodified text of (paths relative to /root/reference)
   tensorhive/utils/DateUtils.py      try_parse_string (the start / end setters go through it)
   tensorhive/core/utils/ReservationVerifier.py   update_user_reservations_statuses :90-109, widening case (section 8f.2),
                                      with is_reservation_allowed -- the restriction walk, out of scope -- replaced by a fixed predicate
+  tensorhive/controllers/reservation.py   get_selected :31-55, the calendar-view endpoint (section 8f.4), with the real
+                                     response strings of controllers/responses.yml and Reservation.as_dict / CRUDModel.as_dict
 
 loaded as modules under their real dotted names with `importlib`.  SQLAlchemy 1.3.0 is not installable in this image,
 so `sys.modules['sqlalchemy']` is a stand-in for the handful of operators those methods use.  It evaluates the
@@ -61,6 +63,7 @@ EXECUTED = {
     'tensorhive/utils/DateUtils.py': ['DateUtils.try_parse_string :47-59', 'parse_string :13-26'],
     'tensorhive/models/CRUDModel.py': ['CRUDModel.save :21-39', 'destroy :41-50', 'get :52-65'],
     'tensorhive/core/utils/ReservationVerifier.py': ['ReservationVerifier.update_user_reservations_statuses :90-109'],
+    'tensorhive/controllers/reservation.py': ['get_selected :31-55 (+ Reservation.as_dict :165-168, CRUDModel.as_dict :72-94)'],
     'tensorhive/models/Reservation.py': ['columns :14-37', 'check_assertions :42-55', 'duration / start / end hybrids :57-78',
                                          'is_cancelled :80-86', 'current_events :88-104',
                                          'upcoming_events_for_resource :106-118', 'would_interfere :120-130',
@@ -263,7 +266,12 @@ class Base:
             setattr(self, k, v)
 
 
-class _FrozenDateTime(dt.datetime):
+class _FrozenMeta(type):
+    def __instancecheck__(cls, inst):                   # the reference's `isinstance(x, datetime.datetime)` checks
+        return isinstance(inst, dt.datetime)
+
+
+class _FrozenDateTime(dt.datetime, metaclass=_FrozenMeta):
     now_us = 0
 
     @classmethod
@@ -310,6 +318,16 @@ def _load(rel):
     return mod
 
 
+def _camelcase(string):
+    """stringcase 1.2.0 `camelcase` (requirements: stringcase), restated: drop a leading separator, lower the first letter,
+    upper-case the letter after each of - _ . and whitespace."""
+    import re
+    string = re.sub(r"^[\-_\.]", '', str(string))
+    if not string:
+        return string
+    return string[0].lower() + re.sub(r"[\-_\.\s]([a-z])", lambda m: m.group(1).upper(), string[1:])
+
+
 def load_reference():
     for pkg in ('tensorhive', 'tensorhive.models', 'tensorhive.utils'):
         _package(pkg)
@@ -321,7 +339,7 @@ def load_reference():
     _module('sqlalchemy.orm', relationship=lambda *a, **k: None, backref=lambda *a, **k: None)
     _module('sqlalchemy.orm.exc', NoResultFound=NoResultFound, MultipleResultsFound=MultipleResultsFound)
     _module('sqlalchemy.exc', SQLAlchemyError=SQLAlchemyError, IntegrityError=type('IntegrityError', (SQLAlchemyError,), {}))
-    _module('stringcase', camelcase=lambda s: s)                   # only as_dict uses it; not on this path
+    _module('stringcase', camelcase=_camelcase, snakecase=lambda s: s)
     _module('tensorhive.database', db_session=_Session(), Base=Base)
     ref = {}
     ref['dateutils'] = _load('tensorhive/utils/DateUtils.py')
@@ -334,6 +352,17 @@ def load_reference():
     ref['verifier'].datetime = _FrozenDateTime                     # `datetime.utcnow()` at ReservationVerifier.py:100
     # `datetime.datetime.utcnow()` at Reservation.py:93,108; the isinstance checks at :141-142 see the same class
     ref['model'].datetime = types.SimpleNamespace(datetime=_FrozenDateTime, timedelta=dt.timedelta)
+    import yaml
+    with open(os.path.join(REF, 'tensorhive/controllers/responses.yml')) as f:
+        responses = yaml.safe_load(f)                               # what tensorhive/config.py:177-180 loads into API.RESPONSES
+    ident = lambda fn: fn
+    _module('flask_jwt_extended', get_jwt_claims=None, get_jwt_identity=None, jwt_required=ident)
+    _module('tensorhive.config', API=types.SimpleNamespace(RESPONSES=responses))
+    _module('tensorhive.models.User', User=type('User', (), {}))
+    _package('tensorhive.exceptions')
+    _module('tensorhive.exceptions.ForbiddenException', ForbiddenException=type('ForbiddenException', (Exception,), {}))
+    _package('tensorhive.controllers')
+    ref['controller'] = _load('tensorhive/controllers/reservation.py')
     logging.getLogger('tensorhive').setLevel(logging.CRITICAL + 1)          # save() logs every refused row
     return ref
 
@@ -596,6 +625,61 @@ def run_verifier(ref, w):
     return {'table': table, 'restored': restored}
 
 
+API_FMT = '%Y-%m-%dT%H:%M:%S.%fZ'
+
+
+def make_view_world(seed):
+    """A calendar for the range endpoint: rows with owners (one owner in the odd worlds has no user row), titles, results of
+    the usage logger, created_at; probes in the API's string format, some malformed, some with arguments missing."""
+    rng = np.random.default_rng(9500 + seed)
+    H = 1_800_000_000
+    uuids = [synth.uuid_string(k) for k in range(4)]
+    rows = []
+    for i in range(int(rng.integers(5, 40))):
+        start = synth.T0_US + int(rng.integers(0, 60)) * H + int(rng.integers(0, 3)) * 250_000
+        rows.append({'id': i + 1, 'resource_id': uuids[int(rng.integers(0, 3))], 'start_us': start,
+                     'end_us': start + int(rng.integers(1, 9)) * H, 'user_id': int(rng.integers(1, 5)),
+                     'is_cancelled': [None, False, True][int(rng.choice(3, p=[0.6, 0.2, 0.2]))], 'title': 'res %d' % i,
+                     'description': 'd' * int(rng.integers(0, 5)), 'gpu_util_avg': [None, int(rng.integers(0, 101))][int(rng.integers(0, 2))],
+                     'mem_util_avg': [None, int(rng.integers(0, 101))][int(rng.integers(0, 2))],
+                     'created_at_us': synth.T0_US - int(rng.integers(0, 10)) * H})
+    users = [[u, 'user%d' % u] for u in range(1, 5) if not (seed % 2 == 1 and u == 4)]
+    probes = []
+    for _ in range(14):
+        a = synth.T0_US + int(rng.integers(-5, 70)) * H + int(rng.integers(0, 2)) * 250_000
+        b = a + int(rng.integers(0, 30)) * H
+        k = int(rng.integers(1, 5))
+        probes.append({'resources_ids': [uuids[int(x)] for x in rng.permutation(4)[:k]], 'start': at(a).strftime(API_FMT),
+                       'end': at(b).strftime(API_FMT)})
+    probes += [{'resources_ids': uuids[:2], 'start': at(synth.T0_US).strftime('%Y_%m_%dT%H:%M:%S.%fZ'), 'end': at(synth.T0_US + H).strftime(API_FMT)},
+               {'resources_ids': uuids[:2], 'start': at(synth.T0_US).strftime(API_FMT), 'end': '2026-13-45T00:00:00.000Z'},
+               {'resources_ids': None, 'start': at(synth.T0_US).strftime(API_FMT), 'end': at(synth.T0_US + H).strftime(API_FMT)},
+               {'resources_ids': [], 'start': at(synth.T0_US).strftime(API_FMT), 'end': at(synth.T0_US + H).strftime(API_FMT)},
+               {'resources_ids': uuids[:1], 'start': None, 'end': at(synth.T0_US + H).strftime(API_FMT)},
+               {'resources_ids': uuids, 'start': at(synth.T0_US - 100 * H).strftime(API_FMT), 'end': at(synth.T0_US + 200 * H).strftime(API_FMT)}]
+    return {'seed': seed, 'rows': rows, 'users': users, 'probes': probes}
+
+
+def run_view(ref, w):
+    R = ref['model'].Reservation
+    plain = lambda us: dt.datetime(1970, 1, 1) + dt.timedelta(microseconds=us)      # the ORM hands out plain datetimes
+    users = {u: types.SimpleNamespace(id=u, username=name) for u, name in w['users']}
+    Table.rows, Table.seq = [], len(w['rows'])
+    for c in w['rows']:
+        r = R.__new__(R)
+        r.id, r.resource_id, r.user_id = c['id'], c['resource_id'], c['user_id']
+        r._start, r._end, r._is_cancelled = plain(c['start_us']), plain(c['end_us']), c['is_cancelled']
+        r.title, r.description = c['title'], c['description']
+        r.gpu_util_avg, r.mem_util_avg, r.created_at = c['gpu_util_avg'], c['mem_util_avg'], plain(c['created_at_us'])
+        r.user = users.get(c['user_id'])
+        Table.rows.append(r)
+    out = []
+    for p in w['probes']:
+        content, status = ref['controller'].get_selected(p['resources_ids'], p['start'], p['end'])
+        out.append({'status': status, 'content': content})
+    return out
+
+
 def main():
     ref = load_reference()
     ran = selfcheck(ref)
@@ -614,6 +698,11 @@ def main():
         w = make_verifier_world(seed)
         w['expect'] = run_verifier(ref, w)
         verifier_worlds.append(w)
+    view_worlds = []
+    for seed in range(8):
+        w = make_view_world(seed)
+        w['expect'] = run_view(ref, w)
+        view_worlds.append(w)
     header = {
         'what': 'inputs and outputs of the reference\'s own Reservation model methods, executed under an expression-'
                 'evaluating stand-in for SQLAlchemy (see tests/golden/make_reference_model_vectors.py)',
@@ -628,12 +717,15 @@ def main():
     }
     path = os.path.join(HERE, 'reference_model_vectors.json')
     with open(path, 'w') as f:
-        json.dump({'header': header, 'worlds': worlds, 'write_scripts': scripts, 'verifier_worlds': verifier_worlds}, f,
+        json.dump({'header': header, 'worlds': worlds, 'write_scripts': scripts, 'verifier_worlds': verifier_worlds,
+                   'view_worlds': view_worlds}, f,
                   separators=(',', ':'))
     n_probe = sum(len(v) for w in worlds for v in w['probes'].values())
     n_true = sum(x['verdict'] for w in worlds for x in w['expect']['interfere'])
     print('wrote %s: %d worlds, %d probes (%d interfering), %d write scripts, %.0f KB' % (
         path, len(worlds), n_probe, n_true, len(scripts), os.path.getsize(path) / 1e3))
+    print(' view worlds: statuses', sorted({x['status'] for w in view_worlds for x in w['expect']}),
+          'rows returned', sum(len(x['content']) for w in view_worlds for x in w['expect'] if x['status'] == 200))
     print(' verifier worlds:', [(len(w['expect']['table']), len(w['expect']['restored'])) for w in verifier_worlds])
     for s in scripts:
         res = [x['result'] + (':' + x.get('message', '')[:28] if 'message' in x else '') for x in s['expect']['steps']]

@@ -184,3 +184,29 @@ def test_bulk_revalidation_matches_the_executed_reference(dropin, w):
     back = dropin.reservations_that_may_be_restored(mine, is_allowed=lambda r: r.id % w['denied_mod'] != 0)
     assert [r.id for r in back] == w['expect']['restored']
     cal.close()
+
+
+class _User:
+    def __init__(self, uid, username):
+        self.id, self.username = uid, username
+
+
+@pytest.mark.parametrize('w', VEC['view_worlds'], ids=['view%d' % w['seed'] for w in VEC['view_worlds']])
+def test_calendar_view_matches_the_executed_reference(dropin, w):
+    """controllers/reservation.py:31-55 `get_selected` executed from the reference's source (with Reservation.as_dict and
+    CRUDModel.as_dict): the same content and status from the drop-in -- row dicts key by key, 400 for malformed or missing
+    arguments with the same message, 500 when a row's owner has no user."""
+    from tensorhive_fixed_b200.calendar import Calendar
+    recs = []
+    for c in w['rows']:
+        r = dropin.Reservation(id=c['id'], resource_id=c['resource_id'], start=at(c['start_us']), end=at(c['end_us']),
+                               user_id=c['user_id'], is_cancelled=c['is_cancelled'], title=c['title'], description=c['description'])
+        r.gpu_util_avg, r.mem_util_avg, r.created_at = c['gpu_util_avg'], c['mem_util_avg'], at(c['created_at_us'])
+        recs.append(r)
+    cal = Calendar(recs, users={u: _User(u, name) for u, name in w['users']})
+    dropin.bind(cal)
+    for p, want in zip(w['probes'], w['expect']):
+        content, status = dropin.get_selected(p['resources_ids'], p['start'], p['end'])
+        assert status == want['status'], p
+        assert content == want['content'], p
+    cal.close()

@@ -112,6 +112,7 @@ test_calendar_view = G.test_calendar_view_controller
 test_model_methods = M.test_model_methods_match_the_executed_reference
 test_write_path = M.test_write_path_matches_the_executed_reference
 test_bulk_revalidation_vectors = M.test_bulk_revalidation_matches_the_executed_reference
+test_calendar_view_vectors = M.test_calendar_view_matches_the_executed_reference
 # ... and the service loops (V, J1-J3) against the vectors of the executed reference services
 test_services = E.test_services_match_the_executed_reference
 

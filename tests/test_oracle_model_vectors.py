@@ -20,7 +20,7 @@ def test_header_names_what_was_executed():
     h = VEC['header']
     files = {e['file'] for e in h['executed']}
     assert {'tensorhive/models/Reservation.py', 'tensorhive/models/CRUDModel.py', 'tensorhive/utils/DateUtils.py',
-            'tensorhive/core/utils/ReservationVerifier.py'} <= files
+            'tensorhive/core/utils/ReservationVerifier.py', 'tensorhive/controllers/reservation.py'} <= files
     assert all(len(e['sha256']) == 64 and e['bodies'] for e in h['executed'])
     assert len(h['stand_in_checked_by']['tests_passed']) == 6           # the reference's own six model tests
     ref = os.environ.get('TH_REFERENCE_ROOT', '/root/reference')
@@ -93,6 +93,7 @@ def test_vectors_are_not_trivial():
     assert any(x for w in WORLDS for x in w['expect']['upcoming'] if len(x) > 2)
     assert any(x for w in WORLDS for x in w['expect']['range'] if len(x) > 5)
     assert sum(len(w['expect']['restored']) for w in VEC['verifier_worlds']) >= 20
+    assert {x['status'] for w in VEC['view_worlds'] for x in w['expect']} == {200, 400, 500}
     msgs = {s.get('message') for sc in VEC['write_scripts'] for s in sc['expect']['steps']}
     assert {'Reservation would interfere with some other reservation!', 'Reservation duration is too short!',
             'Reservation duration is too long!', 'Reservation owner must be given!',
